@@ -1,0 +1,1 @@
+#include "itk_shim.h"
