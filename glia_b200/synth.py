@@ -1,0 +1,103 @@
+"""Seeded synthetic EM-like inputs: jittered-grid Voronoi superpixels and a
+dyadic boundary-probability map.  Pure integer hashing, so the CUDA generator in
+csrc/synth.cu (used by bench.py for the 1024^3 volume) produces the same labels.
+
+labels: uint32, cell index + 1 (label 0 is reserved by the reference as a scratch key,
+util/struct_merge_bc.hxx:19-20).  pb: float32 q/256, q in [0,255], ridge ~1 on superpixel faces.
+"""
+import numpy as np
+
+_M = np.uint64(0xFFFFFFFF)
+
+
+def _hash32(x):
+    """murmur3 finaliser on uint32 arrays (held in uint64 to avoid overflow warnings)."""
+    x = x.astype(np.uint64) & _M
+    x ^= x >> np.uint64(16)
+    x = (x * np.uint64(0x85EBCA6B)) & _M
+    x ^= x >> np.uint64(13)
+    x = (x * np.uint64(0xC2B2AE35)) & _M
+    x ^= x >> np.uint64(16)
+    return x
+
+
+def seed_positions(shape_xyz, cell, seed):
+    """Fixed-point (1/256 voxel) seed position of every grid cell: [ncell, ndim] int64."""
+    nd = len(shape_xyz)
+    nc = [(s + cell - 1) // cell for s in shape_xyz]
+    idx = np.arange(int(np.prod(nc)), dtype=np.uint64)
+    coords = []
+    rem = idx.copy()
+    for d in range(nd):  # x fastest
+        coords.append(rem % np.uint64(nc[d]))
+        rem = rem // np.uint64(nc[d])
+    pos = np.zeros((len(idx), nd), np.int64)
+    for d in range(nd):
+        u = _hash32((np.uint64(seed) * np.uint64(0x9E3779B9) + idx * np.uint64(4) + np.uint64(d)) & _M) >> np.uint64(8)
+        pos[:, d] = (coords[d] * np.uint64(cell * 256) + ((u * np.uint64(cell * 256)) >> np.uint64(24))).astype(np.int64)
+    return pos, nc
+
+
+def voronoi_volume(shape, cell, seed=1234):
+    """shape in numpy order ([z,] y, x).  Returns (labels uint32, pb float32)."""
+    nd = len(shape)
+    sx = list(shape[::-1])
+    pos, nc = seed_positions(sx, cell, seed)
+    N = int(np.prod(shape))
+    lin = np.arange(N, dtype=np.int64)
+    xyz = []
+    rem = lin.copy()
+    for d in range(nd):
+        xyz.append(rem % sx[d])
+        rem //= sx[d]
+    c = [v // cell for v in xyz]
+    best1 = np.full(N, np.iinfo(np.int64).max, np.int64)
+    best2 = best1.copy()
+    lab = np.zeros(N, np.int64)
+    offs = np.stack(np.meshgrid(*[[-1, 0, 1]] * nd, indexing="ij"), -1).reshape(-1, nd)
+    # visit neighbour cells in ascending cell-index order so ties keep the lower index
+    offs = offs[np.lexsort([offs[:, d] for d in range(nd)])]
+    for o in offs:
+        cc = [c[d] + o[d] for d in range(nd)]
+        ok = np.ones(N, bool)
+        for d in range(nd):
+            ok &= (cc[d] >= 0) & (cc[d] < nc[d])
+        ci = np.zeros(N, np.int64)
+        mul = 1
+        for d in range(nd):
+            ci += np.where(ok, cc[d], 0) * mul
+            mul *= nc[d]
+        d2 = np.zeros(N, np.int64)
+        for d in range(nd):
+            dd = xyz[d] * 256 - pos[ci, d]
+            d2 += dd * dd
+        d2 = np.where(ok, d2, np.iinfo(np.int64).max)
+        closer = d2 < best1
+        best2 = np.where(closer, best1, np.minimum(best2, d2))
+        lab = np.where(closer, ci, lab)
+        best1 = np.where(closer, d2, best1)
+    d1 = np.sqrt(best1.astype(np.float64)) / 256.0
+    has2 = best2 < np.iinfo(np.int64).max
+    d2v = np.where(has2, np.sqrt(np.where(has2, best2, 0).astype(np.float64)) / 256.0, d1 + 1e9)
+    u = _hash32((np.uint64(seed) * np.uint64(0x85EBCA77) + np.uint64(0x1234567) + lin.astype(np.uint64)) & _M)
+    u = u.astype(np.float64) / 4294967296.0
+    val = 0.8 * np.exp(-(d2v - d1) / 2.0) + 0.2 * u
+    q = np.floor(255.0 * np.clip(val, 0.0, 1.0))
+    pb = (q / 256.0).astype(np.float32)
+    return (lab + 1).astype(np.uint32).reshape(shape), pb.reshape(shape)
+
+
+def speckle_volume(shape, nlabels, seed=0, dyadic=True):
+    """Random-speckle labels: many tiny/disconnected regions, non-mutual edges, equal areas —
+    the adversarial case for the RAG rules."""
+    rng = np.random.default_rng(seed)
+    lab = rng.integers(1, nlabels + 1, size=shape, dtype=np.uint32)
+    # smooth a little so that regions have some extent
+    for ax in range(len(shape)):
+        keep = rng.random(shape) < 0.6
+        lab = np.where(keep, np.roll(lab, 1, axis=ax), lab)
+    if dyadic:
+        pb = (rng.integers(0, 256, size=shape) / 256.0).astype(np.float32)
+    else:
+        pb = rng.random(shape, dtype=np.float32)
+    return lab.astype(np.uint32), pb

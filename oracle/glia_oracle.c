@@ -1,0 +1,753 @@
+/* TEST INFRASTRUCTURE — not part of the product.  See glia_oracle.h.
+ *
+ * CPU restatement of GLIA's hmt feature + merge-order path.  Each function
+ * cites the reference code it follows (paths relative to
+ * /root/reference/code).  The restatement works on mergeable statistics
+ * (per base region, per directed base edge) instead of pixel lists; that this
+ * reproduces the reference exactly is what tests/test_oracle_vs_ref.py pins
+ * against oracle/_ref (the unmodified reference headers).
+ */
+#include "glia_oracle.h"
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <float.h>
+
+#define FEPS 2.22e-16 /* glia_base.hxx:59 */
+static double sdivide(double a, double b, double d) { return fabs(b) >= FEPS ? a / b : d; } /* :77 */
+static double slog(double x, double d) { return x > 0.0 ? log(x) : d; }                      /* :80 */
+static double ssqrt(double x, double d) { return x >= 0.0 ? sqrt(x) : d; }                   /* :83 */
+
+/* mergeable statistics of a voxel multiset w.r.t. one image */
+typedef struct {
+  uint64_t n;
+  uint64_t* hist; /* bins */
+  double s, s2;
+  double mn, mx; /* DBL_MAX / -DBL_MAX when n == 0 */
+} stat_t;
+
+typedef struct { int bins; double lo, hi; double* bounds; const float* img; } imgspec;
+
+struct go_state {
+  go_cfg cfg;
+  int D, R, E, C;
+  size_t nvox;
+  uint32_t* label;          /* [R] ascending */
+  uint32_t* cnt; uint32_t* border;
+  int32_t* bbmin; int32_t* bbmax; /* [R][3] */
+  imgspec rs[GO_MAX_IMG], rls[GO_MAX_IMG], bs[GO_MAX_IMG];
+  stat_t* rstat[GO_MAX_IMG];  /* [R] */
+  stat_t* rlstat[GO_MAX_IMG]; /* [R] */
+  /* directed edges sorted by (a,b) index */
+  int* ea; int* eb; uint32_t* ecnt; int* rev; /* rev[e] = index of (b,a) or -1 */
+  uint32_t* ethr;           /* [E][T] */
+  stat_t* estat[GO_MAX_IMG]; /* [E] */
+  int* row;                 /* CSR by a: [R+1] */
+  /* incoming edge lists (for non-mutual lookups): in_row [R+1], in_e */
+  double normArea, normLen;
+  /* scratch */
+  int* mark; int stamp;
+  int* mark2;
+};
+
+static void stat_init(stat_t* s, int bins) {
+  s->n = 0; s->s = s->s2 = 0; s->mn = DBL_MAX; s->mx = -DBL_MAX;
+  s->hist = (uint64_t*)calloc((size_t)(bins > 0 ? bins : 1), 8);
+}
+static void stat_clear(stat_t* s, int bins) {
+  s->n = 0; s->s = s->s2 = 0; s->mn = DBL_MAX; s->mx = -DBL_MAX;
+  memset(s->hist, 0, (size_t)bins * 8);
+}
+static void stat_merge(stat_t* d, const stat_t* s, int bins) {
+  d->n += s->n; d->s += s->s; d->s2 += s->s2;
+  if (s->mn < d->mn) d->mn = s->mn;
+  if (s->mx > d->mx) d->mx = s->mx;
+  for (int i = 0; i < bins; ++i) d->hist[i] += s->hist[i];
+}
+
+/* util/image_stats.hxx:12-36 — cumulative bounds, not offset by lo; a value in
+ * (lo,hi) that is >= the last bound falls in no bin. Returns bin or -1. */
+static int hist_bin(const imgspec* sp, float val) {
+  double v = (double)val;
+  if (v > sp->lo && v < sp->hi) {
+    for (int i = 0; i < sp->bins; ++i) if (v < sp->bounds[i]) return i;
+    return -1;
+  } else if (v <= sp->lo) return 0;
+  return sp->bins - 1;
+}
+static void stat_add(stat_t* s, const imgspec* sp, float val) {
+  s->n++;
+  int b = hist_bin(sp, val);
+  if (b >= 0) s->hist[b]++;
+  s->s += val;                       /* type/feat.hxx:730 */
+  s->s2 += (double)val * val;        /* :731 */
+  if (val < s->mn) s->mn = val;
+  if (val > s->mx) s->mx = val;
+}
+static void spec_init(imgspec* sp, const float* img, int bins, double lo, double hi) {
+  sp->img = img; sp->bins = bins; sp->lo = lo; sp->hi = hi;
+  sp->bounds = (double*)malloc(8 * (size_t)(bins > 0 ? bins : 1));
+  double interval = (hi - lo) / bins;
+  sp->bounds[0] = interval;
+  for (int i = 1; i < bins; ++i) sp->bounds[i] = sp->bounds[i - 1] + interval;
+}
+
+static int cmp_u32(const void* a, const void* b) {
+  uint32_t x = *(const uint32_t*)a, y = *(const uint32_t*)b;
+  return x < y ? -1 : x > y;
+}
+static int cmp_u64(const void* a, const void* b) {
+  uint64_t x = *(const uint64_t*)a, y = *(const uint64_t*)b;
+  return x < y ? -1 : x > y;
+}
+static int find_u32(const uint32_t* a, int n, uint32_t v) {
+  int lo = 0, hi = n - 1;
+  while (lo <= hi) { int m = (lo + hi) >> 1; if (a[m] == v) return m; if (a[m] < v) lo = m + 1; else hi = m - 1; }
+  return -1;
+}
+static int find_u64(const uint64_t* a, int n, uint64_t v) {
+  int lo = 0, hi = n - 1;
+  while (lo <= hi) { int m = (lo + hi) >> 1; if (a[m] == v) return m; if (a[m] < v) lo = m + 1; else hi = m - 1; }
+  return -1;
+}
+
+/* type/neighbor.hxx:72-126 + util/struct.hxx:95-108: first differing valid
+ * neighbour in order d0-,d0+,d1-,d1+,(d2-,d2+); nvalid counts in-image,
+ * unmasked neighbours.  Returns 1 boundary (nb set), 2 border, 0 interior. */
+static int classify(const go_state* s, const uint32_t* L, const uint32_t* M, size_t p,
+                    const int* xyz, uint32_t* nb) {
+  const int* dims = s->cfg.dims;
+  size_t stride[3] = {1, (size_t)dims[0], (size_t)dims[0] * dims[1]};
+  uint32_t me = L[p];
+  int nvalid = 0, found = 0;
+  for (int d = 0; d < s->D; ++d) {
+    for (int sgn = -1; sgn <= 1; sgn += 2) {
+      int c = xyz[d] + sgn;
+      if (c < 0 || c >= dims[d]) continue;
+      size_t q = sgn < 0 ? p - stride[d] : p + stride[d];
+      if (M && M[q] == 0) continue;
+      ++nvalid;
+      if (!found && L[q] != me) { found = 1; *nb = L[q]; }
+    }
+  }
+  if (found) return 1;
+  return nvalid < 2 * s->D ? 2 : 0;
+}
+
+go_state* go_build(const go_cfg* cfg, const uint32_t* L, const uint32_t* M, const float* pb) {
+  go_state* s = (go_state*)calloc(1, sizeof(*s));
+  s->cfg = *cfg;
+  s->D = cfg->ndim;
+  if (s->D == 2) s->cfg.dims[2] = 1;
+  const int* dims = s->cfg.dims;
+  size_t N = (size_t)dims[0] * dims[1] * dims[2];
+  s->nvox = N;
+  /* main_merge_order_bc.cxx:36-39; util/image.hxx:173-192 */
+  double diag = 0; for (int d = 0; d < s->D; ++d) diag += (double)dims[d] * dims[d];
+  s->normArea = cfg->normalize ? (double)N : 1.0;
+  s->normLen = cfg->normalize ? sqrt(diag) : 1.0;
+  for (int i = 0; i < cfg->n_rimg; ++i) spec_init(&s->rs[i], cfg->rimg[i], cfg->rbins[i], cfg->rlo[i], cfg->rhi[i]);
+  for (int i = 0; i < cfg->n_rlimg; ++i) spec_init(&s->rls[i], cfg->rlimg[i], cfg->rlbins[i], cfg->rllo[i], cfg->rlhi[i]);
+  for (int i = 0; i < cfg->n_bimg; ++i) spec_init(&s->bs[i], cfg->bimg[i], cfg->bbins[i], cfg->blo[i], cfg->bhi[i]);
+  /* labels present (unmasked voxels only): util/struct.hxx:61-92 */
+  uint32_t* tmp = (uint32_t*)malloc(4 * (N ? N : 1));
+  size_t nu = 0;
+  for (size_t p = 0; p < N; ++p) if (!M || M[p] != 0) tmp[nu++] = L[p];
+  qsort(tmp, nu, 4, cmp_u32);
+  int R = 0;
+  for (size_t i = 0; i < nu; ++i) if (i == 0 || tmp[i] != tmp[i - 1]) tmp[R++] = tmp[i];
+  s->R = R;
+  s->label = (uint32_t*)malloc(4 * (size_t)(R ? R : 1));
+  memcpy(s->label, tmp, 4 * (size_t)R);
+  free(tmp);
+  s->cnt = (uint32_t*)calloc((size_t)R + 1, 4);
+  s->border = (uint32_t*)calloc((size_t)R + 1, 4);
+  s->bbmin = (int32_t*)malloc(12 * ((size_t)R + 1));
+  s->bbmax = (int32_t*)malloc(12 * ((size_t)R + 1));
+  for (int i = 0; i < 3 * R; ++i) { s->bbmin[i] = INT32_MAX; s->bbmax[i] = INT32_MIN; }
+  for (int i = 0; i < cfg->n_rimg; ++i) {
+    s->rstat[i] = (stat_t*)malloc(sizeof(stat_t) * ((size_t)R + 1));
+    for (int r = 0; r < R; ++r) stat_init(&s->rstat[i][r], s->rs[i].bins);
+  }
+  for (int i = 0; i < cfg->n_rlimg; ++i) {
+    s->rlstat[i] = (stat_t*)malloc(sizeof(stat_t) * ((size_t)R + 1));
+    for (int r = 0; r < R; ++r) stat_init(&s->rlstat[i][r], s->rls[i].bins);
+  }
+  /* pass 1: classify every voxel, region stats, collect directed keys */
+  uint8_t* cls = (uint8_t*)malloc(N ? N : 1);
+  uint64_t* vkey = (uint64_t*)malloc(8 * (N ? N : 1)); /* per boundary voxel */
+  size_t nb = 0;
+  size_t p = 0;
+  int xyz[3];
+  for (xyz[2] = 0; xyz[2] < dims[2]; ++xyz[2])
+    for (xyz[1] = 0; xyz[1] < dims[1]; ++xyz[1])
+      for (xyz[0] = 0; xyz[0] < dims[0]; ++xyz[0], ++p) {
+        cls[p] = 0;
+        if (M && M[p] == 0) continue;
+        int a = find_u32(s->label, R, L[p]);
+        s->cnt[a]++;
+        for (int d = 0; d < s->D; ++d) { /* alg/geometry.hxx:21-39 */
+          if (xyz[d] < s->bbmin[3 * a + d]) s->bbmin[3 * a + d] = xyz[d];
+          if (xyz[d] > s->bbmax[3 * a + d]) s->bbmax[3 * a + d] = xyz[d];
+        }
+        for (int i = 0; i < cfg->n_rimg; ++i) stat_add(&s->rstat[i][a], &s->rs[i], s->rs[i].img[p]);
+        for (int i = 0; i < cfg->n_rlimg; ++i) stat_add(&s->rlstat[i][a], &s->rls[i], s->rls[i].img[p]);
+        uint32_t nbl = 0;
+        int c = classify(s, L, M, p, xyz, &nbl);
+        if (c == 2) s->border[a]++;
+        if (c == 1) {
+          int b = find_u32(s->label, R, nbl);
+          vkey[p] = ((uint64_t)a << 32) | (uint32_t)b;
+          cls[p] = 1;
+          ++nb;
+        }
+      }
+  uint64_t* keys = (uint64_t*)malloc(8 * (nb ? nb : 1));
+  size_t k = 0;
+  for (p = 0; p < N; ++p) if (cls[p]) keys[k++] = vkey[p];
+  qsort(keys, nb, 8, cmp_u64);
+  int E = 0;
+  for (size_t i = 0; i < nb; ++i) if (i == 0 || keys[i] != keys[i - 1]) keys[E++] = keys[i];
+  s->E = E;
+  int T = cfg->n_thr;
+  s->ea = (int*)malloc(4 * ((size_t)E + 1)); s->eb = (int*)malloc(4 * ((size_t)E + 1));
+  s->ecnt = (uint32_t*)calloc((size_t)E + 1, 4);
+  s->rev = (int*)malloc(4 * ((size_t)E + 1));
+  s->ethr = (uint32_t*)calloc(((size_t)E + 1) * (T ? T : 1), 4);
+  s->row = (int*)calloc((size_t)R + 2, 4);
+  for (int e = 0; e < E; ++e) {
+    s->ea[e] = (int)(keys[e] >> 32); s->eb[e] = (int)(keys[e] & 0xffffffffu);
+    s->row[s->ea[e] + 1]++;
+  }
+  for (int r = 0; r < R; ++r) s->row[r + 1] += s->row[r];
+  s->C = 0;
+  for (int e = 0; e < E; ++e) {
+    s->rev[e] = find_u64(keys, E, ((uint64_t)s->eb[e] << 32) | (uint32_t)s->ea[e]);
+    if (s->rev[e] >= 0 && s->ea[e] < s->eb[e]) s->C++;
+  }
+  for (int i = 0; i < cfg->n_bimg; ++i) {
+    s->estat[i] = (stat_t*)malloc(sizeof(stat_t) * ((size_t)E + 1));
+    for (int e = 0; e < E; ++e) stat_init(&s->estat[i][e], s->bs[i].bins);
+  }
+  /* pass 2: per directed edge statistics */
+  for (p = 0; p < N; ++p) {
+    if (!cls[p]) continue;
+    int e = find_u64(keys, E, vkey[p]);
+    s->ecnt[e]++;
+    for (int t = 0; t < T; ++t) if ((double)pb[p] >= cfg->thr[t]) s->ethr[(size_t)e * T + t]++; /* feat.hxx:498 */
+    for (int i = 0; i < cfg->n_bimg; ++i) stat_add(&s->estat[i][e], &s->bs[i], s->bs[i].img[p]);
+  }
+  free(keys); free(vkey); free(cls);
+  s->mark = (int*)calloc((size_t)R + 1, 4);
+  s->mark2 = (int*)calloc((size_t)R + 1, 4);
+  s->stamp = 0;
+  return s;
+}
+
+static void stat_free_arr(stat_t* a, int n) {
+  if (!a) return;
+  for (int i = 0; i < n; ++i) free(a[i].hist);
+  free(a);
+}
+void go_free(go_state* s) {
+  if (!s) return;
+  for (int i = 0; i < GO_MAX_IMG; ++i) {
+    stat_free_arr(s->rstat[i], s->R); stat_free_arr(s->rlstat[i], s->R); stat_free_arr(s->estat[i], s->E);
+    free(s->rs[i].bounds); free(s->rls[i].bounds); free(s->bs[i].bounds);
+  }
+  free(s->label); free(s->cnt); free(s->border); free(s->bbmin); free(s->bbmax);
+  free(s->ea); free(s->eb); free(s->ecnt); free(s->rev); free(s->ethr); free(s->row);
+  free(s->mark); free(s->mark2); free(s);
+}
+int go_num_regions(const go_state* s) { return s->R; }
+int go_num_edges(const go_state* s) { return s->E; }
+int go_num_candidates(const go_state* s) { return s->C; }
+
+void go_get_regions(const go_state* s, uint32_t* label, uint32_t* count, uint32_t* border,
+                    int32_t* bbmin, int32_t* bbmax) {
+  if (label) memcpy(label, s->label, 4 * (size_t)s->R);
+  if (count) memcpy(count, s->cnt, 4 * (size_t)s->R);
+  if (border) memcpy(border, s->border, 4 * (size_t)s->R);
+  if (bbmin) memcpy(bbmin, s->bbmin, 12 * (size_t)s->R);
+  if (bbmax) memcpy(bbmax, s->bbmax, 12 * (size_t)s->R);
+}
+static void dump_stats(const stat_t* st, int n, int bins, uint32_t* hist, double* sum, double* sum2,
+                       float* mn, float* mx) {
+  for (int i = 0; i < n; ++i) {
+    if (hist) for (int b = 0; b < bins; ++b) hist[(size_t)i * bins + b] = (uint32_t)st[i].hist[b];
+    if (sum) sum[i] = st[i].s;
+    if (sum2) sum2[i] = st[i].s2;
+    if (mn) mn[i] = (float)st[i].mn;
+    if (mx) mx[i] = (float)st[i].mx;
+  }
+}
+void go_get_region_stats(const go_state* s, int kind, int i, uint32_t* hist, double* sum,
+                         double* sum2, float* mn, float* mx) {
+  if (kind == 0) dump_stats(s->rstat[i], s->R, s->rs[i].bins, hist, sum, sum2, mn, mx);
+  else dump_stats(s->rlstat[i], s->R, s->rls[i].bins, hist, sum, sum2, mn, mx);
+}
+void go_get_edges(const go_state* s, uint32_t* a, uint32_t* b, uint32_t* count, uint8_t* mutual,
+                  uint32_t* thr_count) {
+  for (int e = 0; e < s->E; ++e) {
+    if (a) a[e] = s->label[s->ea[e]];
+    if (b) b[e] = s->label[s->eb[e]];
+    if (count) count[e] = s->ecnt[e];
+    if (mutual) mutual[e] = s->rev[e] >= 0;
+  }
+  if (thr_count) memcpy(thr_count, s->ethr, 4 * (size_t)s->E * s->cfg.n_thr);
+}
+void go_get_edge_stats(const go_state* s, int i, uint32_t* hist, double* sum, double* sum2,
+                       float* mn, float* mx) {
+  dump_stats(s->estat[i], s->E, s->bs[i].bins, hist, sum, sum2, mn, mx);
+}
+
+/* ------------------------------------------------------------------------
+ * Features of a region given as a set of base regions (type/region.hxx:66-75,
+ * type/feat.hxx:71-90, :485-502, :632-638, :706-738; hmt/bc_feat.hxx:88-127).
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  double entropy, mean, stddev, mn, mx;
+  double hist[256];
+} imgfeat;
+
+typedef struct {
+  double area, perim, compactness, bboxArea, bboxSize[3];
+  double validPerims[GO_MAX_THR], rValidPerims[GO_MAX_THR];
+  imgfeat region[GO_MAX_IMG], labelRegion[GO_MAX_IMG], boundary[GO_MAX_IMG];
+  int has_sal; double sal;
+} regfeat;
+
+/* util/image_stats.hxx:39-53, util/stats.hxx:145-152, type/feat.hxx:706-738 */
+static void img_feats(imgfeat* f, const stat_t* st, int bins) {
+  uint32_t n = (uint32_t)st->n;
+  f->entropy = 0.0;
+  for (int i = 0; i < bins; ++i) f->hist[i] = n ? st->hist[i] / (double)n : 0.0;
+  for (int i = 0; i < bins; ++i)
+    if (!(fabs(f->hist[i] - 0.0) < FEPS)) f->entropy -= f->hist[i] * log2(f->hist[i]);
+  if (n == 0) { f->mean = f->stddev = f->mn = f->mx = 0.0; return; }
+  int ni = (int)n;
+  f->mean = st->s / ni;
+  f->stddev = ssqrt(st->s2 / ni - f->mean * f->mean, 0.0);
+  f->mn = st->mn; f->mx = st->mx;
+}
+
+static stat_t g_tmp; static int g_tmp_bins = 0;
+static stat_t* tmp_stat(int bins) {
+  if (g_tmp_bins < 256) { free(g_tmp.hist); g_tmp.hist = (uint64_t*)calloc(256, 8); g_tmp_bins = 256; }
+  stat_clear(&g_tmp, bins > 0 ? bins : 1);
+  return &g_tmp;
+}
+
+/* is directed edge e of a region (membership marks == stamp) still an entry? */
+#define LIVE(s, e, mk, st) (!((mk)[(s)->eb[e]] == (st) && (s)->rev[e] >= 0))
+
+static void region_feats(go_state* s, const int* S, int n, regfeat* f, const double* sal) {
+  const go_cfg* c = &s->cfg;
+  int D = s->D, T = c->n_thr;
+  int st = ++s->stamp;
+  for (int i = 0; i < n; ++i) s->mark[S[i]] = st;
+  uint64_t area = 0, nbnd = 0, nborder = 0, vp[GO_MAX_THR] = {0};
+  int32_t mn[3] = {INT32_MAX, INT32_MAX, INT32_MAX}, mx[3] = {INT32_MIN, INT32_MIN, INT32_MIN};
+  for (int i = 0; i < n; ++i) {
+    int a = S[i];
+    area += s->cnt[a]; nborder += s->border[a];
+    for (int d = 0; d < D; ++d) {
+      if (s->bbmin[3 * a + d] < mn[d]) mn[d] = s->bbmin[3 * a + d];
+      if (s->bbmax[3 * a + d] > mx[d]) mx[d] = s->bbmax[3 * a + d];
+    }
+    for (int e = s->row[a]; e < s->row[a + 1]; ++e) {
+      if (!LIVE(s, e, s->mark, st)) continue;
+      nbnd += s->ecnt[e];
+      for (int t = 0; t < T; ++t) vp[t] += s->ethr[(size_t)e * T + t];
+    }
+  }
+  /* RegionShapeFeats::generate, type/feat.hxx:71-90 */
+  f->area = (double)area;
+  f->perim = (double)(nbnd + nborder);
+  f->compactness = sdivide(pow(f->perim, (double)D / (D - 1)), f->area, 0.0);
+  f->area = sdivide(f->area, s->normArea, 0.0);
+  f->perim = sdivide(f->perim, s->normLen, 0.0);
+  f->bboxArea = 1.0;
+  for (int d = 0; d < D; ++d) {
+    double bb = n ? (double)(mx[d] - mn[d]) : 0.0; /* geometry.hxx:36-38: max - min */
+    f->bboxSize[d] = sdivide(bb, s->normLen, 0.0);
+    f->bboxArea *= bb;
+  }
+  f->bboxArea = sdivide(f->bboxArea, s->normArea, 0.0);
+  /* ImageRegionShapeFeats::generate, type/feat.hxx:485-502 */
+  for (int t = 0; t < T; ++t) {
+    f->validPerims[t] = sdivide((double)(uint32_t)vp[t], s->normLen, 0.0);
+    f->rValidPerims[t] = sdivide((double)(uint32_t)vp[t], (double)nbnd, 0.0);
+  }
+  for (int i = 0; i < c->n_rimg; ++i) {
+    stat_t* t = tmp_stat(s->rs[i].bins);
+    for (int j = 0; j < n; ++j) stat_merge(t, &s->rstat[i][S[j]], s->rs[i].bins);
+    img_feats(&f->region[i], t, s->rs[i].bins);
+  }
+  for (int i = 0; i < c->n_rlimg; ++i) {
+    stat_t* t = tmp_stat(s->rls[i].bins);
+    for (int j = 0; j < n; ++j) stat_merge(t, &s->rlstat[i][S[j]], s->rls[i].bins);
+    img_feats(&f->labelRegion[i], t, s->rls[i].bins);
+  }
+  for (int i = 0; i < c->n_bimg; ++i) {
+    stat_t* t = tmp_stat(s->bs[i].bins);
+    for (int j = 0; j < n; ++j)
+      for (int e = s->row[S[j]]; e < s->row[S[j] + 1]; ++e)
+        if (LIVE(s, e, s->mark, st)) stat_merge(t, &s->estat[i][e], s->bs[i].bins);
+    img_feats(&f->boundary[i], t, s->bs[i].bins);
+  }
+  f->has_sal = sal != NULL;
+  f->sal = sal ? *sal : 0.0;
+}
+
+/* util/stats.hxx:155-185 (pow(d,2) == d*d) */
+static double dist_l1(const double* a, const double* b, int n) {
+  double r = 0; for (int i = 0; i < n; ++i) r += fabs(a[i] - b[i]); return r;
+}
+static double dist_x2(const double* a, const double* b, int n) {
+  double r = 0;
+  for (int i = 0; i < n; ++i) { double d = a[i] - b[i]; r += d * d / (a[i] + b[i] + FEPS); }
+  return r;
+}
+
+static void push_region(const go_state* s, const regfeat* f, double** o) {
+  const go_cfg* c = &s->cfg;
+  int lg = c->use_log;
+  double* p = *o;
+  *p++ = lg ? slog(f->area, 0) : f->area;
+  *p++ = lg ? slog(f->perim, 0) : f->perim;
+  *p++ = f->compactness;
+  *p++ = lg ? slog(f->bboxArea, 0) : f->bboxArea;
+  for (int d = 0; d < s->D; ++d) *p++ = lg ? slog(f->bboxSize[d], 0) : f->bboxSize[d];
+  for (int t = 0; t < c->n_thr; ++t) *p++ = lg ? slog(f->validPerims[t], 0) : f->validPerims[t];
+  for (int t = 0; t < c->n_thr; ++t) *p++ = f->rValidPerims[t];
+  for (int i = 0; i < c->n_rimg; ++i) {
+    const imgfeat* g = &f->region[i];
+    *p++ = g->entropy; *p++ = g->mean; *p++ = g->stddev; *p++ = g->mn; *p++ = g->mx;
+  }
+  for (int i = 0; i < c->n_rlimg; ++i) *p++ = f->labelRegion[i].entropy;
+  for (int i = 0; i < c->n_bimg; ++i) {
+    const imgfeat* g = &f->boundary[i];
+    *p++ = g->entropy; *p++ = g->mean; *p++ = g->stddev; *p++ = g->mn; *p++ = g->mx;
+  }
+  if (f->has_sal) *p++ = f->sal;
+  *o = p;
+}
+
+int go_row_dim(const go_state* s, int with_sal) {
+  const go_cfg* c = &s->cfg;
+  if (c->simple) return 5 + c->n_bimg + 4 * c->n_rimg + 2 * c->n_rlimg;
+  int x0 = 11 + 4 * c->n_thr + 7 * c->n_rimg + 3 * c->n_rlimg + 5 * c->n_bimg + (with_sal ? 2 : 0);
+  int xi = s->D + 4 + 2 * c->n_thr + 5 * c->n_rimg + c->n_rlimg + 5 * c->n_bimg + (with_sal ? 1 : 0);
+  return x0 + 3 * xi;
+}
+
+/* Candidate row for regions X, Y (base-index sets) and Z = X u Y
+ * (main_merge_order_bc.cxx:54-95; bc_feat.hxx:179-238; feat.hxx:124-132,
+ * :176-186, :567-589, :663-669, :801-810; util/struct.hxx:10-16;
+ * region.hxx:42-51).  f0,f1,f2 are the RegionFeats of X, Y, Z. */
+static void candidate_row(go_state* s, const int* X, int nx, const int* Y, int ny,
+                          const regfeat* fX, const regfeat* fY, const regfeat* fZ, double* out) {
+  const go_cfg* c = &s->cfg;
+  int T = c->n_thr, lg = c->use_log;
+  const regfeat *f1 = fX, *f2 = fY;
+  if (f1->area > f2->area) { const regfeat* t = f1; f1 = f2; f2 = t; } /* :77-80 */
+  /* pair boundary b(X,Y) */
+  int sx = ++s->stamp; for (int i = 0; i < nx; ++i) s->mark[X[i]] = sx;
+  int sy = ++s->stamp; for (int i = 0; i < ny; ++i) s->mark2[Y[i]] = sy;
+  /* active flags: base region with at least one live entry, stored as sign in a scratch pass */
+  /* (computed on the fly: small sets) */
+  uint64_t nb = 0, vp[GO_MAX_THR] = {0};
+  stat_t bst[GO_MAX_IMG];
+  for (int i = 0; i < c->n_bimg; ++i) stat_init(&bst[i], s->bs[i].bins);
+  for (int side = 0; side < 2; ++side) {
+    const int* A = side ? Y : X; int na = side ? ny : nx;
+    int* mkA = side ? s->mark2 : s->mark; int stA = side ? sy : sx;
+    int* mkB = side ? s->mark : s->mark2; int stB = side ? sx : sy;
+    for (int i = 0; i < na; ++i) {
+      for (int e = s->row[A[i]]; e < s->row[A[i] + 1]; ++e) {
+        if (!LIVE(s, e, mkA, stA)) continue;
+        int b = s->eb[e];
+        if (mkB[b] != stB) continue;
+        /* b must be the first key of some remaining entry of the other region */
+        int act = 0;
+        for (int e2 = s->row[b]; e2 < s->row[b + 1] && !act; ++e2) act = LIVE(s, e2, mkB, stB);
+        if (!act) continue;
+        nb += s->ecnt[e];
+        for (int t = 0; t < T; ++t) vp[t] += s->ethr[(size_t)e * T + t];
+        for (int k = 0; k < c->n_bimg; ++k) stat_merge(&bst[k], &s->estat[k][e], s->bs[k].bins);
+      }
+    }
+  }
+  double* p = out;
+  double areaDiff = fabs(f1->area - f2->area), perimDiff = fabs(f1->perim - f2->perim);
+  double bl = sdivide(ceil((uint32_t)nb / 2.0), s->normLen, 0.0);
+  imgfeat bf[GO_MAX_IMG];
+  for (int k = 0; k < c->n_bimg; ++k) { img_feats(&bf[k], &bst[k], s->bs[k].bins); free(bst[k].hist); }
+  if (c->simple) { /* bc_feat.hxx:247-279 (log applied before selection) */
+    *p++ = lg ? slog(f1->area, 0) : f1->area;
+    *p++ = lg ? slog(f2->area, 0) : f2->area;
+    *p++ = lg ? slog(f1->perim, 0) : f1->perim;
+    *p++ = lg ? slog(f2->perim, 0) : f2->perim;
+    *p++ = lg ? slog(bl, 0) : bl;
+    for (int k = 0; k < c->n_bimg; ++k) *p++ = bf[k].mean;
+    for (int i = 0; i < c->n_rimg; ++i) {
+      const imgfeat *a = &f1->region[i], *b = &f2->region[i];
+      *p++ = fabs(a->mean - b->mean);
+      *p++ = dist_l1(a->hist, b->hist, s->rs[i].bins);
+      *p++ = dist_x2(a->hist, b->hist, s->rs[i].bins);
+      *p++ = fabs(a->entropy - b->entropy);
+    }
+    for (int i = 0; i < c->n_rlimg; ++i) {
+      const imgfeat *a = &f1->labelRegion[i], *b = &f2->labelRegion[i];
+      *p++ = dist_l1(a->hist, b->hist, s->rls[i].bins);
+      *p++ = dist_x2(a->hist, b->hist, s->rls[i].bins);
+    }
+    return;
+  }
+  *p++ = lg ? slog(areaDiff, 0) : areaDiff;
+  *p++ = sdivide(areaDiff, f1->area, 0.0);
+  *p++ = sdivide(areaDiff, f2->area, 0.0);
+  *p++ = lg ? slog(perimDiff, 0) : perimDiff;
+  *p++ = sdivide(perimDiff, f1->perim, 0.0);
+  *p++ = sdivide(perimDiff, f2->perim, 0.0);
+  *p++ = lg ? slog(bl, 0) : bl;
+  *p++ = sdivide(bl, f1->area, 0.0);
+  *p++ = sdivide(bl, f2->area, 0.0);
+  *p++ = sdivide(bl, f1->perim, 0.0);
+  *p++ = sdivide(bl, f2->perim, 0.0);
+  double vbl[GO_MAX_THR];
+  for (int t = 0; t < T; ++t) vbl[t] = sdivide(ceil((uint32_t)vp[t] / 2.0), s->normLen, 0.0);
+  for (int t = 0; t < T; ++t) *p++ = lg ? slog(vbl[t], 0) : vbl[t];
+  for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], bl, 0.0);
+  for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], f1->perim, 0.0);
+  for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], f2->perim, 0.0);
+  for (int i = 0; i < c->n_rimg; ++i) {
+    const imgfeat *a = &f1->region[i], *b = &f2->region[i];
+    *p++ = dist_l1(a->hist, b->hist, s->rs[i].bins);
+    *p++ = dist_x2(a->hist, b->hist, s->rs[i].bins);
+    *p++ = fabs(a->entropy - b->entropy);
+    *p++ = fabs(a->mean - b->mean);
+    *p++ = fabs(a->stddev - b->stddev);
+    *p++ = fabs(a->mn - b->mn);
+    *p++ = fabs(a->mx - b->mx);
+  }
+  for (int i = 0; i < c->n_rlimg; ++i) {
+    const imgfeat *a = &f1->labelRegion[i], *b = &f2->labelRegion[i];
+    *p++ = dist_l1(a->hist, b->hist, s->rls[i].bins);
+    *p++ = dist_x2(a->hist, b->hist, s->rls[i].bins);
+    *p++ = fabs(a->entropy - b->entropy);
+  }
+  for (int k = 0; k < c->n_bimg; ++k) {
+    *p++ = bf[k].entropy; *p++ = bf[k].mean; *p++ = bf[k].stddev; *p++ = bf[k].mn; *p++ = bf[k].mx;
+  }
+  if (f1->has_sal && f2->has_sal && fZ->has_sal) { /* bc_feat.hxx:208-213 */
+    double d02 = fabs(f1->sal - fZ->sal), d12 = fabs(f2->sal - fZ->sal);
+    *p++ = d02 < d12 ? d02 : d12;
+    *p++ = d02 < d12 ? d12 : d02;
+  }
+  push_region(s, f1, &p);
+  push_region(s, f2, &p);
+  push_region(s, fZ, &p);
+}
+
+/* ------------------------------------------------------------------------
+ * Initial candidates: mutual base pairs in ascending (min,max) label order
+ * (type/boundary_table.hxx:91-114; util/struct_merge_bc.hxx:18-23).
+ * ---------------------------------------------------------------------- */
+void go_init_candidates(go_state* s, uint32_t* keys, double* rows, const uint8_t* swap) {
+  int dim = go_row_dim(s, 0), k = 0;
+  regfeat fa, fb, fz;
+  for (int e = 0; e < s->E; ++e) { /* edges are sorted by (a,b): a<b with reverse present */
+    int a = s->ea[e], b = s->eb[e];
+    if (!(a < b && s->rev[e] >= 0)) continue;
+    if (keys) { keys[2 * k] = s->label[a]; keys[2 * k + 1] = s->label[b]; }
+    if (rows) {
+      int Z[2] = {a, b};
+      region_feats(s, &a, 1, &fa, NULL);
+      region_feats(s, &b, 1, &fb, NULL);
+      region_feats(s, Z, 2, &fz, NULL);
+      /* The reference passes the pair in the direction it meets first while
+       * iterating an unordered_map (boundary_table.hxx:93-104); that only matters
+       * when both areas are equal (x1 = first argument).  swap[k] selects (b,a). */
+      if (swap && swap[k]) candidate_row(s, &b, 1, &a, 1, &fb, &fa, &fz, rows + (size_t)k * dim);
+      else candidate_row(s, &a, 1, &b, 1, &fa, &fb, &fz, rows + (size_t)k * dim);
+    }
+    ++k;
+  }
+}
+
+/* ------------------------------------------------------------------------
+ * Greedy merge order (util/struct_merge.hxx:10-33; boundary_table.hxx:47-52,
+ * :121-167).  Table = ordered map keyed (r0<r1); priority = (saliency,
+ * insertion sequence), max first (multimap rbegin: largest key, and among
+ * equal keys the most recently inserted).
+ * ---------------------------------------------------------------------- */
+typedef struct { uint32_t r0, r1; double sal; uint64_t seq; int alive; double* row; } titem;
+typedef struct { titem* it; int n, cap; } ttable; /* kept sorted by (r0,r1) */
+
+static int t_lower(const ttable* t, uint32_t r0, uint32_t r1) {
+  int lo = 0, hi = t->n;
+  while (lo < hi) {
+    int m = (lo + hi) >> 1;
+    const titem* x = &t->it[m];
+    if (x->r0 < r0 || (x->r0 == r0 && x->r1 < r1)) lo = m + 1; else hi = m;
+  }
+  return lo;
+}
+static int t_find(const ttable* t, uint32_t r0, uint32_t r1) {
+  int i = t_lower(t, r0, r1);
+  return (i < t->n && t->it[i].r0 == r0 && t->it[i].r1 == r1) ? i : -1;
+}
+static int t_insert(ttable* t, titem v) {
+  if (t->n == t->cap) { t->cap = t->cap ? 2 * t->cap : 64; t->it = (titem*)realloc(t->it, sizeof(titem) * t->cap); }
+  int i = t_lower(t, v.r0, v.r1);
+  memmove(&t->it[i + 1], &t->it[i], sizeof(titem) * (size_t)(t->n - i));
+  t->it[i] = v; t->n++;
+  return i;
+}
+static void t_erase(ttable* t, int i) {
+  free(t->it[i].row);
+  memmove(&t->it[i], &t->it[i + 1], sizeof(titem) * (size_t)(t->n - i - 1));
+  t->n--;
+}
+
+typedef struct { int* base; int n; } rset; /* base-region index set of a (merged) region */
+
+int go_greedy(go_state* s, const rf_oracle* rf, go_pred_fn fn, void* ctx, uint32_t* order,
+              double* sal, double* rows, uint32_t* cand_keys, double* cand_rows,
+              double* cand_scores, size_t max_cand, size_t* n_cand_out, const uint8_t* init_swap) {
+  int dim = go_row_dim(s, 0), R = s->R;
+  if (R == 0) { if (n_cand_out) *n_cand_out = 0; return 0; }
+  uint32_t maxKey = s->label[R - 1];
+  /* region id -> set; ids: base labels then maxKey+1+i */
+  int nsets = 2 * R;
+  rset* sets = (rset*)calloc((size_t)nsets, sizeof(rset));
+  for (int r = 0; r < R; ++r) { sets[r].base = (int*)malloc(4); sets[r].base[0] = r; sets[r].n = 1; }
+#define SET_OF(key) ((key) <= maxKey ? &sets[find_u32(s->label, R, (key))] : &sets[R + ((key) - maxKey - 1)])
+  ttable tb = {0, 0, 0};
+  uint64_t seq = 0; size_t ncand = 0;
+  double* row = (double*)malloc(8 * (size_t)dim);
+  regfeat fa, fb, fz;
+#define FEATURIZE(k0, k1, k2key)                                                        \
+  do {                                                                                  \
+    rset* A_ = SET_OF(k0); rset* B_ = SET_OF(k1);                                       \
+    int* Z_ = (int*)malloc(4 * (size_t)(A_->n + B_->n));                                \
+    memcpy(Z_, A_->base, 4 * (size_t)A_->n); memcpy(Z_ + A_->n, B_->base, 4 * (size_t)B_->n); \
+    region_feats(s, A_->base, A_->n, &fa, NULL);                                        \
+    region_feats(s, B_->base, B_->n, &fb, NULL);                                        \
+    region_feats(s, Z_, A_->n + B_->n, &fz, NULL);                                      \
+    candidate_row(s, A_->base, A_->n, B_->base, B_->n, &fa, &fb, &fz, row);             \
+    free(Z_);                                                                           \
+    if (ncand < max_cand) {                                                             \
+      if (cand_keys) { cand_keys[3 * ncand] = (k0); cand_keys[3 * ncand + 1] = (k1); cand_keys[3 * ncand + 2] = (k2key); } \
+      if (cand_rows) memcpy(cand_rows + ncand * dim, row, 8 * (size_t)dim);             \
+    }                                                                                   \
+  } while (0)
+#define SCORE() (rf ? rf_oracle_predict1(rf, row, dim, -1) : fn(row, dim, ctx))
+  /* init: featurise in rmap iteration order (unspecified) — we use key order; scores in key order */
+  for (int e = 0; e < s->E; ++e) {
+    int a = s->ea[e], b = s->eb[e];
+    if (!(a < b && s->rev[e] >= 0)) continue;
+    titem v; v.r0 = s->label[a]; v.r1 = s->label[b]; v.alive = 1;
+    if (init_swap && init_swap[ncand]) FEATURIZE(v.r1, v.r0, 0u);
+    else FEATURIZE(v.r0, v.r1, 0u);
+    v.row = (double*)malloc(8 * (size_t)dim); memcpy(v.row, row, 8 * (size_t)dim);
+    v.sal = SCORE(); v.seq = seq++;
+    if (ncand < max_cand && cand_scores) cand_scores[ncand] = v.sal;
+    ++ncand;
+    t_insert(&tb, v);
+  }
+  int M = 0;
+  uint32_t keyToAssign = maxKey + 1;
+  while (tb.n > 0) {
+    int top = 0;
+    for (int i = 1; i < tb.n; ++i)
+      if (tb.it[i].sal > tb.it[top].sal || (tb.it[i].sal == tb.it[top].sal && tb.it[i].seq > tb.it[top].seq)) top = i;
+    uint32_t r0 = tb.it[top].r0, r1 = tb.it[top].r1, r2 = keyToAssign++;
+    order[3 * M] = r0; order[3 * M + 1] = r1; order[3 * M + 2] = r2;
+    sal[M] = tb.it[top].sal;
+    if (rows) memcpy(rows + (size_t)M * dim, tb.it[top].row, 8 * (size_t)dim);
+    ++M;
+    { /* rmap.merge(r0, r1, r2): region_map.hxx:113-118 */
+      rset* A = SET_OF(r0); rset* B = SET_OF(r1); rset* Z = &sets[R + (r2 - maxKey - 1)];
+      Z->n = A->n + B->n; Z->base = (int*)malloc(4 * (size_t)Z->n);
+      memcpy(Z->base, A->base, 4 * (size_t)A->n); memcpy(Z->base + A->n, B->base, 4 * (size_t)B->n);
+    }
+    t_erase(&tb, top);
+    /* update: scan keys ascending while first <= r1 (boundary_table.hxx:127-166) */
+    int i = 0;
+    while (i < tb.n && tb.it[i].r0 <= r1) {
+      uint32_t k0 = tb.it[i].r0, k1 = tb.it[i].r1, rs;
+      if (k0 == r0 || k0 == r1) rs = k1;
+      else if (k1 == r0 || k1 == r1) rs = k0;
+      else { ++i; continue; }
+      titem v; v.r0 = rs; v.r1 = r2; v.alive = 1;
+      FEATURIZE(rs, r2, 0u);
+      v.row = (double*)malloc(8 * (size_t)dim); memcpy(v.row, row, 8 * (size_t)dim);
+      v.sal = SCORE(); v.seq = seq++;
+      if (ncand < max_cand && cand_scores) cand_scores[ncand] = v.sal;
+      ++ncand;
+      t_insert(&tb, v); /* (rs, r2) sorts after every key with first == rs and second < r2 */
+      /* erase (rs,r0) and (rs,r1) whichever exist; continue from the element after the current */
+      uint32_t ck0 = k0, ck1 = k1;
+      int j;
+      j = t_find(&tb, rs < r0 ? rs : r0, rs < r0 ? r0 : rs); if (j >= 0) t_erase(&tb, j);
+      j = t_find(&tb, rs < r1 ? rs : r1, rs < r1 ? r1 : rs); if (j >= 0) t_erase(&tb, j);
+      i = t_lower(&tb, ck0, ck1); /* first key >= the erased current key */
+    }
+  }
+  for (int r = 0; r < nsets; ++r) free(sets[r].base);
+  free(sets); free(row); free(tb.it);
+  if (n_cand_out) *n_cand_out = ncand;
+  return M;
+#undef SET_OF
+#undef FEATURIZE
+#undef SCORE
+}
+
+/* ------------------------------------------------------------------------
+ * bc_feat stage for a given order (hmt/main_bc_feat.cxx:27-112;
+ * bc_feat.hxx:12-26 genSaliencyMap).  Region keys in `order` are labels.
+ * ---------------------------------------------------------------------- */
+int go_bc_feat(go_state* s, const uint32_t* order, int n, const double* sal_in, double init_sal,
+               double sal_bias, double* rows) {
+  int R = s->R, with_sal = sal_in != NULL;
+  int dim = go_row_dim(s, with_sal);
+  /* key -> set; merged keys are arbitrary labels given by the file: map via sorted table */
+  uint32_t* mkeys = (uint32_t*)malloc(4 * (size_t)(n ? n : 1));
+  rset* msets = (rset*)calloc((size_t)(n ? n : 1), sizeof(rset));
+  double* msal = (double*)malloc(8 * (size_t)(n ? n : 1));
+  int status = 0;
+  for (int i = 0; i < n && !status; ++i) {
+    rset in[2]; double insal[2];
+    for (int j = 0; j < 2; ++j) {
+      uint32_t key = order[3 * i + j];
+      int found = 0;
+      for (int m = i - 1; m >= 0 && !found; --m)
+        if (mkeys[m] == key) { in[j] = msets[m]; insal[j] = msal[m]; found = 1; }
+      if (!found) {
+        int b = find_u32(s->label, R, key);
+        if (b < 0) { status = -1; break; }
+        static int single[2]; single[j] = b;
+        in[j].base = &single[j]; in[j].n = 1; insal[j] = init_sal;
+      }
+    }
+    if (status) break;
+    mkeys[i] = order[3 * i + 2];
+    msets[i].n = in[0].n + in[1].n;
+    msets[i].base = (int*)malloc(4 * (size_t)msets[i].n);
+    memcpy(msets[i].base, in[0].base, 4 * (size_t)in[0].n);
+    memcpy(msets[i].base + in[0].n, in[1].base, 4 * (size_t)in[1].n);
+    msal[i] = with_sal ? sal_in[i] + sal_bias : 0.0;
+    regfeat fa, fb, fz;
+    region_feats(s, in[0].base, in[0].n, &fa, with_sal ? &insal[0] : NULL);
+    region_feats(s, in[1].base, in[1].n, &fb, with_sal ? &insal[1] : NULL);
+    region_feats(s, msets[i].base, msets[i].n, &fz, with_sal ? &msal[i] : NULL);
+    candidate_row(s, in[0].base, in[0].n, in[1].base, in[1].n, &fa, &fb, &fz, rows + (size_t)i * dim);
+  }
+  for (int i = 0; i < n; ++i) free(msets[i].base);
+  free(mkeys); free(msets); free(msal);
+  return status;
+}

@@ -291,8 +291,8 @@ int glia_ref_run(
     std::vector<double> rows;
     for (auto const& it : bt.table()) {
       size_t i = callIdx[it.first];
-      keys.push_back(it.first.first);
-      keys.push_back(it.first.second);
+      keys.push_back(G.cand_keys[3 * i]);      // as passed to fBcFeat: the direction
+      keys.push_back(G.cand_keys[3 * i + 1]);  // met first in unordered_map iteration
       keys.push_back(0);
       rows.insert(rows.end(), G.cand_rows.begin() + i * G.dim,
                   G.cand_rows.begin() + (i + 1) * G.dim);
