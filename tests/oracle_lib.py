@@ -39,6 +39,13 @@ def build_oracle():
     subprocess.run(["make", "-s", "-C", ORACLE_DIR, "oracle"], check=True)
 
 
+def build_ref():
+    """Compile the unmodified reference headers into oracle/_ref (only where /root/reference exists)."""
+    if not os.path.isdir("/root/reference/code"):
+        raise RuntimeError("reference tree absent")
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR, "ref"], check=True)
+
+
 _lib = None
 
 
