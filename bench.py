@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""bench.py — labels + boundary probabilities -> scored initial merge candidates.
+
+A "step" is one pass of the hot path (voxel pass -> graph -> featurise -> RF score) over one
+synthetic EM-like slice/volume per rank.  See DESIGN.md §6 for what each JSON key means.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c4|c1] [--impl reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (shape in numpy order, cell, description)
+    "c1": ((512, 512), 11, "2D 512x512, ~2.2k superpixels (BASELINE.json configs[0])"),
+    "c2": ((4096, 4096), 13, "2D 4096x4096 synthetic EM slice, ~100k superpixels (BASELINE.json configs[1])"),
+    "c3": ((2048, 2048), 13, "2D 2048x2048 slices, ~25k superpixels each (BASELINE.json configs[2])"),
+    "c4": ((1024, 1024, 1024), 10, "3D 1024^3 synthetic EM volume, ~1.09M supervoxels (BASELINE.json configs[3])"),
+}
+THR = (0.2, 0.5, 0.8)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_forest(api, synth, torch, dim, ndim, device):
+    """255-tree forest over `dim` features (random structure, thresholds drawn from real feature
+    rows of a small synthetic image so that traversals are data-dependent)."""
+    shape = (192, 192) if ndim == 2 else (40, 48, 48)
+    lab, pb = synth.voronoi_volume(shape, 9 if ndim == 2 else 8, seed=99)
+    spec = [(pb, 16, 0.0, 1.0)]
+    g = api.MergeTreeBuilder(shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR), device=device).build(lab, pb)
+    _, rows = g.init_candidates()
+    g.close()
+    assert rows.shape[1] == dim
+    f = synth.random_forest(255, dim, max_depth=20, seed=0, thr_pool=rows, leaf_prob=0.3)
+    return f, api.Forest.from_arrays(f, dim, device=device)
+
+
+# ------------------------------------------------------------------ reference arm (CPU)
+def _ref_worker(job):
+    """One bounded sample through the UNMODIFIED reference (oracle/_ref, compiled from
+    /root/reference/code) with the oracle's classForest restatement as the predictor: TRegionMap
+    build + TBoundaryTable::init (fBcFeat + fBcPred for every initial candidate)."""
+    shape, cell, seed, forest = job
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    from glia_b200 import synth
+    lab, pb = synth.voronoi_volume(shape, cell, seed=seed)
+    spec = [(pb, 16, 0.0, 1.0)]
+    cfg = ol.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR)
+    use_ref = ol.ref_available(len(shape))
+    t0 = time.perf_counter()
+    if use_ref:
+        orf = ol.OracleRF.from_arrays(forest, int(forest["bestvar"].max()))
+        r = ol.ref_run(1, lab, pb, cfg, pred_c=ol.rf_pred_callback(orf), threads=1)
+        ncand = len(r["cand_keys"])
+    else:  # the oracle port (only where oracle/_ref is absent)
+        orf = ol.OracleRF.from_arrays(forest, int(forest["bestvar"].max()))
+        o = ol.Oracle(lab, pb, cfg)
+        _, rows = o.init_candidates()
+        orf.predict(rows)
+        ncand = len(rows)
+    return time.perf_counter() - t0, int(np.prod(shape)), ncand, "reference" if use_ref else "port"
+
+
+def cpu_reference(wl, forest, steps, warmup, procs=None):
+    """Times the reference on the host cores: `procs` independent processes (the reference's own
+    data-parallel mechanism is one process per image, gadget/python/script_util.py:6-23), each
+    step = one bounded sample per process."""
+    import multiprocessing as mp
+    shape, cell, _ = WORKLOADS[wl]
+    nd = len(shape)
+    sample = (1024, 1024) if nd == 2 else (96, 96, 96)
+    procs = procs or os.cpu_count() or 1
+    ctx = mp.get_context("spawn")
+    times, vox, cand, kind = [], 0, 0, "reference"
+    with ctx.Pool(procs) as pool:
+        for s in range(warmup + steps):
+            jobs = [(sample, cell, 5000 + 100 * s + i, forest) for i in range(procs)]
+            res = pool.map(_ref_worker, jobs)
+            dt = max(r[0] for r in res)  # the processes run side by side; input synthesis is not timed
+            if s >= warmup:
+                times.append(dt)
+                vox += sum(r[1] for r in res); cand += sum(r[2] for r in res)
+            kind = res[0][3]
+    total = sum(times)
+    return dict(mvox_s=vox / total / 1e6, cand_s=cand / total, ms_per_step=1e3 * total / max(len(times), 1),
+                cores=procs, kind=kind,
+                sample="%d processes x one %s synthetic sample (cell %d) per step: TRegionMap + TBoundaryTable::init "
+                       "(fBcFeat+RF) per sample" % (procs, "x".join(map(str, sample)), cell))
+
+
+def forest_arrays_cpu(synth, dim, ndim):
+    """Same forest recipe as make_forest, thresholds from oracle rows (reference arm: no GPU code)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    shape = (192, 192) if ndim == 2 else (40, 48, 48)
+    lab, pb = synth.voronoi_volume(shape, 9 if ndim == 2 else 8, seed=99)
+    spec = [(pb, 16, 0.0, 1.0)]
+    o = ol.Oracle(lab, pb, ol.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR))
+    _, rows = o.init_candidates()
+    assert rows.shape[1] == dim
+    return synth.random_forest(255, dim, max_depth=20, seed=0, thr_pool=rows, leaf_prob=0.3)
+
+
+def row_dim(ndim):
+    return (11 + 4 * 3 + 7 + 5) + 3 * (ndim + 4 + 2 * 3 + 5 + 5)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("GLIA_BENCH_WORKLOAD", "c2"), choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    shape, cell, desc = WORKLOADS[args.workload]
+    nd = len(shape)
+    nvox = int(np.prod(shape))
+    dim = row_dim(nd)
+    from glia_b200 import synth
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        forest = forest_arrays_cpu(synth, dim, nd)
+        steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+        r = cpu_reference(args.workload, forest, steps, warmup)
+        line = {"impl": "reference", "metric": "Mvoxels/s, labels+pb -> scored initial merge candidates",
+                "value": r["mvox_s"], "unit": "Mvoxels/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
+                "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u32 labels / f32 pb / f64 features", "data": "synthetic",
+                "config": {"workload": args.workload + ": " + desc, "sample": r["sample"]},
+                "candidates_per_s": r["cand_s"],
+                "cpu_baseline": {"value": r["mvox_s"], "unit": "Mvoxels/s", "cores": r["cores"], "kind": r["kind"],
+                                 "sample": r["sample"]},
+                "e2e": {"value": r["mvox_s"], "unit": "Mvoxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from glia_b200 import api
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = api.lib()
+    import ctypes as C
+    L.glia_b200_synth_voronoi.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+    stream = torch.cuda.current_stream().cuda_stream
+
+    # ---- synthetic inputs resident in HBM: NSETS distinct slices/volumes per rank, rotated so that
+    # consecutive steps never see L2-resident inputs (2D) / one volume >> L2 (3D)
+    nsets = 4 if nd == 2 else 1
+    dims = (C.c_int * 3)(*(list(shape[::-1]) + [1] * (3 - nd)))
+    sets, ncells = [], C.c_uint64(0)
+    for i in range(nsets):
+        lab = torch.empty(nvox, dtype=torch.int32, device=dev)
+        pb = torch.empty(nvox, dtype=torch.float32, device=dev)
+        st = L.glia_b200_synth_voronoi(nd, dims, cell, 1234 + 1000 * rank + i, lab.data_ptr(), pb.data_ptr(),
+                                       C.c_void_p(stream), C.byref(ncells))
+        assert st == 0
+        sets.append((lab, pb))
+    torch.cuda.synchronize()
+    label_bound = int(ncells.value) + 1
+
+    forest_arrays, forest = make_forest(api, synth, torch, dim, nd, local_rank)
+
+    def new_builder(pb_ptr, device_pointers):
+        spec = [(pb_ptr, 16, 0.0, 1.0)]
+        return api.MergeTreeBuilder(shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR), device=local_rank,
+                                    device_pointers=device_pointers, label_bound=label_bound,
+                                    stream=stream if device_pointers else None)
+
+    # one handle per input set (the image pointers are part of the handle's configuration)
+    builders = [new_builder(pb.data_ptr(), True) for (_, pb) in sets]
+    sal_dev = torch.empty(64, dtype=torch.float64, device=dev)
+
+    def step(i):
+        nonlocal sal_dev
+        b = builders[i % nsets]
+        lab, pb = sets[i % nsets]
+        b.build(lab.data_ptr(), pb.data_ptr())
+        if sal_dev.numel() < b.Cn:
+            sal_dev = torch.empty(int(b.Cn * 1.2) + 64, dtype=torch.float64, device=dev)
+        b.score_candidates(forest, sal_dev.data_ptr())
+        return b
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    sampler = ClockSampler(local_rank)
+    launches0 = sum(b.launch_count() for b in builders)
+    kern_ms = np.zeros(5)
+    cands = 0
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        b = step(args.warmup + i)
+        kern_ms += np.array(b.last_ms())
+        cands += b.Cn
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    elapsed_ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+        c = torch.tensor([cands], device=dev, dtype=torch.float64)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        cands_all = float(c.item())
+    else:
+        cands_all = float(cands)
+    launches = sum(b.launch_count() for b in builders) - launches0
+    kern_ms /= args.steps
+    R, E, Cn = b.R, b.E, b.Cn
+    value = world * nvox * args.steps / (elapsed_ms * 1e-3) / 1e6
+
+    # ---- e2e: host (pinned) buffers through the C ABI, H2D + D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        hl = torch.empty(nvox, dtype=torch.int32).pin_memory()
+        hp = torch.empty(nvox, dtype=torch.float32).pin_memory()
+        hl.copy_(sets[0][0]); hp.copy_(sets[0][1])
+        hln, hpn = hl.numpy().view(np.uint32).reshape(shape), hp.numpy().reshape(shape)
+        hb = new_builder(hpn, False)
+        hsal = torch.empty(int(Cn * 1.5) + 64, dtype=torch.float64).pin_memory().numpy()
+        for b2 in builders[1:]:
+            b2.close()
+        n_e2e = max(2, min(args.steps, 5))
+        for i in range(2):
+            hb.build(hln, hpn); hb.score_candidates(forest, hsal)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(n_e2e):
+            hb.build(hln, hpn)
+            hb.score_candidates(forest, hsal)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * nvox * n_e2e / dt / 1e6, "unit": "Mvoxels/s", "h2d_bytes_per_step": 8 * nvox,
+               "d2h_bytes_per_step": 8 * int(hb.Cn), "steps": n_e2e, "ms_per_step": 1e3 * dt / n_e2e}
+        hb.close()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    peak, peak_src = load_peaks()
+    alg_bytes = 8.0 * nvox  # label u32 + pb f32 read once
+    achieved = alg_bytes / (kern_ms[0] * 1e-3) / 1e9
+    line = {"metric": "Mvoxels/s, labels+pb -> scored initial merge candidates", "value": value, "unit": "Mvoxels/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32 labels / f32 pb / f64 features", "data": "synthetic",
+            "config": {"workload": args.workload + ": " + desc, "per_gpu": "one %s per step" % "x".join(map(str, shape)),
+                       "regions": int(R), "directed_boundaries": int(E), "candidates": int(Cn), "row_dim": dim,
+                       "forest": "255 trees, %d nodes" % int(forest_arrays["ndbigtree"].sum()),
+                       "l2": ("rotating %d distinct inputs (%d MB) + tables re-zeroed each step" % (nsets, nsets * 8 * nvox >> 20))
+                       if nd == 2 else "input 8.6 GB >> 126 MB L2", "sharding": "independent inputs per rank, no collective"},
+            "candidates_per_s": cands_all / (elapsed_ms * 1e-3),
+            "stage_ms": {"table_init": kern_ms[4], "voxel_pass": kern_ms[0], "graph": kern_ms[1], "featurize": kern_ms[2],
+                         "rf_score": kern_ms[3]},
+            "roofline": {"bound": "hbm", "kernel": "voxel_pass_generic", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_bytes},
+            "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
+    if not args.no_cpu_baseline and world == 1:
+        r = cpu_reference(args.workload, forest_arrays, 1, 0)
+        line["cpu_baseline"] = {"value": r["mvox_s"], "unit": "Mvoxels/s", "cores": r["cores"], "kind": r["kind"],
+                                "sample": r["sample"], "candidates_per_s": r["cand_s"]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

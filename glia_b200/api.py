@@ -1,0 +1,333 @@
+"""ctypes binding of libglia_b200.so (include/glia_b200.h) — the reference-side stub a maintainer
+would write.  No torch types cross the C ABI; numpy arrays are host buffers,
+integer addresses are device buffers.  There is no CPU fallback: a missing library or GPU raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libglia_b200.so")
+MAX_IMG, MAX_THR = 4, 8
+ERRORS = {1: "bad argument", 2: "CUDA error", 3: "edge table capacity", 4: "bad state",
+          5: "model file I/O", 6: "bad merge order"}
+
+
+class GliaError(RuntimeError):
+    def __init__(self, code, msg=""):
+        super().__init__("glia_b200 error %d (%s): %s" % (code, ERRORS.get(code, "?"), msg))
+        self.code = code
+
+
+class ImageSpec(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("bins", C.c_int), ("lo", C.c_double), ("hi", C.c_double)]
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("ndim", C.c_int), ("dims", C.c_int * 3),
+        ("n_rimg", C.c_int), ("n_rlimg", C.c_int), ("n_bimg", C.c_int), ("n_thr", C.c_int),
+        ("rimg", ImageSpec * MAX_IMG), ("rlimg", ImageSpec * MAX_IMG), ("bimg", ImageSpec * MAX_IMG),
+        ("thr", C.c_double * MAX_THR),
+        ("normalize", C.c_int), ("use_log", C.c_int), ("simple", C.c_int),
+        ("device_pointers", C.c_int), ("device", C.c_int),
+        ("label_bound", C.c_uint32), ("edge_capacity", C.c_uint64),
+        ("z_begin", C.c_int), ("z_end", C.c_int), ("halo_lo", C.c_int), ("halo_hi", C.c_int),
+        ("stream", C.c_void_p),
+    ]
+
+
+def build_library(verbose=False):
+    """Compile libglia_b200.so for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    r = subprocess.run(["make", "-s", "-j8", "-C", os.path.join(HERE, "csrc")],
+                       capture_output=not verbose, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building libglia_b200.so failed:\n" + (r.stdout or "") + (r.stderr or ""))
+
+
+_lib = None
+EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "glia_b200_build",
+           "glia_b200_counts", "glia_b200_row_dim", "glia_b200_get_regions",
+           "glia_b200_get_region_stats", "glia_b200_get_edges", "glia_b200_get_edge_stats",
+           "glia_b200_init_candidates", "glia_b200_score_candidates", "glia_b200_merge_order_bc",
+           "glia_b200_bc_feat", "glia_b200_rf_load", "glia_b200_rf_from_arrays",
+           "glia_b200_rf_destroy", "glia_b200_rf_info", "glia_b200_rf_score", "glia_b200_last_ms",
+           "glia_b200_launch_count"]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libglia_b200.so is not built (run __graft_entry__.build()); "
+                               "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.glia_b200_create.argtypes = [C.POINTER(Params), C.POINTER(vp)]
+        L.glia_b200_destroy.argtypes = [vp]
+        L.glia_b200_destroy.restype = None
+        L.glia_b200_last_error.argtypes = [vp]
+        L.glia_b200_last_error.restype = C.c_char_p
+        L.glia_b200_build.argtypes = [vp, vp, vp, vp]
+        L.glia_b200_counts.argtypes = [vp] + [C.POINTER(C.c_int64)] * 3
+        L.glia_b200_row_dim.argtypes = [vp, C.c_int]
+        L.glia_b200_get_regions.argtypes = [vp] * 6
+        L.glia_b200_get_region_stats.argtypes = [vp, C.c_int, C.c_int] + [vp] * 5
+        L.glia_b200_get_edges.argtypes = [vp] * 6
+        L.glia_b200_get_edge_stats.argtypes = [vp, C.c_int] + [vp] * 5
+        L.glia_b200_init_candidates.argtypes = [vp, vp, vp]
+        L.glia_b200_score_candidates.argtypes = [vp, vp, vp]
+        L.glia_b200_merge_order_bc.argtypes = [vp, vp, vp, vp, vp, C.POINTER(C.c_int64),
+                                               C.POINTER(C.c_int64)]
+        L.glia_b200_bc_feat.argtypes = [vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp]
+        L.glia_b200_rf_load.argtypes = [C.c_char_p, C.c_int, C.POINTER(vp)]
+        L.glia_b200_rf_from_arrays.argtypes = [C.c_int] * 4 + [vp] * 7 + [C.c_int, C.POINTER(vp)]
+        L.glia_b200_rf_destroy.argtypes = [vp]
+        L.glia_b200_rf_destroy.restype = None
+        L.glia_b200_rf_info.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
+        L.glia_b200_rf_score.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int, vp, vp, C.c_int, vp]
+        L.glia_b200_last_ms.argtypes = [vp, C.c_int]
+        L.glia_b200_last_ms.restype = C.c_double
+        L.glia_b200_launch_count.argtypes = [vp]
+        L.glia_b200_launch_count.restype = C.c_int64
+        _lib = L
+    return _lib
+
+
+def _addr(a):
+    """numpy array -> host address; int -> device address; None -> NULL."""
+    if a is None:
+        return None
+    if isinstance(a, (int, np.integer)):
+        return C.c_void_p(int(a))
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class FeatureConfig:
+    """Mirrors the options of hmt/main_merge_order_bc.cxx:172-242 (--rbi/--ri/--rli/--bi, --bt,
+    --ns, --logs, --simpf).  Each image entry: (array-or-device-address, bins, lo, hi)."""
+
+    def __init__(self, rimgs=(), rlimgs=(), bimgs=(), thr=(0.2, 0.5, 0.8), normalize=False,
+                 use_log=False, simple=False):
+        self.rimgs, self.rlimgs, self.bimgs = list(rimgs), list(rlimgs), list(bimgs)
+        self.thr = list(thr)
+        self.normalize, self.use_log, self.simple = normalize, use_log, simple
+
+
+def default_config(pb, **kw):
+    """--rbi pb --rbb 16 --rbl 0 --rbu 1 --bt 0.2 0.5 0.8"""
+    return FeatureConfig(rimgs=[(pb, 16, 0.0, 1.0)], bimgs=[(pb, 16, 0.0, 1.0)], **kw)
+
+
+class Forest:
+    """alg::RandomForest (alg/rf.hxx:9-60) on the device."""
+
+    def __init__(self, handle):
+        self.h = handle
+        v = [C.c_int() for _ in range(4)]
+        lib().glia_b200_rf_info(self.h, *[C.byref(x) for x in v])
+        self.ntree, self.nrnodes, self.nclass, self.mdim = (x.value for x in v)
+
+    @classmethod
+    def load(cls, path, device=0):
+        h = C.c_void_p()
+        st = lib().glia_b200_rf_load(path.encode(), device, C.byref(h))
+        if st:
+            raise GliaError(st, path)
+        return cls(h)
+
+    @classmethod
+    def from_arrays(cls, f, mdim=0, device=0):
+        nt, nr = f["nodestatus"].shape
+        a = {k: np.ascontiguousarray(f[k], np.float64 if k == "xbestsplit" else np.int32) for k in
+             ("treemap", "nodestatus", "xbestsplit", "bestvar", "nodeclass", "ndbigtree", "orig_labels")}
+        h = C.c_void_p()
+        st = lib().glia_b200_rf_from_arrays(nt, nr, len(a["orig_labels"]), mdim, _addr(a["treemap"]),
+                                            _addr(a["nodestatus"]), _addr(a["xbestsplit"]),
+                                            _addr(a["bestvar"]), _addr(a["nodeclass"]),
+                                            _addr(a["ndbigtree"]), _addr(a["orig_labels"]), device,
+                                            C.byref(h))
+        if st:
+            raise GliaError(st)
+        return cls(h)
+
+    def predict(self, X, label=-1, want_votes=True):
+        """Host rows [N][D] -> (votes [N][nclass] or None, prob [N])."""
+        X = np.ascontiguousarray(X, np.float64)
+        n, d = X.shape
+        votes = np.zeros((n, self.nclass), np.int32) if want_votes else None
+        prob = np.zeros(n)
+        st = lib().glia_b200_rf_score(self.h, _addr(X), n, d, label, _addr(votes), _addr(prob), 0, None)
+        if st:
+            raise GliaError(st)
+        return votes, prob
+
+    def predict_device(self, x_ptr, n, d, prob_ptr, votes_ptr=None, label=-1, stream=None):
+        st = lib().glia_b200_rf_score(self.h, _addr(int(x_ptr)), n, d, label,
+                                      _addr(votes_ptr), _addr(int(prob_ptr)), 1,
+                                      C.c_void_p(stream) if stream else None)
+        if st:
+            raise GliaError(st)
+
+    def close(self):
+        if self.h:
+            lib().glia_b200_rf_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class MergeTreeBuilder:
+    """One handle = TRegionMap + TBoundaryTable of the reference for one volume on one GPU.
+
+    shape is in numpy order ([z,] y, x).  With device_pointers=True every bulk argument is a
+    device address (int) instead of a numpy array.
+    """
+
+    def __init__(self, shape, cfg, device=0, device_pointers=False, label_bound=0,
+                 edge_capacity=0, slab=None, stream=None):
+        self.shape = tuple(int(s) for s in shape)
+        self.cfg = cfg
+        self.device_pointers = device_pointers
+        p = Params()
+        p.ndim = len(self.shape)
+        dims = list(self.shape[::-1]) + [1] * (3 - len(self.shape))
+        for i in range(3):
+            p.dims[i] = dims[i]
+        self._keep = []
+
+        def fill(dst, lst):
+            for i, (img, bins, lo, hi) in enumerate(lst):
+                if not device_pointers:
+                    img = np.ascontiguousarray(img, np.float32)
+                    self._keep.append(img)
+                    dst[i].data = img.ctypes.data
+                else:
+                    dst[i].data = int(img)
+                dst[i].bins, dst[i].lo, dst[i].hi = bins, lo, hi
+
+        p.n_rimg, p.n_rlimg, p.n_bimg, p.n_thr = len(cfg.rimgs), len(cfg.rlimgs), len(cfg.bimgs), len(cfg.thr)
+        fill(p.rimg, cfg.rimgs)
+        fill(p.rlimg, cfg.rlimgs)
+        fill(p.bimg, cfg.bimgs)
+        for i, t in enumerate(cfg.thr):
+            p.thr[i] = t
+        p.normalize, p.use_log, p.simple = int(cfg.normalize), int(cfg.use_log), int(cfg.simple)
+        p.device_pointers, p.device = int(device_pointers), device
+        p.label_bound, p.edge_capacity = label_bound, edge_capacity
+        if slab is not None:
+            p.z_begin, p.z_end, p.halo_lo, p.halo_hi = slab
+        p.stream = stream
+        self.params = p
+        self.h = C.c_void_p()
+        st = lib().glia_b200_create(C.byref(p), C.byref(self.h))
+        if st:
+            self.h = None
+            raise GliaError(st, "create")
+        self.R = self.E = self.Cn = 0
+
+    def _check(self, st):
+        if st:
+            raise GliaError(st, lib().glia_b200_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().glia_b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def build(self, labels, pb, mask=None):
+        if not self.device_pointers:
+            labels = np.ascontiguousarray(labels, np.uint32)
+            pb = np.ascontiguousarray(pb, np.float32)
+            mask = None if mask is None else np.ascontiguousarray(mask, np.uint32)
+            self._keep += [labels, pb, mask]
+        self._check(lib().glia_b200_build(self.h, _addr(labels), _addr(mask), _addr(pb)))
+        v = [C.c_int64() for _ in range(3)]
+        self._check(lib().glia_b200_counts(self.h, *[C.byref(x) for x in v]))
+        self.R, self.E, self.Cn = (x.value for x in v)
+        return self
+
+    def row_dim(self, with_sal=False):
+        return lib().glia_b200_row_dim(self.h, int(with_sal))
+
+    def last_ms(self):
+        return [lib().glia_b200_last_ms(self.h, i) for i in range(5)]
+
+    def launch_count(self):
+        return lib().glia_b200_launch_count(self.h)
+
+    # ---- dumps (host) ----
+    def regions(self):
+        R = self.R
+        lab, cnt, bor = (np.zeros(R, np.uint32) for _ in range(3))
+        mn, mx = np.zeros((R, 3), np.int32), np.zeros((R, 3), np.int32)
+        self._check(lib().glia_b200_get_regions(self.h, _addr(lab), _addr(cnt), _addr(bor), _addr(mn), _addr(mx)))
+        return dict(label=lab, count=cnt, border=bor, bbmin=mn, bbmax=mx)
+
+    def _stats(self, fn, n, bins, *pre):
+        hist = np.zeros((n, bins), np.uint32)
+        s, s2 = np.zeros(n), np.zeros(n)
+        mn, mx = np.zeros(n, np.float32), np.zeros(n, np.float32)
+        self._check(fn(self.h, *pre, _addr(hist), _addr(s), _addr(s2), _addr(mn), _addr(mx)))
+        return dict(hist=hist, sum=s, sum2=s2, min=mn, max=mx)
+
+    def region_stats(self, i, kind=0):
+        bins = (self.cfg.rimgs if kind == 0 else self.cfg.rlimgs)[i][1]
+        return self._stats(lib().glia_b200_get_region_stats, self.R, bins, kind, i)
+
+    def edges(self):
+        E, T = self.E, len(self.cfg.thr)
+        a, b, c = (np.zeros(E, np.uint32) for _ in range(3))
+        m = np.zeros(E, np.uint8)
+        t = np.zeros((E, T), np.uint32)
+        self._check(lib().glia_b200_get_edges(self.h, _addr(a), _addr(b), _addr(c), _addr(m), _addr(t)))
+        return dict(a=a, b=b, count=c, mutual=m, thr=t)
+
+    def edge_stats(self, i):
+        return self._stats(lib().glia_b200_get_edge_stats, self.E, self.cfg.bimgs[i][1], i)
+
+    # ---- candidates ----
+    def init_candidates(self, rows=True):
+        keys = np.zeros((self.Cn, 2), np.uint32)
+        out = np.zeros((self.Cn, self.row_dim()), np.float64) if rows else None
+        self._check(lib().glia_b200_init_candidates(self.h, _addr(keys), _addr(out)))
+        return keys, out
+
+    def score_candidates(self, forest, sal=None):
+        """sal: numpy [C] (host mode) or device address; returns sal."""
+        if sal is None:
+            sal = np.zeros(self.Cn)
+        self._check(lib().glia_b200_score_candidates(self.h, forest.h, _addr(sal)))
+        return sal
+
+    def merge_order_bc(self, forest, want_rows=False):
+        M = max(self.R - 1, 0)
+        order = np.zeros((M, 3), np.uint32)
+        sal = np.zeros(M)
+        rows = np.zeros((M, self.row_dim())) if want_rows else None
+        nm, nf = C.c_int64(), C.c_int64()
+        self._check(lib().glia_b200_merge_order_bc(self.h, forest.h, _addr(order), _addr(sal),
+                                                   _addr(rows), C.byref(nm), C.byref(nf)))
+        m = nm.value
+        return dict(order=order[:m], sal=sal[:m], rows=None if rows is None else rows[:m],
+                    n_featurized=nf.value)
+
+    def bc_feat(self, order, sal=None, init_sal=1.0, sal_bias=0.0):
+        order = np.ascontiguousarray(order, np.uint32)
+        n = len(order)
+        s = None if sal is None else np.ascontiguousarray(sal, np.float64)
+        rows = np.zeros((n, self.row_dim(sal is not None)))
+        self._check(lib().glia_b200_bc_feat(self.h, _addr(order), n, _addr(s), init_sal, sal_bias, _addr(rows)))
+        return rows

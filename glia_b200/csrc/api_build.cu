@@ -1,0 +1,291 @@
+// C ABI, part 2: glia_b200_build and the candidate entry points.
+#include <string.h>
+#include <algorithm>
+#include <vector>
+#include "handle.cuh"
+
+namespace glia {
+cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
+cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
+}  // namespace glia
+int glia_finalize_graph(glia_handle* h);
+int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
+int glia_rf_label_index(const glia_rf* m, int label);
+int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, int labelIdx,
+                         int* dVotes, double* dProb, cudaStream_t st);
+
+using namespace glia;
+#define CK(expr) GLIA_CUDA_CHECK(h, expr)
+static uint64_t pow2ceil(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
+
+extern "C" int glia_b200_build(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
+                               const float* pb) {
+  if (!h || !labels || !pb) return GLIA_E_ARG;
+  const glia_params& prm = h->prm;
+  for (int i = 0; i < prm.n_rimg; ++i) if (!prm.rimg[i].data) { h->err = "rimg data null"; return GLIA_E_ARG; }
+  for (int i = 0; i < prm.n_rlimg; ++i) if (!prm.rlimg[i].data) { h->err = "rlimg data null"; return GLIA_E_ARG; }
+  for (int i = 0; i < prm.n_bimg; ++i) if (!prm.bimg[i].data) { h->err = "bimg data null"; return GLIA_E_ARG; }
+  CK(cudaSetDevice(prm.device));
+  cudaStream_t st = h->stream;
+  h->built = false;
+  VoxParams& P = h->vp;
+  const size_t n = h->nvoxBuf;
+  // ---- inputs on the device (host buffers are staged; identical host pointers once)
+  std::vector<std::pair<const void*, const void*>> staged;
+  int nextImg = 0;
+  auto dev_of = [&](const void* src, size_t bytes, DevBuf& buf, const void** out) -> int {
+    if (prm.device_pointers) { *out = src; return GLIA_OK; }
+    for (auto& s : staged) if (s.first == src) { *out = s.second; return GLIA_OK; }
+    CK(buf.ensure(bytes));
+    CK(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, st));
+    staged.push_back({src, buf.p});
+    *out = buf.p;
+    return GLIA_OK;
+  };
+  const void* d = nullptr;
+  int s;
+  if ((s = dev_of(labels, 4 * n, h->inLabels, &d))) return s; P.labels = (const uint32_t*)d;
+  P.mask = nullptr;
+  if (mask) { if ((s = dev_of(mask, 4 * n, h->inMask, &d))) return s; P.mask = (const uint32_t*)d; }
+  if ((s = dev_of(pb, 4 * n, h->inPb, &d))) return s; P.pb = (const float*)d;
+  int ch = 0;
+  for (int i = 0; i < prm.n_rimg; ++i, ++ch) { if ((s = dev_of(prm.rimg[i].data, 4 * n, h->inImg[nextImg++], &d))) return s; h->vc.reg[ch].data = (const float*)d; }
+  for (int i = 0; i < prm.n_rlimg; ++i, ++ch) { if ((s = dev_of(prm.rlimg[i].data, 4 * n, h->inImg[nextImg++], &d))) return s; h->vc.reg[ch].data = (const float*)d; }
+  for (int i = 0; i < prm.n_bimg; ++i) { if ((s = dev_of(prm.bimg[i].data, 4 * n, h->inImg[nextImg++], &d))) return s; h->vc.edge[i].data = (const float*)d; }
+
+  CK(cudaEventRecord(h->ev[0], st));
+  CK(h->scalars.ensure(64));
+  // ---- label bound
+  uint32_t LB = prm.label_bound;
+  if (LB == 0) {
+    CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));
+    CK(launch_label_max(P.labels, n, h->scalars.as<uint32_t>(), st));
+    h->launches++;
+    uint32_t mxl = 0;
+    CK(cudaMemcpyAsync(&mxl, h->scalars.p, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (mxl == 0xFFFFFFFFu) { h->err = "label 0xFFFFFFFF is reserved"; return GLIA_E_ARG; }
+    LB = mxl + 1;
+  }
+  P.labelBound = LB;
+  // ---- raw tables (zero == identity for every word kind)
+  size_t owned = (size_t)P.X * P.Y * (size_t)(P.zEnd - P.zBegin);
+  uint64_t cap = prm.edge_capacity;
+  if (cap == 0) {
+    uint64_t est = std::min<uint64_t>(owned, 16ull * LB);
+    cap = pow2ceil(est + est / 2 + 1024);
+  } else cap = pow2ceil(cap);
+  const uint64_t capMax = pow2ceil(2 * (uint64_t)owned + 1024);
+  if (cap > capMax) cap = capMax;
+  for (;;) {  // grows the directed-boundary table and re-runs the pass if it overflowed
+  P.edgeCap = cap;
+  CK(h->regAdd.ensure(4 * (size_t)LB * P.reg.nAdd));
+  CK(h->regMax.ensure(4 * (size_t)LB * P.reg.nMax));
+  CK(h->regF64.ensure(8 * (size_t)LB * std::max(1, P.reg.nF64)));
+  CK(h->edgeKeys.ensure(8 * (size_t)cap));
+  CK(h->edgeAdd.ensure(4 * (size_t)cap * P.edge.nAdd));
+  CK(h->edgeMax.ensure(4 * (size_t)cap * std::max(1, P.edge.nMax)));
+  CK(h->edgeF64.ensure(8 * (size_t)cap * std::max(1, P.edge.nF64)));
+  CK(cudaMemsetAsync(h->regAdd.p, 0, 4 * (size_t)LB * P.reg.nAdd, st));
+  CK(cudaMemsetAsync(h->regMax.p, 0, 4 * (size_t)LB * P.reg.nMax, st));
+  CK(cudaMemsetAsync(h->regF64.p, 0, 8 * (size_t)LB * P.reg.nF64, st));
+  CK(cudaMemsetAsync(h->edgeKeys.p, 0xFF, 8 * (size_t)cap, st));
+  CK(cudaMemsetAsync(h->edgeAdd.p, 0, 4 * (size_t)cap * P.edge.nAdd, st));
+  CK(cudaMemsetAsync(h->edgeMax.p, 0, 4 * (size_t)cap * P.edge.nMax, st));
+  CK(cudaMemsetAsync(h->edgeF64.p, 0, 8 * (size_t)cap * P.edge.nF64, st));
+  CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));
+  h->launches += 8;
+  P.regAdd = h->regAdd.as<uint32_t>(); P.regMax = h->regMax.as<uint32_t>(); P.regF64 = h->regF64.as<double>();
+  P.edgeKeys = (unsigned long long*)h->edgeKeys.p;
+  P.edgeAdd = h->edgeAdd.as<uint32_t>(); P.edgeMax = h->edgeMax.as<uint32_t>(); P.edgeF64 = h->edgeF64.as<double>();
+  P.overflow = (int*)h->scalars.p + 12;
+  // ---- voxel pass
+  CK(cudaEventRecord(h->ev[6], st));
+  CK(launch_voxel_pass_generic(P, h->vc, st));
+  h->launches++;
+  CK(cudaEventRecord(h->ev[1], st));
+  int ovf = 0;
+  CK(cudaMemcpyAsync(&ovf, P.overflow, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (ovf == 2) { h->err = "label value >= label_bound"; return GLIA_E_ARG; }
+  if (ovf == 1) {
+    if (prm.edge_capacity != 0 || cap >= capMax) { h->err = "directed-boundary table full: raise edge_capacity"; return GLIA_E_CAPACITY; }
+    cap *= 4;
+    if (cap > capMax) cap = capMax;
+    continue;
+  }
+  break;
+  }
+  // ---- graph
+  if (prm.z_end > 0 && (P.zBegin > 0 || P.zEnd < P.Z)) {
+    // partial slab: the caller reduces the raw tables across ranks, then calls
+    // glia_b200_finalize (multi-GPU path)
+    h->err = "slab built; reduce raw tables then finalize";
+  }
+  s = glia_finalize_graph(h);
+  if (s != GLIA_OK) return s;
+  CK(cudaEventRecord(h->ev[2], st));
+  CK(cudaStreamSynchronize(st));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev[6], h->ev[1]); h->ms[0] = ms;
+  cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]); h->ms[1] = ms;
+  cudaEventElapsedTime(&ms, h->ev[0], h->ev[6]); h->ms[4] = ms;
+  h->built = true;
+  h->err.clear();
+  return GLIA_OK;
+}
+
+// ---- dumps ---------------------------------------------------------------------------------
+template <class T>
+static int d2h(glia_handle* h, std::vector<T>& v, const void* src, size_t count) {
+  v.resize(count);
+  if (!count) return GLIA_OK;
+  CK(cudaMemcpyAsync(v.data(), src, sizeof(T) * count, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_get_regions(glia_handle* h, uint32_t* label, uint32_t* count,
+                                     uint32_t* border, int32_t* bbmin, int32_t* bbmax) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  const RecLayout L = h->vp.reg;
+  std::vector<uint32_t> lab, add, mx;
+  int s;
+  if ((s = d2h(h, lab, h->regLabel.p, (size_t)h->R))) return s;
+  if ((s = d2h(h, add, h->cAdd.p, (size_t)h->R * L.nAdd))) return s;
+  if ((s = d2h(h, mx, h->cMax.p, (size_t)h->R * L.nMax))) return s;
+  for (long long r = 0; r < h->R; ++r) {
+    if (label) label[r] = lab[r];
+    if (count) count[r] = add[r * L.nAdd];
+    if (border) border[r] = add[r * L.nAdd + 1];
+    for (int d = 0; d < 3; ++d) {
+      int ax = h->fc.axis[d];
+      bool used = d < h->prm.ndim;
+      uint32_t wmin = mx[r * L.nMax + ax], wmax = mx[r * L.nMax + 3 + ax];
+      if (bbmin) bbmin[3 * r + d] = (used && wmin) ? (int32_t)(~wmin) : INT32_MAX;
+      if (bbmax) bbmax[3 * r + d] = (used && wmax) ? (int32_t)(wmax - 1) : INT32_MIN;
+    }
+  }
+  return GLIA_OK;
+}
+
+static int dump_stats(glia_handle* h, long long n, const RecLayout& L, int bins, int addOff,
+                      int maxOff, int f64Off, const void* dAdd, const void* dMax, const void* dF64,
+                      uint32_t* hist, double* sum, double* sum2, float* mn, float* mx) {
+  std::vector<uint32_t> add, m;
+  std::vector<double> f;
+  int s;
+  if ((s = d2h(h, add, dAdd, (size_t)n * L.nAdd))) return s;
+  if ((s = d2h(h, m, dMax, (size_t)n * L.nMax))) return s;
+  if ((s = d2h(h, f, dF64, (size_t)n * L.nF64))) return s;
+  for (long long i = 0; i < n; ++i) {
+    if (hist) for (int b = 0; b < bins; ++b) hist[i * bins + b] = add[i * L.nAdd + addOff + b];
+    if (sum) sum[i] = f[i * L.nF64 + f64Off];
+    if (sum2) sum2[i] = f[i * L.nF64 + f64Off + 1];
+    uint32_t wmin = m[i * L.nMax + maxOff], wmax = m[i * L.nMax + maxOff + 1];
+    if (mn) mn[i] = wmin ? ord2f(~wmin) : 0.0f;
+    if (mx) mx[i] = wmax ? ord2f(wmax) : 0.0f;
+  }
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_get_region_stats(glia_handle* h, int kind, int i, uint32_t* hist,
+                                          double* sum, double* sum2, float* mn, float* mx) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  int nk = kind == 0 ? h->prm.n_rimg : h->prm.n_rlimg;
+  if (kind < 0 || kind > 1 || i < 0 || i >= nk) return GLIA_E_ARG;
+  const Channel& c = h->vc.reg[kind == 0 ? i : h->prm.n_rimg + i];
+  return dump_stats(h, h->R, h->vp.reg, c.bins, c.addOff, c.maxOff, c.f64Off, h->cAdd.p, h->cMax.p,
+                    h->cF64.p, hist, sum, sum2, mn, mx);
+}
+
+extern "C" int glia_b200_get_edges(glia_handle* h, uint32_t* a, uint32_t* b, uint32_t* count,
+                                   uint8_t* mutual, uint32_t* thr_count) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  const RecLayout L = h->vp.edge;
+  const int T = h->prm.n_thr;
+  std::vector<uint32_t> lab, add;
+  std::vector<int> ea, eb, rev;
+  int s;
+  if ((s = d2h(h, lab, h->regLabel.p, (size_t)h->R))) return s;
+  if ((s = d2h(h, ea, h->ea.p, (size_t)h->E))) return s;
+  if ((s = d2h(h, eb, h->eb.p, (size_t)h->E))) return s;
+  if ((s = d2h(h, rev, h->rev.p, (size_t)h->E))) return s;
+  if ((s = d2h(h, add, h->sAdd.p, (size_t)h->E * L.nAdd))) return s;
+  for (long long e = 0; e < h->E; ++e) {
+    if (a) a[e] = lab[ea[e]];
+    if (b) b[e] = lab[eb[e]];
+    if (count) count[e] = add[e * L.nAdd];
+    if (mutual) mutual[e] = rev[e] >= 0;
+    if (thr_count) for (int t = 0; t < T; ++t) thr_count[e * T + t] = add[e * L.nAdd + 1 + t];
+  }
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_get_edge_stats(glia_handle* h, int i, uint32_t* hist, double* sum,
+                                        double* sum2, float* mn, float* mx) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  if (i < 0 || i >= h->prm.n_bimg) return GLIA_E_ARG;
+  const Channel& c = h->vc.edge[i];
+  return dump_stats(h, h->E, h->vp.edge, c.bins, c.addOff, c.maxOff, c.f64Off, h->sAdd.p, h->sMax.p,
+                    h->sF64.p, hist, sum, sum2, mn, mx);
+}
+
+// ---- candidates ------------------------------------------------------------------------------
+extern "C" int glia_b200_init_candidates(glia_handle* h, uint32_t* keys, double* rows) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  const size_t C = (size_t)h->C, dim = (size_t)h->fc.dim;
+  if (!C) return GLIA_OK;
+  uint32_t* dKeys = nullptr; double* dRows = nullptr;
+  if (h->prm.device_pointers) { dKeys = keys; dRows = rows; }
+  else {
+    if (keys) { CK(h->keysOut.ensure(8 * C)); dKeys = h->keysOut.as<uint32_t>(); }
+    if (rows) { CK(h->rows.ensure(8 * C * dim)); dRows = h->rows.as<double>(); }
+  }
+  CK(cudaEventRecord(h->ev[3], h->stream));
+  int s = glia_featurize_init_device(h, dKeys, dRows);
+  if (s) return s;
+  CK(cudaEventRecord(h->ev[4], h->stream));
+  if (!h->prm.device_pointers) {
+    if (keys) CK(cudaMemcpyAsync(keys, dKeys, 8 * C, cudaMemcpyDeviceToHost, h->stream));
+    if (rows) CK(cudaMemcpyAsync(rows, dRows, 8 * C * dim, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CK(cudaStreamSynchronize(h->stream));
+  float ms = 0; cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]); h->ms[2] = ms;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_score_candidates(glia_handle* h, const glia_rf* rf, double* sal) {
+  if (!h || !rf || !sal) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  if (rf->device != h->prm.device) { h->err = "forest lives on another device"; return GLIA_E_ARG; }
+  if (rf->mdim > h->fc.dim) { h->err = "forest uses more features than the row has"; return GLIA_E_ARG; }
+  int li = glia_rf_label_index(rf, -1);  // BC_LABEL_MERGE, hmt/bc_label.hxx:11
+  if (li < 0) { h->err = "forest has no class -1"; return GLIA_E_ARG; }
+  CK(cudaSetDevice(h->prm.device));
+  const size_t C = (size_t)h->C, dim = (size_t)h->fc.dim;
+  if (!C) return GLIA_OK;
+  CK(h->rows.ensure(8 * C * dim));
+  double* dSal = sal;
+  if (!h->prm.device_pointers) { CK(h->sal.ensure(8 * C)); dSal = h->sal.as<double>(); }
+  CK(cudaEventRecord(h->ev[3], h->stream));
+  int s = glia_featurize_init_device(h, nullptr, h->rows.as<double>());
+  if (s) return s;
+  CK(cudaEventRecord(h->ev[4], h->stream));
+  s = glia_rf_score_device(rf, h->rows.as<double>(), C, (int)dim, li, nullptr, dSal, h->stream);
+  h->launches++;
+  if (s) { h->err = "rf kernel launch failed"; return s; }
+  CK(cudaEventRecord(h->ev[5], h->stream));
+  if (!h->prm.device_pointers) CK(cudaMemcpyAsync(sal, dSal, 8 * C, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]); h->ms[2] = ms;
+  cudaEventElapsedTime(&ms, h->ev[4], h->ev[5]); h->ms[3] = ms;
+  return GLIA_OK;
+}

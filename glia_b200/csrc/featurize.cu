@@ -1,0 +1,80 @@
+// K6 driver: featurise the initial merge candidates (mutual base pairs) on the device.
+//
+// Replaces TBoundaryTable::init's initFb calls (type/boundary_table.hxx:91-114,
+// util/struct_merge_bc.hxx:18-23) and fBcFeat (hmt/main_merge_order_bc.cxx:54-95): where the
+// reference builds a temporary merged region and re-walks every pixel of r0, r1 and r0 u r1,
+// a candidate row here is a pure function of the records of a, b, their boundary aggregates
+// and the two directed boundaries a->b, b->a.
+#include "featurize.cuh"
+
+namespace glia {
+
+struct GraphView {
+  long long R, E, C;
+  const int* cand; const int* ea; const int* eb; const int* rev; const int* row;
+  const uint32_t* regLabel;
+  const uint32_t* cAdd; const uint32_t* cMax; const double* cF64;        // regions
+  const uint32_t* sAdd; const uint32_t* sMax; const double* sF64;        // directed boundaries
+  const uint32_t* aAdd; const uint32_t* aMax; const double* aF64;        // per-region boundary aggregate
+};
+
+__global__ void __launch_bounds__(128)
+init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G,
+                       uint32_t* __restrict__ keys, double* __restrict__ rows) {
+  long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (c >= G.C) return;
+  const int e = G.cand[c], rv = G.rev[e];
+  const int a = G.ea[e], b = G.eb[e];
+  if (keys) { keys[2 * c] = G.regLabel[a]; keys[2 * c + 1] = G.regLabel[b]; }
+  if (!rows) return;
+  const RecLayout LR = F.reg, LE = F.edge;
+  RecSingle rx{G.cAdd + (size_t)a * LR.nAdd, G.cMax + (size_t)a * LR.nMax, G.cF64 + (size_t)a * LR.nF64};
+  RecSingle ry{G.cAdd + (size_t)b * LR.nAdd, G.cMax + (size_t)b * LR.nMax, G.cF64 + (size_t)b * LR.nF64};
+  RecSum2 rz{rx, ry};
+  RecSingle bx{G.aAdd + (size_t)a * LE.nAdd, G.aMax + (size_t)a * LE.nMax, G.aF64 + (size_t)a * LE.nF64};
+  RecSingle by{G.aAdd + (size_t)b * LE.nAdd, G.aMax + (size_t)b * LE.nMax, G.aF64 + (size_t)b * LE.nF64};
+  RecSingle pe{G.sAdd + (size_t)e * LE.nAdd, G.sMax + (size_t)e * LE.nMax, G.sF64 + (size_t)e * LE.nF64};
+  RecSingle pr{G.sAdd + (size_t)rv * LE.nAdd, G.sMax + (size_t)rv * LE.nMax, G.sF64 + (size_t)rv * LE.nF64};
+  RecSum2 pb{pe, pr};  // pair boundary b(X,Y) = (a->b) u (b->a)   (util/struct.hxx:10-16)
+  RecBoundaryZ bz;
+  bz.pa = bx.a; bz.qa = by.a; bz.ea = pe.a; bz.ra = pr.a;
+  for (int i = 0; i < LE.nMax; ++i) bz.mxw[i] = 0;
+  for (int i = 0; i < LE.nF64; ++i) bz.f[i] = 0.0;
+  // entries(Z): all directed boundaries of a then of b except the mutual pair (region.hxx:66-75)
+  for (int side = 0; side < 2; ++side) {
+    int r = side ? b : a;
+    for (int k = G.row[r]; k < G.row[r + 1]; ++k) {
+      if (k == e || k == rv) continue;
+      for (int i = 0; i < LE.nMax; ++i) bz.mxw[i] = max(bz.mxw[i], G.sMax[(size_t)k * LE.nMax + i]);
+      for (int i = 0; i < LE.nF64; ++i) bz.f[i] += G.sF64[(size_t)k * LE.nF64 + i];
+    }
+  }
+  featurize_row(F, rx, ry, rz, bx, by, bz, pb, nullptr, rows + (size_t)c * F.dim);
+}
+
+}  // namespace glia
+
+using namespace glia;
+
+GraphView glia_graph_view(const glia_handle* h) {
+  GraphView G;
+  G.R = h->R; G.E = h->E; G.C = h->C;
+  G.cand = h->cand.as<int>(); G.ea = h->ea.as<int>(); G.eb = h->eb.as<int>();
+  G.rev = h->rev.as<int>(); G.row = h->row.as<int>();
+  G.regLabel = h->regLabel.as<uint32_t>();
+  G.cAdd = h->cAdd.as<uint32_t>(); G.cMax = h->cMax.as<uint32_t>(); G.cF64 = h->cF64.as<double>();
+  G.sAdd = h->sAdd.as<uint32_t>(); G.sMax = h->sMax.as<uint32_t>(); G.sF64 = h->sF64.as<double>();
+  G.aAdd = h->bAggAdd.as<uint32_t>(); G.aMax = h->bAggMax.as<uint32_t>(); G.aF64 = h->bAggF64.as<double>();
+  return G;
+}
+
+// dKeys [C][2] or null, dRows [C][dim] or null: device buffers
+int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows) {
+  if (h->C == 0) return GLIA_OK;
+  GraphView G = glia_graph_view(h);
+  unsigned blocks = (unsigned)((h->C + 127) / 128);
+  init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, dKeys, dRows);
+  h->launches++;
+  GLIA_CUDA_CHECK(h, cudaGetLastError());
+  return GLIA_OK;
+}

@@ -1,0 +1,264 @@
+// K2: from the raw tables of the voxel pass to the finalised region adjacency graph.
+//
+// Replaces (reference, /root/reference/code):
+//   boundaryMap[(a,b)].push_back + TPointPairMap::prepare   util/struct.hxx:104, type/point_map.hxx:53-60
+//   TRegionMap::init (adjacency lists a -> [(b, pts*)])      type/region_map.hxx:79-95
+//   mutual-pair filter of TBoundaryTable::init               type/boundary_table.hxx:99-102
+// Regions become dense indices in ascending label order (prefix sum over label presence);
+// directed boundaries are compacted out of the hash table, sorted by (a,b) index pair
+// (64-bit radix sort-by-key) into a CSR edge list with reverse-edge links; mutual pairs with
+// a < b are the initial merge candidates, already in the reference's table order.
+#include <cub/cub.cuh>
+#include "handle.cuh"
+
+namespace glia {
+
+__global__ void mark_present_kernel(const uint32_t* __restrict__ regAdd, int nAdd, uint32_t n,
+                                    uint32_t* __restrict__ flags) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flags[i] = regAdd[(size_t)i * nAdd] > 0 ? 1u : 0u;
+}
+
+// one warp per label: copy the three record parts to the compact slot
+__global__ void gather_regions_kernel(const uint32_t* __restrict__ flags,
+                                      const uint32_t* __restrict__ rank, uint32_t n, RecLayout L,
+                                      const uint32_t* __restrict__ gAdd,
+                                      const uint32_t* __restrict__ gMax,
+                                      const double* __restrict__ gF64, uint32_t* __restrict__ label,
+                                      uint32_t* __restrict__ cAdd, uint32_t* __restrict__ cMax,
+                                      double* __restrict__ cF64) {
+  uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= n || !flags[w]) return;
+  uint32_t r = rank[w];
+  if (lane == 0) label[r] = w;
+  for (int i = lane; i < L.nAdd; i += 32) cAdd[(size_t)r * L.nAdd + i] = gAdd[(size_t)w * L.nAdd + i];
+  for (int i = lane; i < L.nMax; i += 32) cMax[(size_t)r * L.nMax + i] = gMax[(size_t)w * L.nMax + i];
+  for (int i = lane; i < L.nF64; i += 32) cF64[(size_t)r * L.nF64 + i] = gF64[(size_t)w * L.nF64 + i];
+}
+
+// occupied hash slots -> (index-pair key, slot); warp-aggregated append
+__global__ void compact_edges_kernel(const unsigned long long* __restrict__ keys, uint64_t cap,
+                                     const uint32_t* __restrict__ rank,
+                                     const uint32_t* __restrict__ flags, uint32_t labelBound,
+                                     unsigned long long* __restrict__ outKey,
+                                     uint32_t* __restrict__ outSlot, unsigned long long* counter,
+                                     int* errFlag) {
+  uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  unsigned long long k = (i < cap) ? keys[i] : EDGE_EMPTY;
+  bool occ = k != EDGE_EMPTY;
+  unsigned m = __ballot_sync(0xffffffffu, occ);
+  if (!m) return;
+  int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (occ) {
+    uint32_t a = (uint32_t)(k >> 32), b = (uint32_t)k;
+    if (a >= labelBound || b >= labelBound || !flags[a] || !flags[b]) { atomicExch(errFlag, 3); return; }
+    unsigned long long pos = base + __popc(m & ((1u << lane) - 1));
+    outKey[pos] = ((unsigned long long)rank[a] << 32) | rank[b];
+    outSlot[pos] = (uint32_t)i;
+  }
+}
+
+__global__ void gather_edges_kernel(const unsigned long long* __restrict__ keySorted,
+                                    const uint32_t* __restrict__ slotSorted, long long E, RecLayout L,
+                                    const uint32_t* __restrict__ gAdd,
+                                    const uint32_t* __restrict__ gMax,
+                                    const double* __restrict__ gF64, int* __restrict__ ea,
+                                    int* __restrict__ eb, uint32_t* __restrict__ sAdd,
+                                    uint32_t* __restrict__ sMax, double* __restrict__ sF64) {
+  long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  if (w >= E) return;
+  size_t s = slotSorted[w];
+  if (lane == 0) { unsigned long long k = keySorted[w]; ea[w] = (int)(k >> 32); eb[w] = (int)(uint32_t)k; }
+  for (int i = lane; i < L.nAdd; i += 32) sAdd[(size_t)w * L.nAdd + i] = gAdd[s * L.nAdd + i];
+  for (int i = lane; i < L.nMax; i += 32) sMax[(size_t)w * L.nMax + i] = gMax[s * L.nMax + i];
+  for (int i = lane; i < L.nF64; i += 32) sF64[(size_t)w * L.nF64 + i] = gF64[s * L.nF64 + i];
+}
+
+// row[r] = first edge with a >= r (r in 0..R)
+__global__ void csr_rows_kernel(const int* __restrict__ ea, long long E, long long R,
+                                int* __restrict__ row) {
+  long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (r > R) return;
+  long long lo = 0, hi = E;
+  while (lo < hi) { long long m = (lo + hi) >> 1; if (ea[m] < r) lo = m + 1; else hi = m; }
+  row[r] = (int)lo;
+}
+
+__global__ void reverse_edges_kernel(const int* __restrict__ ea, const int* __restrict__ eb,
+                                     const int* __restrict__ row, long long E,
+                                     int* __restrict__ rev) {
+  long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  int a = ea[e], b = eb[e];
+  int lo = row[b], hi = row[b + 1], r = -1;
+  while (lo < hi) { int m = (lo + hi) >> 1; int v = eb[m]; if (v == a) { r = m; break; } if (v < a) lo = m + 1; else hi = m; }
+  rev[e] = r;
+}
+
+struct IsCandidate {
+  const int* ea; const int* eb; const int* rev;
+  __device__ bool operator()(int e) const { return ea[e] < eb[e] && rev[e] >= 0; }
+};
+
+// Per-region aggregate over all of its directed boundaries (entries of a base region):
+// one warp per region, word-parallel.
+__global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long R, RecLayout L,
+                                          const uint32_t* __restrict__ sAdd,
+                                          const uint32_t* __restrict__ sMax,
+                                          const double* __restrict__ sF64,
+                                          uint32_t* __restrict__ aAdd, uint32_t* __restrict__ aMax,
+                                          double* __restrict__ aF64) {
+  long long r = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  if (r >= R) return;
+  int e0 = row[r], e1 = row[r + 1];
+  for (int i = lane; i < L.nAdd; i += 32) {
+    uint32_t s = 0;
+    for (int e = e0; e < e1; ++e) s += sAdd[(size_t)e * L.nAdd + i];
+    aAdd[(size_t)r * L.nAdd + i] = s;
+  }
+  for (int i = lane; i < L.nMax; i += 32) {
+    uint32_t s = 0;
+    for (int e = e0; e < e1; ++e) s = max(s, sMax[(size_t)e * L.nMax + i]);
+    aMax[(size_t)r * L.nMax + i] = s;
+  }
+  for (int i = lane; i < L.nF64; i += 32) {
+    double s = 0.0;
+    for (int e = e0; e < e1; ++e) s += sF64[(size_t)e * L.nF64 + i];
+    aF64[(size_t)r * L.nF64 + i] = s;
+  }
+}
+
+}  // namespace glia
+
+using namespace glia;
+
+#define CK(expr) GLIA_CUDA_CHECK(h, expr)
+static inline unsigned nblk(long long n, int per) { return (unsigned)((n + per - 1) / per); }
+
+// Builds the finalised graph from the raw tables.  Returns a GLIA_* status.
+int glia_finalize_graph(glia_handle* h) {
+  cudaStream_t st = h->stream;
+  const VoxParams& P = h->vp;
+  const uint32_t LB = P.labelBound;
+  // scalars: [0] edge counter (u64), [1] cand count (int as u64 slot), [2] err flag
+  CK(h->scalars.ensure(64));
+  CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));
+  unsigned long long* dCounter = h->scalars.as<unsigned long long>();
+  int* dNumSel = (int*)(dCounter + 1);
+  int* dErr = (int*)(dCounter + 2);
+
+  // ---- regions: presence -> rank
+  CK(h->flags.ensure(4 * (size_t)LB + 4));
+  CK(h->rank.ensure(4 * (size_t)LB + 4));
+  mark_present_kernel<<<nblk(LB, 256), 256, 0, st>>>(h->regAdd.as<uint32_t>(), P.reg.nAdd, LB,
+                                                     h->flags.as<uint32_t>());
+  h->launches++;
+  size_t tmpBytes = 0;
+  CK(cub::DeviceScan::ExclusiveSum(nullptr, tmpBytes, h->flags.as<uint32_t>(), h->rank.as<uint32_t>(), (int)LB, st));
+  CK(h->cubTmp.ensure(tmpBytes));
+  CK(cub::DeviceScan::ExclusiveSum(h->cubTmp.p, tmpBytes, h->flags.as<uint32_t>(), h->rank.as<uint32_t>(), (int)LB, st));
+  h->launches += 2;
+  uint32_t lastRank = 0, lastFlag = 0;
+  CK(cudaMemcpyAsync(&lastRank, h->rank.as<uint32_t>() + (LB - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&lastFlag, h->flags.as<uint32_t>() + (LB - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  h->R = (long long)lastRank + lastFlag;
+  const long long R = h->R;
+  CK(h->regLabel.ensure(4 * (size_t)(R + 1)));
+  CK(h->cAdd.ensure(4 * (size_t)(R + 1) * P.reg.nAdd));
+  CK(h->cMax.ensure(4 * (size_t)(R + 1) * P.reg.nMax));
+  CK(h->cF64.ensure(8 * (size_t)(R + 1) * P.reg.nF64));
+  gather_regions_kernel<<<nblk((long long)LB * 32, 256), 256, 0, st>>>(
+      h->flags.as<uint32_t>(), h->rank.as<uint32_t>(), LB, P.reg, h->regAdd.as<uint32_t>(),
+      h->regMax.as<uint32_t>(), h->regF64.as<double>(), h->regLabel.as<uint32_t>(),
+      h->cAdd.as<uint32_t>(), h->cMax.as<uint32_t>(), h->cF64.as<double>());
+  h->launches++;
+
+  // ---- directed boundaries: compact, sort by (a,b) index pair
+  // Upper bound on E is not known before compaction: count first with a null-output pass
+  // would cost a second sweep, so size the outputs by the table capacity bound instead.
+  size_t eCap = (size_t)P.edgeCap;
+  CK(h->eKey.ensure(8 * eCap));
+  CK(h->eSlot.ensure(4 * eCap));
+  compact_edges_kernel<<<nblk((long long)eCap, 256), 256, 0, st>>>(
+      (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(),
+      h->flags.as<uint32_t>(), LB, h->eKey.as<unsigned long long>(), h->eSlot.as<uint32_t>(),
+      dCounter, dErr);
+  h->launches++;
+  unsigned long long E64 = 0; int errv = 0;
+  CK(cudaMemcpyAsync(&E64, dCounter, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&errv, dErr, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (errv) { h->err = "directed boundary refers to a label with no voxels (reduce the partial tables first)"; return GLIA_E_STATE; }
+  if (E64 > 0x7fffffffull) { h->err = "more than 2^31 directed boundaries"; return GLIA_E_ARG; }
+  h->E = (long long)E64;
+  const long long E = h->E;
+  CK(h->eKeySorted.ensure(8 * (size_t)(E + 1)));
+  CK(h->eSlotSorted.ensure(4 * (size_t)(E + 1)));
+  int rbits = 1; while ((1ll << rbits) < R + 1) ++rbits;
+  int endBit = 32 + rbits > 64 ? 64 : 32 + rbits;
+  if (E > 0) {
+    tmpBytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, h->eKey.as<unsigned long long>(),
+                                       h->eKeySorted.as<unsigned long long>(), h->eSlot.as<uint32_t>(),
+                                       h->eSlotSorted.as<uint32_t>(), (int)E, 0, endBit, st));
+    CK(h->cubTmp.ensure(tmpBytes));
+    CK(cub::DeviceRadixSort::SortPairs(h->cubTmp.p, tmpBytes, h->eKey.as<unsigned long long>(),
+                                       h->eKeySorted.as<unsigned long long>(), h->eSlot.as<uint32_t>(),
+                                       h->eSlotSorted.as<uint32_t>(), (int)E, 0, endBit, st));
+    h->launches += 8;
+  }
+  CK(h->ea.ensure(4 * (size_t)(E + 1)));
+  CK(h->eb.ensure(4 * (size_t)(E + 1)));
+  CK(h->rev.ensure(4 * (size_t)(E + 1)));
+  CK(h->row.ensure(4 * (size_t)(R + 2)));
+  CK(h->sAdd.ensure(4 * (size_t)(E + 1) * P.edge.nAdd));
+  CK(h->sMax.ensure(4 * (size_t)(E + 1) * (P.edge.nMax + 1)));
+  CK(h->sF64.ensure(8 * (size_t)(E + 1) * (P.edge.nF64 + 1)));
+  if (E > 0) {
+    gather_edges_kernel<<<nblk(E * 32, 256), 256, 0, st>>>(
+        h->eKeySorted.as<unsigned long long>(), h->eSlotSorted.as<uint32_t>(), E, P.edge,
+        h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(),
+        h->ea.as<int>(), h->eb.as<int>(), h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
+        h->sF64.as<double>());
+    h->launches++;
+  }
+  csr_rows_kernel<<<nblk(R + 1, 256), 256, 0, st>>>(h->ea.as<int>(), E, R, h->row.as<int>());
+  h->launches++;
+  CK(h->cand.ensure(4 * (size_t)(E + 1)));
+  h->C = 0;
+  if (E > 0) {
+    reverse_edges_kernel<<<nblk(E, 256), 256, 0, st>>>(h->ea.as<int>(), h->eb.as<int>(),
+                                                       h->row.as<int>(), E, h->rev.as<int>());
+    h->launches++;
+    IsCandidate pred{h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>()};
+    cub::CountingInputIterator<int> it(0);
+    tmpBytes = 0;
+    CK(cub::DeviceSelect::If(nullptr, tmpBytes, it, h->cand.as<int>(), dNumSel, (int)E, pred, st));
+    CK(h->cubTmp.ensure(tmpBytes));
+    CK(cub::DeviceSelect::If(h->cubTmp.p, tmpBytes, it, h->cand.as<int>(), dNumSel, (int)E, pred, st));
+    h->launches += 2;
+    int c = 0;
+    CK(cudaMemcpyAsync(&c, dNumSel, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    h->C = c;
+  }
+  // ---- per-region aggregate over its boundaries
+  CK(h->bAggAdd.ensure(4 * (size_t)(R + 1) * P.edge.nAdd));
+  CK(h->bAggMax.ensure(4 * (size_t)(R + 1) * (P.edge.nMax + 1)));
+  CK(h->bAggF64.ensure(8 * (size_t)(R + 1) * (P.edge.nF64 + 1)));
+  if (R > 0) {
+    boundary_aggregate_kernel<<<nblk(R * 32, 256), 256, 0, st>>>(
+        h->row.as<int>(), R, P.edge, h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
+        h->sF64.as<double>(), h->bAggAdd.as<uint32_t>(), h->bAggMax.as<uint32_t>(),
+        h->bAggF64.as<double>());
+    h->launches++;
+  }
+  CK(cudaGetLastError());
+  return GLIA_OK;
+}

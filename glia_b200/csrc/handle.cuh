@@ -1,0 +1,84 @@
+// glia_b200 — the handle behind the C ABI (include/glia_b200.h).
+#pragma once
+#include <vector>
+#include "common.cuh"
+
+namespace glia {
+
+// Grow-only device buffer (reused across calls on the same handle).
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+
+// Featurisation constants (device copy of the feature configuration).
+struct FeatCfg {
+  int D;             // DIMENSION
+  int axis[3];       // kernel axis of reference dimension d (2D volumes run as X x 1 x Y)
+  int nThr, nR, nRL, nB;
+  int rBins[GLIA_MAX_IMG], rlBins[GLIA_MAX_IMG], bBins[GLIA_MAX_IMG];
+  int rAdd[GLIA_MAX_IMG], rMax[GLIA_MAX_IMG], rF64[GLIA_MAX_IMG];     // offsets in region records
+  int rlAdd[GLIA_MAX_IMG];
+  int bAdd[GLIA_MAX_IMG], bMax[GLIA_MAX_IMG], bF64[GLIA_MAX_IMG];     // offsets in edge records
+  RecLayout reg, edge;
+  double normArea, normLen;
+  int useLog, simple;
+  int dim;           // row length without saliency terms
+};
+
+}  // namespace glia
+
+struct glia_rf {
+  int device = 0;
+  int ntree = 0, nrnodes = 0, nclass = 0, mdim = 0;
+  std::vector<int> treemap, nodestatus, bestvar, nodeclass, ndbigtree, orig_labels;
+  std::vector<double> xbestsplit;
+  // device: compact breadth-first forest (rf.cu)
+  int totalNodes = 0;
+  int* d_treeOff = nullptr;      // [ntree+1]
+  void* d_nodes = nullptr;       // packed nodes
+  double* d_thr = nullptr;       // thresholds, SoA
+  int maxDepth = 0;
+};
+
+struct glia_handle {
+  glia_params prm;
+  std::string err;
+  cudaStream_t stream = nullptr;
+  bool ownStream = false;
+  cudaEvent_t ev[8];
+  double ms[5] = {-1, -1, -1, -1, -1};
+  long long launches = 0;
+  bool built = false;
+
+  // kernel-axis geometry (2D runs as X x 1 x rows)
+  int KX = 0, KY = 0, KZ = 0;
+  size_t nvoxBuf = 0;
+
+  glia::VoxParams vp;
+  glia::VoxChannels vc;
+  glia::FeatCfg fc;
+
+  // staging of host inputs
+  glia::DevBuf inLabels, inMask, inPb, inImg[3 * GLIA_MAX_IMG];
+  // raw tables of the voxel pass
+  glia::DevBuf regAdd, regMax, regF64, edgeKeys, edgeAdd, edgeMax, edgeF64, flags;
+  // finalised graph
+  long long R = 0, E = 0, C = 0;
+  glia::DevBuf rank, regLabel, cAdd, cMax, cF64;          // regions ascending by label
+  glia::DevBuf eSlot, eKey, eSlotSorted, eKeySorted;      // compaction + sort
+  glia::DevBuf sAdd, sMax, sF64, ea, eb, row, rev, cand;  // directed boundaries, CSR by a
+  glia::DevBuf bAggAdd, bAggMax, bAggF64;                 // per-region sum over its boundaries
+  glia::DevBuf cubTmp, scalars, rows, sal, keysOut;
+};

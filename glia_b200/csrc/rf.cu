@@ -1,0 +1,286 @@
+// K7: random-forest scoring of merge candidates + the rf_old model-file reader.
+//
+// Replaces (reference, /root/reference/code):
+//   alg::RandomForest::operator()              alg/rf.hxx:35-36
+//   ml::rf::Model::predict / helperPredict     ml/rf/rf.hxx:362-439
+//   extern classForest (third party)           ml/rf/rf.hxx:8-14  -> predictClassTree semantics:
+//     k = 0; while nodestatus[k] != -1: k = (x[bestvar[k]-1] <= xbestsplit[k]) ? left : right;
+//     votes[nodeclass[k]-1] += 1            (source absent from the reference tree)
+//   rf_old::readModelFromBinaryFile, readArray ml/rf/ml_rf_model.cxx:459-563, :48-70
+//
+// Device layout: every tree is compacted to its used nodes (ndbigtree[t], not the padded
+// nrnodes stride) and re-ordered breadth-first with sibling pairs adjacent, so a node is one
+// 16-byte record {threshold, left-child (right = left+1) | class, feature | -1}.  One thread
+// scores one candidate; all lanes of a warp walk the same tree at the same time, so the upper
+// levels are broadcast fetches.  Trees whose nodes fit are staged in shared memory.
+#include <stdio.h>
+#include <string.h>
+#include <queue>
+#include "handle.cuh"
+
+namespace glia {
+
+struct __align__(16) RfNode {
+  double thr;
+  int left;  // internal: absolute index of the left child; leaf: class index
+  int feat;  // internal: 0-based feature; leaf: -1
+};
+
+// votesOut: [N][nclass] or null.  Dynamic smem: blockDim.x * nclass ints when votesOut.
+template <bool WANT_VOTES>
+__global__ void __launch_bounds__(128)
+rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, int ntree,
+                int nclass, int labelIdx, const double* __restrict__ X, size_t N, int D,
+                int* __restrict__ votesOut, double* __restrict__ prob) {
+  extern __shared__ int svotes[];
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const bool active = i < N;
+  const double* x = X + (active ? i : 0) * (size_t)D;
+  if (WANT_VOTES)
+    for (int c = 0; c < nclass; ++c) svotes[c * blockDim.x + threadIdx.x] = 0;
+  int hits = 0;
+  if (active) {
+    for (int t = 0; t < ntree; ++t) {
+      int k = __ldg(treeOff + t);
+      RfNode nd = nodes[k];
+      while (nd.feat >= 0) {
+        double v = __ldg(x + nd.feat);
+        k = nd.left + (v <= nd.thr ? 0 : 1);
+        nd = nodes[k];
+      }
+      if (WANT_VOTES) svotes[nd.left * blockDim.x + threadIdx.x] += 1;
+      hits += (nd.left == labelIdx);
+    }
+    if (prob) prob[i] = (double)hits / (double)ntree;  // ml/rf/rf.hxx:366-369
+    if (WANT_VOTES)
+      for (int c = 0; c < nclass; ++c) votesOut[i * nclass + c] = svotes[c * blockDim.x + threadIdx.x];
+  }
+}
+
+}  // namespace glia
+
+using namespace glia;
+
+static int rf_build_device(glia_rf* m) {
+  // breadth-first compaction, siblings adjacent
+  std::vector<RfNode> nodes;
+  std::vector<int> treeOff(m->ntree + 1);
+  const int nr = m->nrnodes;
+  for (int t = 0; t < m->ntree; ++t) {
+    const size_t o = (size_t)t * nr;
+    const int* tm = m->treemap.data() + 2 * o;
+    treeOff[t] = (int)nodes.size();
+    std::queue<std::pair<int, int>> q;  // (original node, new index)
+    nodes.push_back(RfNode{0.0, 0, -1});
+    q.push({0, treeOff[t]});
+    int visited = 0;
+    while (!q.empty()) {
+      auto cur = q.front(); q.pop();
+      int k = cur.first;
+      if (k < 0 || k >= nr || ++visited > nr) return GLIA_E_IO;
+      if (m->nodestatus[o + k] == -1) {
+        int cls = m->nodeclass[o + k] - 1;
+        if (cls < 0 || cls >= m->nclass) return GLIA_E_IO;
+        nodes[cur.second] = RfNode{0.0, cls, -1};
+      } else {
+        int f = m->bestvar[o + k] - 1;
+        if (f < 0) return GLIA_E_IO;
+        if (f + 1 > m->mdim) m->mdim = f + 1;
+        int left = (int)nodes.size();
+        nodes.push_back(RfNode{0.0, 0, -1});
+        nodes.push_back(RfNode{0.0, 0, -1});
+        nodes[cur.second] = RfNode{m->xbestsplit[o + k], left, f};
+        q.push({tm[2 * k] - 1, left});
+        q.push({tm[2 * k + 1] - 1, left + 1});
+      }
+    }
+  }
+  treeOff[m->ntree] = (int)nodes.size();
+  m->totalNodes = (int)nodes.size();
+  if (cudaSetDevice(m->device) != cudaSuccess) return GLIA_E_CUDA;
+  if (cudaMalloc(&m->d_nodes, sizeof(RfNode) * nodes.size()) != cudaSuccess) return GLIA_E_CUDA;
+  if (cudaMalloc((void**)&m->d_treeOff, 4 * treeOff.size()) != cudaSuccess) return GLIA_E_CUDA;
+  if (cudaMemcpy(m->d_nodes, nodes.data(), sizeof(RfNode) * nodes.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+  if (cudaMemcpy(m->d_treeOff, treeOff.data(), 4 * treeOff.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_rf_from_arrays(int ntree, int nrnodes, int nclass, int mdim,
+                                        const int* treemap, const int* nodestatus,
+                                        const double* xbestsplit, const int* bestvar,
+                                        const int* nodeclass, const int* ndbigtree,
+                                        const int* orig_labels, int device, glia_rf** out) {
+  if (!out || ntree <= 0 || nrnodes <= 0 || nclass <= 0 || nclass > 64 || !treemap || !nodestatus ||
+      !xbestsplit || !bestvar || !nodeclass || !orig_labels)
+    return GLIA_E_ARG;
+  glia_rf* m = new glia_rf();
+  size_t n = (size_t)ntree * nrnodes;
+  m->device = device; m->ntree = ntree; m->nrnodes = nrnodes; m->nclass = nclass; m->mdim = mdim;
+  m->treemap.assign(treemap, treemap + 2 * n);
+  m->nodestatus.assign(nodestatus, nodestatus + n);
+  m->xbestsplit.assign(xbestsplit, xbestsplit + n);
+  m->bestvar.assign(bestvar, bestvar + n);
+  m->nodeclass.assign(nodeclass, nodeclass + n);
+  if (ndbigtree) m->ndbigtree.assign(ndbigtree, ndbigtree + ntree);
+  m->orig_labels.assign(orig_labels, orig_labels + nclass);
+  int st = rf_build_device(m);
+  if (st != GLIA_OK) { glia_b200_rf_destroy(m); return st; }
+  *out = m;
+  return GLIA_OK;
+}
+
+// ---- rf_old binary model file -------------------------------------------------------------
+// The file starts with a raw dump of rf_old::Model (ml/rf/ml_rf.h:97-157; 520 bytes on
+// x86-64/libstdc++): only the {rows, cols} pairs of each array header are meaningful on read
+// (the pointers are stale).  Offsets of those pairs, in declaration order:
+namespace {
+struct ArrDim { int rows, cols; };
+// 4 std::vector headers (96 bytes), then array headers {ptr(8), int[2]} = 16 bytes each.
+const size_t OFF_NCAT = 96, OFF_CATF = 112, OFF_XBEST = 136, OFF_CLASSWT = 152, OFF_CUTOFF = 168,
+             OFF_TREEMAP = 184, OFF_NODESTATUS = 200, OFF_NODECLASS = 216, OFF_BESTVAR = 232,
+             OFF_NDBIG = 248, OFF_ORIG = 272, OFF_NEWL = 288;
+ArrDim dim_at(const unsigned char* hdr, size_t off) { ArrDim d; memcpy(&d, hdr + off + 8, 8); return d; }
+
+template <class T>
+bool read_array(FILE* f, std::vector<T>& out, long long size) {  // ml_rf_model.cxx:48-70
+  out.assign((size_t)(size > 0 ? size : 0), T(0));
+  if (size <= 0) return true;
+  if (size > 128) {
+    unsigned char sparse;
+    if (fread(&sparse, 1, 1, f) != 1) return false;
+    if (sparse) {
+      int num;
+      if (fread(&num, 4, 1, f) != 1 || num < 0) return false;
+      for (int i = 0; i < num; ++i) {
+        int idx; T v;
+        if (fread(&idx, 4, 1, f) != 1 || fread(&v, sizeof(T), 1, f) != 1) return false;
+        if (idx < 0 || idx >= size) return false;
+        out[idx] = v;
+      }
+      return true;
+    }
+  }
+  return fread(out.data(), sizeof(T), (size_t)size, f) == (size_t)size;
+}
+// file matrix is rows x cols row-major; native layout is its transpose (ml_rf_model.cxx:542-557)
+template <class T>
+std::vector<T> transposed(const std::vector<T>& x, int rows, int cols) {
+  std::vector<T> r(x.size());
+  for (int i = 0; i < cols; ++i)
+    for (int j = 0; j < rows; ++j) r[(size_t)i * rows + j] = x[(size_t)j * cols + i];
+  return r;
+}
+}  // namespace
+
+extern "C" int glia_b200_rf_load(const char* path, int device, glia_rf** out) {
+  if (!path || !out) return GLIA_E_ARG;
+  FILE* f = fopen(path, "rb");
+  if (!f) return GLIA_E_IO;
+  unsigned char hdr[520];
+  if (fread(hdr, 520, 1, f) != 1) { fclose(f); return GLIA_E_IO; }
+  for (int i = 0; i < 4; ++i) {  // categorical-feature vectors must be empty (begin == end)
+    if (memcmp(hdr + 24 * i, hdr + 24 * i + 8, 8) != 0) { fclose(f); return GLIA_E_IO; }
+  }
+  auto nel = [&](size_t off) { ArrDim d = dim_at(hdr, off); return (long long)d.rows * d.cols; };
+  std::vector<int> ncat, catf, tm, ns, nc, bv, nb, ol, nl;
+  std::vector<double> xb, cw, co;
+  int nrnodes = 0, ntree = 0, mtry = 0, nclass = 0;
+  bool ok = true;
+  ok = ok && read_array(f, ncat, nel(OFF_NCAT));
+  ok = ok && read_array(f, catf, nel(OFF_CATF));
+  ok = ok && fread(&nrnodes, 4, 1, f) == 1 && fread(&ntree, 4, 1, f) == 1;
+  ok = ok && read_array(f, xb, nel(OFF_XBEST));
+  ok = ok && read_array(f, cw, nel(OFF_CLASSWT));
+  ok = ok && read_array(f, co, nel(OFF_CUTOFF));
+  ok = ok && read_array(f, tm, nel(OFF_TREEMAP));
+  ok = ok && read_array(f, ns, nel(OFF_NODESTATUS));
+  ok = ok && read_array(f, nc, nel(OFF_NODECLASS));
+  ok = ok && read_array(f, bv, nel(OFF_BESTVAR));
+  ok = ok && read_array(f, nb, nel(OFF_NDBIG));
+  ok = ok && fread(&mtry, 4, 1, f) == 1;
+  ok = ok && read_array(f, ol, nel(OFF_ORIG));
+  ok = ok && read_array(f, nl, nel(OFF_NEWL));
+  ok = ok && fread(&nclass, 4, 1, f) == 1;
+  fclose(f);  // the remaining arrays are out-of-bag statistics, unused for scoring
+  for (int v : catf) if (v) ok = false;
+  long long n = (long long)nrnodes * ntree;
+  if (!ok || ntree <= 0 || nrnodes <= 0 || nclass <= 0 || (long long)xb.size() != n ||
+      (long long)tm.size() != 2 * n || (long long)ns.size() != n || (long long)nc.size() != n ||
+      (long long)bv.size() != n || (long long)ol.size() < nclass)
+    return GLIA_E_IO;
+  ArrDim dx = dim_at(hdr, OFF_XBEST), dt = dim_at(hdr, OFF_TREEMAP), ds = dim_at(hdr, OFF_NODESTATUS),
+         dc = dim_at(hdr, OFF_NODECLASS), db = dim_at(hdr, OFF_BESTVAR);
+  std::vector<double> xbT = transposed(xb, dx.rows, dx.cols);
+  std::vector<int> tmT = transposed(tm, dt.rows, dt.cols), nsT = transposed(ns, ds.rows, ds.cols),
+                   ncT = transposed(nc, dc.rows, dc.cols), bvT = transposed(bv, db.rows, db.cols);
+  return glia_b200_rf_from_arrays(ntree, nrnodes, nclass, 0, tmT.data(), nsT.data(), xbT.data(),
+                                  bvT.data(), ncT.data(), nb.empty() ? nullptr : nb.data(),
+                                  ol.data(), device, out);
+}
+
+extern "C" void glia_b200_rf_destroy(glia_rf* m) {
+  if (!m) return;
+  if (m->d_nodes) cudaFree(m->d_nodes);
+  if (m->d_treeOff) cudaFree(m->d_treeOff);
+  delete m;
+}
+
+extern "C" int glia_b200_rf_info(const glia_rf* m, int* ntree, int* nrnodes, int* nclass, int* mdim) {
+  if (!m) return GLIA_E_ARG;
+  if (ntree) *ntree = m->ntree;
+  if (nrnodes) *nrnodes = m->nrnodes;
+  if (nclass) *nclass = m->nclass;
+  if (mdim) *mdim = m->mdim;
+  return GLIA_OK;
+}
+
+int glia_rf_label_index(const glia_rf* m, int label) {
+  for (int i = 0; i < m->nclass; ++i) if (m->orig_labels[i] == label) return i;
+  return -1;
+}
+
+// device-side scoring of N rows already on the device
+int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, int labelIdx,
+                         int* dVotes, double* dProb, cudaStream_t st) {
+  if (!N) return GLIA_OK;
+  unsigned blocks = (unsigned)((N + 127) / 128);
+  if (dVotes)
+    rf_score_kernel<true><<<blocks, 128, 128 * m->nclass * sizeof(int), st>>>(
+        (const RfNode*)m->d_nodes, m->d_treeOff, m->ntree, m->nclass, labelIdx, dX, N, D, dVotes, dProb);
+  else
+    rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->ntree,
+                                                   m->nclass, labelIdx, dX, N, D, nullptr, dProb);
+  return cudaGetLastError() == cudaSuccess ? GLIA_OK : GLIA_E_CUDA;
+}
+
+extern "C" int glia_b200_rf_score(const glia_rf* m, const double* X, size_t N, int D, int label,
+                                  int* votes, double* prob, int device_pointers, void* stream) {
+  if (!m || !X || D < m->mdim) return GLIA_E_ARG;
+  int li = glia_rf_label_index(m, label);
+  if (li < 0) return GLIA_E_ARG;  // ml/rf/rf.hxx:370 perr
+  if (cudaSetDevice(m->device) != cudaSuccess) return GLIA_E_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (device_pointers) {
+    int s = glia_rf_score_device(m, X, N, D, li, votes, prob, st);
+    return s;
+  }
+  // host buffers: stream the rows through the device in chunks
+  const size_t chunk = 1 << 20;
+  double* dX = nullptr; int* dV = nullptr; double* dP = nullptr;
+  size_t c = N < chunk ? (N ? N : 1) : chunk;
+  int status = GLIA_OK;
+  if (cudaMalloc(&dX, 8 * c * D) != cudaSuccess || cudaMalloc(&dP, 8 * c) != cudaSuccess ||
+      (votes && cudaMalloc(&dV, 4 * c * m->nclass) != cudaSuccess))
+    status = GLIA_E_CUDA;
+  for (size_t o = 0; o < N && status == GLIA_OK; o += c) {
+    size_t n = N - o < c ? N - o : c;
+    if (cudaMemcpyAsync(dX, X + o * D, 8 * n * D, cudaMemcpyHostToDevice, st) != cudaSuccess) { status = GLIA_E_CUDA; break; }
+    status = glia_rf_score_device(m, dX, n, D, li, votes ? dV : nullptr, dP, st);
+    if (status != GLIA_OK) break;
+    if (prob && cudaMemcpyAsync(prob + o, dP, 8 * n, cudaMemcpyDeviceToHost, st) != cudaSuccess) status = GLIA_E_CUDA;
+    if (votes && cudaMemcpyAsync(votes + o * m->nclass, dV, 4 * n * m->nclass, cudaMemcpyDeviceToHost, st) != cudaSuccess) status = GLIA_E_CUDA;
+    if (cudaStreamSynchronize(st) != cudaSuccess) status = GLIA_E_CUDA;
+  }
+  cudaFree(dX); cudaFree(dV); cudaFree(dP);
+  return status;
+}

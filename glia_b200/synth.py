@@ -101,3 +101,44 @@ def speckle_volume(shape, nlabels, seed=0, dyadic=True):
     else:
         pb = rng.random(shape, dtype=np.float32)
     return lab.astype(np.uint32), pb
+
+
+def random_forest(ntree, mdim, max_depth=12, seed=0, nclass=2, orig_labels=(-1, 1), thr_pool=None,
+                  leaf_prob=0.15):
+    """Random forest in the rf_old / classRF array layout (ml/rf/ml_rf.h:97-157): per tree a
+    padded block of nrnodes nodes; treemap 1-based child ids, nodestatus -1 = terminal,
+    bestvar 1-based feature, nodeclass 1-based class.  thr_pool: optional [n, mdim] sample matrix
+    whose values are used as thresholds (so that x <= t ties really occur)."""
+    rng = np.random.default_rng(seed)
+    trees = []
+    for _ in range(ntree):
+        tm, ns, xb, bv, nc = [[0, 0]], [0], [0.0], [0], [0]
+        stack = [(0, 0)]
+        while stack:
+            k, depth = stack.pop()
+            if depth >= max_depth or (depth > 1 and rng.random() < leaf_prob):
+                ns[k] = -1
+                nc[k] = int(rng.integers(1, nclass + 1))
+                continue
+            f = int(rng.integers(0, mdim))
+            t = float(thr_pool[rng.integers(0, len(thr_pool)), f]) if thr_pool is not None else float(rng.random())
+            ns[k], bv[k], xb[k] = 1, f + 1, t
+            for side in range(2):
+                tm.append([0, 0]); ns.append(0); xb.append(0.0); bv.append(0); nc.append(0)
+                tm[k][side] = len(ns)  # 1-based id of the new node
+                stack.append((len(ns) - 1, depth + 1))
+        trees.append((tm, ns, xb, bv, nc))
+    nr = max(len(t[1]) for t in trees)
+    f = dict(treemap=np.zeros((ntree, nr, 2), np.int32), nodestatus=np.zeros((ntree, nr), np.int32),
+             xbestsplit=np.zeros((ntree, nr)), bestvar=np.zeros((ntree, nr), np.int32),
+             nodeclass=np.zeros((ntree, nr), np.int32), ndbigtree=np.zeros(ntree, np.int32),
+             orig_labels=np.asarray(orig_labels, np.int32))
+    for i, (tm, ns, xb, bv, nc) in enumerate(trees):
+        n = len(ns)
+        f["treemap"][i, :n] = tm
+        f["nodestatus"][i, :n] = ns
+        f["xbestsplit"][i, :n] = xb
+        f["bestvar"][i, :n] = bv
+        f["nodeclass"][i, :n] = nc
+        f["ndbigtree"][i] = n
+    return f

@@ -1,0 +1,159 @@
+/* glia_b200 — C ABI of the B200-native hmt feature + merge-order path.
+ *
+ * The reference (tingliu/glia) has no FFI layer; the seams this library sits behind are
+ * (reference paths relative to /root/reference/code):
+ *   - TRegionMap(seg, mask, false)                     type/region_map.hxx:52-95
+ *     genPointMap / genContourMap / getContourTraits   util/struct.hxx:61-144, type/neighbor.hxx:72-126
+ *       -> glia_b200_build()  (RAG + per-region / per-directed-boundary statistics)
+ *   - TBoundaryTable::init + fBcFeat + fBcPred         type/boundary_table.hxx:91-114,
+ *                                                      hmt/main_merge_order_bc.cxx:54-139
+ *       -> glia_b200_init_candidates(), glia_b200_score_candidates()
+ *   - genMergeOrderGreedyUsingBoundaryClassifier       util/struct_merge_bc.hxx:8-58
+ *       -> glia_b200_merge_order_bc()
+ *   - bc_feat operation()                              hmt/main_bc_feat.cxx:27-112
+ *       -> glia_b200_bc_feat()
+ *   - alg::RandomForest::operator(), Model::predict    alg/rf.hxx:35-36, ml/rf/rf.hxx:362-405
+ *     extern classForest(...)                          ml/rf/rf.hxx:8-14
+ *     rf_old::readModelFromBinaryFile                  ml/rf/ml_rf_model.cxx:459-563
+ *       -> glia_b200_rf_load(), glia_b200_rf_from_arrays(), glia_b200_rf_score()
+ *
+ * Conventions: every function returns an int status (GLIA_OK == 0); nothing calls exit().
+ * The caller owns every buffer passed in or out.  Buffers are HOST pointers unless the
+ * handle was created with device_pointers != 0, in which case the bulk inputs (labels, mask,
+ * images, RF feature matrix) and bulk outputs documented as "host or device" are DEVICE
+ * pointers on the handle's GPU.  One handle per GPU/stream; a handle is not thread-safe.
+ * There is no CPU fallback: every entry point fails with GLIA_E_CUDA when no device is usable.
+ */
+#ifndef GLIA_B200_H
+#define GLIA_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GLIA_API __attribute__((visibility("default")))
+#else
+#define GLIA_API
+#endif
+
+#define GLIA_MAX_IMG 4
+#define GLIA_MAX_THR 8
+#define GLIA_MAX_BINS 64
+
+enum {
+  GLIA_OK = 0,
+  GLIA_E_ARG = 1,      /* bad argument / unsupported configuration */
+  GLIA_E_CUDA = 2,     /* CUDA runtime error (see glia_b200_last_error) */
+  GLIA_E_CAPACITY = 3, /* edge table too small: recreate with a larger edge_capacity */
+  GLIA_E_STATE = 4,    /* call order violated (e.g. candidates before build) */
+  GLIA_E_IO = 5,       /* model file unreadable / malformed */
+  GLIA_E_ORDER = 6     /* merge order references an unknown region */
+};
+
+/* One image + histogram spec: ImageHistPair (type/feat.hxx) = --rbi/--rbb/--rbl/--rbu etc. */
+typedef struct glia_image_spec {
+  const float* data; /* same extent as the label volume */
+  int bins;          /* 1..GLIA_MAX_BINS */
+  double lo, hi;     /* histogram range (util/image_stats.hxx:12-36 semantics) */
+} glia_image_spec;
+
+typedef struct glia_params {
+  int ndim;    /* 2 or 3: the reference's compile-time DIMENSION (glia_base.hxx:49-53) */
+  int dims[3]; /* x (fastest), y, z; dims[2] ignored when ndim == 2 */
+  int n_rimg, n_rlimg, n_bimg, n_thr;
+  glia_image_spec rimg[GLIA_MAX_IMG];  /* region images   (rImages,  hmt_util.hxx:17-56) */
+  glia_image_spec rlimg[GLIA_MAX_IMG]; /* label images    (rlImages) */
+  glia_image_spec bimg[GLIA_MAX_IMG];  /* boundary images (bImages) */
+  double thr[GLIA_MAX_THR];            /* --bt thresholds on pb (type/feat.hxx:485-502) */
+  int normalize;                       /* --ns   (main_merge_order_bc.cxx:36-39) */
+  int use_log;                         /* --logs (main_merge_order_bc.cxx:86-91) */
+  int simple;                          /* --simpf (hmt/bc_feat.hxx:247-279) */
+  int device_pointers;                 /* 0: host buffers, 1: device buffers */
+  int device;                          /* CUDA device ordinal */
+  uint32_t label_bound;  /* exclusive upper bound of label values; 0 = scan the volume */
+  uint64_t edge_capacity; /* slots of the directed-boundary table; 0 = automatic */
+  /* z-slab sharding (multi-GPU).  The buffers given to glia_b200_build hold
+   * planes [z_begin - halo_lo, z_end + halo_hi) of a volume whose full extent is dims[];
+   * only voxels of planes [z_begin, z_end) are owned (classified and accumulated), the halo
+   * planes supply neighbour labels/mask.  z_end == 0 means the whole volume (no slab). */
+  int z_begin, z_end, halo_lo, halo_hi;
+  void* stream; /* cudaStream_t to run on (NULL = a private stream) */
+} glia_params;
+
+typedef struct glia_handle glia_handle;
+typedef struct glia_rf glia_rf;
+
+GLIA_API int glia_b200_create(const glia_params* p, glia_handle** out);
+GLIA_API void glia_b200_destroy(glia_handle* h);
+GLIA_API const char* glia_b200_last_error(const glia_handle* h);
+
+/* RAG + base statistics.  labels/mask: uint32 volumes (mask may be NULL); pb: float32. */
+GLIA_API int glia_b200_build(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);
+/* R regions, E directed boundaries, C mutual pairs (= initial merge candidates) */
+GLIA_API int glia_b200_counts(const glia_handle* h, int64_t* R, int64_t* E, int64_t* C);
+GLIA_API int glia_b200_row_dim(const glia_handle* h, int with_saliency);
+
+/* Dumps (host buffers; any pointer may be NULL).  Regions ascending by label. */
+GLIA_API int glia_b200_get_regions(glia_handle* h, uint32_t* label, uint32_t* count, uint32_t* border,
+                          int32_t* bbmin /*[R][3]*/, int32_t* bbmax /*[R][3]*/);
+/* kind 0: rimg[i], kind 1: rlimg[i].  hist [R][bins]; min/max are 0 for empty sets. */
+GLIA_API int glia_b200_get_region_stats(glia_handle* h, int kind, int i, uint32_t* hist, double* sum,
+                               double* sum2, float* mn, float* mx);
+/* Directed boundaries ascending by (a, b) label. thr_count [E][n_thr]. */
+GLIA_API int glia_b200_get_edges(glia_handle* h, uint32_t* a, uint32_t* b, uint32_t* count,
+                        uint8_t* mutual, uint32_t* thr_count);
+GLIA_API int glia_b200_get_edge_stats(glia_handle* h, int i, uint32_t* hist, double* sum, double* sum2,
+                             float* mn, float* mx);
+
+/* Initial candidates in ascending (min,max) label order: keys [C][2], rows [C][dim]
+ * (host or device; either may be NULL).  Candidate (a,b), a<b, is featurised as
+ * fBcFeat(reg a, reg b): for equal areas x1 = a. */
+GLIA_API int glia_b200_init_candidates(glia_handle* h, uint32_t* keys, double* rows);
+/* Featurise + RF-score the initial candidates on the device: sal [C] (host or device). */
+GLIA_API int glia_b200_score_candidates(glia_handle* h, const glia_rf* rf, double* sal);
+
+/* Full greedy merge order (hmt/main_merge_order_bc.cxx:143-157).  order [R-1][3], sal [R-1],
+ * rows [R-1][dim] or NULL (the -b output).  *n_merges receives the number of merges. */
+GLIA_API int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint32_t* order, double* sal,
+                             double* rows, int64_t* n_merges, int64_t* n_featurized);
+/* bc_feat stage for a given order (hmt/main_bc_feat.cxx:27-112).  sal_in NULL = no saliency
+ * features; rows [n][row_dim(sal_in != NULL)]. */
+GLIA_API int glia_b200_bc_feat(glia_handle* h, const uint32_t* order /*[n][3]*/, int64_t n,
+                      const double* sal_in, double init_sal, double sal_bias, double* rows);
+
+/* ---- random forest ---- */
+GLIA_API int glia_b200_rf_load(const char* path, int device, glia_rf** out);
+/* Native layouts after readModelFromBinaryFile's transposes (ml_rf_model.cxx:542-557):
+ * treemap [ntree][nrnodes][2] (1-based child ids), others [ntree][nrnodes]. */
+GLIA_API int glia_b200_rf_from_arrays(int ntree, int nrnodes, int nclass, int mdim, const int* treemap,
+                             const int* nodestatus, const double* xbestsplit, const int* bestvar,
+                             const int* nodeclass, const int* ndbigtree, const int* orig_labels,
+                             int device, glia_rf** out);
+GLIA_API void glia_b200_rf_destroy(glia_rf* m);
+GLIA_API int glia_b200_rf_info(const glia_rf* m, int* ntree, int* nrnodes, int* nclass, int* mdim);
+/* X [N][D] row-major doubles (x[m + i*mdim], ml/rf/rf.hxx:362-365).  votes [N][nclass] int
+ * (may be NULL), prob [N] = votes[idx(label)]/ntree (ml/rf/rf.hxx:366-369).
+ * device_pointers: X, votes, prob are device buffers. stream may be NULL. */
+GLIA_API int glia_b200_rf_score(const glia_rf* m, const double* X, size_t N, int D, int label, int* votes,
+                       double* prob, int device_pointers, void* stream);
+
+/* Timing of the last glia_b200_build/score call, measured with CUDA events on the handle's
+ * stream: which = 0 voxel-pass kernel, 1 graph (compaction+sort+CSR), 2 featurise, 3 RF score,
+ * 4 table initialisation (+ label scan when label_bound == 0).
+ * Returns milliseconds, or a negative value if not available. */
+GLIA_API double glia_b200_last_ms(const glia_handle* h, int which);
+/* Number of kernels launched by this handle so far (bench.py's gpu_launches). */
+GLIA_API int64_t glia_b200_launch_count(const glia_handle* h);
+
+/* Bench/test utility (not part of the reference's path): seeded jittered-Voronoi superpixels +
+ * dyadic boundary map written straight into DEVICE buffers; same integer hashing as
+ * glia_b200/synth.py::voronoi_volume.  dims: x (fastest), y, z. */
+GLIA_API int glia_b200_synth_voronoi(int ndim, const int* dims, int cell, uint32_t seed,
+                                     uint32_t* labels, float* pb, void* stream, uint64_t* n_cells);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

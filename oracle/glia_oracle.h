@@ -90,6 +90,7 @@ void rf_oracle_arrays(const rf_oracle* m, int* treemap, int* nodestatus, double*
 /* votes [N][nclass] (int), prob [N] = votes[idx(label)]/ntree.  threads<=0 -> serial. */
 int rf_oracle_predict(const rf_oracle* m, const double* X, size_t N, int D, int label,
                       int* votes, double* prob, int threads);
+double rf_oracle_pred_cb(const double* row, int dim, void* ctx);
 double rf_oracle_predict1(const rf_oracle* m, const double* x, int D, int label);
 /* writes the rf_old binary layout (ml_rf_model.cxx:565-…) for fixtures */
 int rf_oracle_save(const rf_oracle* m, const char* path);

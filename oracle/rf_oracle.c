@@ -240,6 +240,11 @@ double rf_oracle_predict1(const rf_oracle* m, const double* x, int D, int label)
   return votes[li] / (double)m->ntree;
 }
 
+/* go_pred_fn / ref_pred_fn adapter: ctx is the rf_oracle*, label -1 = BC_LABEL_MERGE. */
+double rf_oracle_pred_cb(const double* row, int dim, void* ctx) {
+  return rf_oracle_predict1((const rf_oracle*)ctx, row, dim, -1);
+}
+
 int rf_oracle_predict(const rf_oracle* m, const double* X, size_t N, int D, int label, int* votes,
                       double* prob, int threads) {
   int li = label_index(m, label);

@@ -85,6 +85,7 @@ def lib():
         L.rf_oracle_predict1.restype = C.c_double
         L.rf_oracle_predict1.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.rf_oracle_save.argtypes = [C.c_void_p, C.c_char_p]
+        L.rf_oracle_pred_cb.restype = C.c_double
         _lib = L
     return _lib
 
@@ -302,8 +303,14 @@ def _ref_get(L, name, dtype):
     return np.ctypeslib.as_array(C.cast(p, C.POINTER(np.ctypeslib.as_ctypes_type(dtype))), (n,)).copy()
 
 
+def rf_pred_callback(orf):
+    """(function pointer, ctx) pair scoring a row with an OracleRF without going through Python."""
+    fn = C.cast(lib().rf_oracle_pred_cb, C.c_void_p)
+    return fn, C.c_void_p(orf.h)
+
+
 def ref_run(mode, labels, pb, cfg, mask=None, pred=None, order=None, sal=None, init_sal=1.0,
-            sal_bias=0.0, threads=0):
+            sal_bias=0.0, threads=0, pred_c=None):
     """Run the compiled unmodified reference (oracle/ref_driver.cxx). mode: 0 RAG, 1 init
     candidates, 2 full greedy, 3 bc_feat stage."""
     labels = np.ascontiguousarray(labels, np.uint32)
@@ -331,7 +338,8 @@ def ref_run(mode, labels, pb, cfg, mask=None, pred=None, order=None, sal=None, i
     args = [C.c_int(mode), dims, _ptr(labels), _ptr(m), _ptr(pb)] + pack(cfg.rimgs) + \
         pack(cfg.rlimgs) + pack(cfg.bimgs) + [C.c_int(len(cfg.thr)), thr, C.c_int(int(cfg.normalize)),
                                               C.c_int(int(cfg.use_log)), C.c_int(int(cfg.simple)),
-                                              cb if cb else C.c_void_p(None), C.c_void_p(None), _ptr(o),
+                                              (pred_c[0] if pred_c else (cb if cb else C.c_void_p(None))),
+                                              (pred_c[1] if pred_c else C.c_void_p(None)), _ptr(o),
                                               C.c_int(0 if o is None else len(o)), _ptr(s),
                                               C.c_double(init_sal), C.c_double(sal_bias),
                                               C.c_int(threads)]
