@@ -177,11 +177,24 @@ def test_score_candidates_matches_oracle():
     o = ol.Oracle(lab, pb, co)
     g = api.MergeTreeBuilder((96, 128), cg).build(lab, pb)
     _, rowo = o.init_candidates()
-    f = synth.random_forest(255, o.row_dim(), max_depth=10, seed=4, thr_pool=rowo)
+    _, rowg = g.init_candidates()
+    # thresholds from ANOTHER image's rows: realistic splits without forcing x == t ties
+    lab2, pb2 = synth.voronoi_volume((80, 80), 7, seed=8)
+    o2 = ol.Oracle(lab2, pb2, _cfg_pair(pb2)[0])
+    _, pool = o2.init_candidates()
+    f = synth.random_forest(255, o.row_dim(), max_depth=12, seed=4, thr_pool=pool)
     orf, grf = ol.OracleRF.from_arrays(f, o.row_dim()), api.Forest.from_arrays(f, o.row_dim())
-    _, po = orf.predict(rowo)
     sal = g.score_candidates(grf)
-    # RF decision flips caused by a threshold tie on a feature that differs in the last bits:
+    # (1) votes are bit-exact on identical input rows
+    _, p_same = orf.predict(rowg)
+    assert np.array_equal(sal, p_same)
+    # (2) against the oracle end to end, the only differences are RF decision flips where a
+    # transcendental feature (entropy / compactness, last-bit differences) sits on a threshold:
+    # enumerate them
+    _, po = orf.predict(rowo)
     flips = np.flatnonzero(sal != po)
-    assert len(flips) <= 0.01 * len(po), "flips: %s" % flips[:20]
-    assert np.abs(sal - po).max() <= 2.0 / 255
+    assert len(flips) <= 0.02 * len(po), "flips: %s" % flips[:20]
+    for c in flips:
+        cols = np.flatnonzero(rowg[c] != rowo[c])
+        assert len(cols) > 0
+        np.testing.assert_allclose(rowg[c], rowo[c], rtol=RTOL, atol=1e-12)
