@@ -1,0 +1,372 @@
+// K8: greedy merge order with the boundary classifier (the merge-order stage).
+//
+// Replaces (reference, /root/reference/code):
+//   genMergeOrderGreedyUsingBoundaryClassifier     util/struct_merge_bc.hxx:8-58
+//   genMergeOrderGreedy                            util/struct_merge.hxx:10-33
+//   TBoundaryTable::{init,top,update}              type/boundary_table.hxx:47-52, :91-167
+//   TRegionMap::merge / TRegion::merge             type/region_map.hxx:113-118, type/region.hxx:66-75
+//   fBcFeat / fBcPred                              hmt/main_merge_order_bc.cxx:54-139
+// The loop is a strict sequential chain (each pop depends on the scores of the previous
+// merge's new candidates), so the host keeps the TOPOLOGY (which regions touch, the ordered
+// table and the priority queue, exactly as the reference does) and combines the mergeable
+// records of the merged regions; the device featurises and RF-scores every batch of new
+// candidates (one launch per merge).  No pixel is ever re-walked: where the reference's
+// fBcFeat costs O(|r0| + |r1| + |r0 u r1|) voxels per candidate, a candidate here costs
+// O(deg) record combinations.
+#include <algorithm>
+#include <map>
+#include <set>
+#include <unordered_map>
+#include <vector>
+#include "featurize.cuh"
+
+int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
+int glia_rf_label_index(const glia_rf* m, int label);
+int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, int labelIdx,
+                         int* dVotes, double* dProb, cudaStream_t st);
+
+namespace glia {
+
+struct __align__(16) RfNode16 { double thr; int left; int feat; };  // == RfNode (rf.cu)
+
+// One warp per candidate.  Lane 0 builds the feature row from the six staged records (region
+// X, Y; boundary-of X, Y, Z; pair boundary), then the 32 lanes split the trees of the forest.
+__global__ void __launch_bounds__(128)
+merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __restrict__ stage,
+                   int stageWords, const RfNode16* __restrict__ nodes,
+                   const int* __restrict__ treeOff, int ntree, int labelIdx,
+                   double* __restrict__ rows, double* __restrict__ sal) {
+  int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= m) return;
+  const RecLayout LR = F.reg, LE = F.edge;
+  const int regW = LR.nAdd + LR.nMax + ((LR.nAdd + LR.nMax) & 1) + 2 * LR.nF64;
+  const int edgeW = LE.nAdd + LE.nMax + ((LE.nAdd + LE.nMax) & 1) + 2 * LE.nF64;
+  const uint32_t* base = stage + (size_t)w * stageWords;
+  double* row = rows + (size_t)w * F.dim;
+  if (lane == 0) {
+    auto regRec = [&](int k) {
+      const uint32_t* p = base + (size_t)k * regW;
+      return RecSingle{p, p + LR.nAdd, (const double*)(p + LR.nAdd + LR.nMax + ((LR.nAdd + LR.nMax) & 1))};
+    };
+    auto edgeRec = [&](int k) {
+      const uint32_t* p = base + 2 * (size_t)regW + (size_t)k * edgeW;
+      return RecSingle{p, p + LE.nAdd, (const double*)(p + LE.nAdd + LE.nMax + ((LE.nAdd + LE.nMax) & 1))};
+    };
+    RecSingle rx = regRec(0), ry = regRec(1);
+    RecSum2 rz{rx, ry};
+    featurize_row(F, rx, ry, rz, edgeRec(0), edgeRec(1), edgeRec(2), edgeRec(3), nullptr, row);
+  }
+  __syncwarp();
+  int hits = 0;
+  for (int t = lane; t < ntree; t += 32) {
+    int k = treeOff[t];
+    RfNode16 nd = nodes[k];
+    while (nd.feat >= 0) {
+      k = nd.left + (row[nd.feat] <= nd.thr ? 0 : 1);
+      nd = nodes[k];
+    }
+    hits += (nd.left == labelIdx);
+  }
+  for (int o = 16; o; o >>= 1) hits += __shfl_xor_sync(0xffffffffu, hits, o);
+  if (lane == 0) sal[w] = (double)hits / (double)ntree;
+}
+
+}  // namespace glia
+
+using namespace glia;
+#define CK(expr) GLIA_CUDA_CHECK(h, expr)
+
+namespace {
+
+// host-side mergeable record (common.cuh word kinds)
+struct Rec {
+  std::vector<uint32_t> add, mx;
+  std::vector<double> f;
+  void init(const RecLayout& L) { add.assign(L.nAdd, 0); mx.assign(L.nMax, 0); f.assign(L.nF64, 0.0); }
+  void merge(const Rec& o) {
+    for (size_t i = 0; i < add.size(); ++i) add[i] += o.add[i];
+    for (size_t i = 0; i < mx.size(); ++i) mx[i] = std::max(mx[i], o.mx[i]);
+    for (size_t i = 0; i < f.size(); ++i) f[i] += o.f[i];
+  }
+};
+
+struct Item { double sal; unsigned long long seq; std::vector<double> row; };
+typedef std::pair<int, int> Key;
+
+struct Greedy {
+  glia_handle* h;
+  RecLayout LR, LE;
+  int R, E;
+  std::vector<int> ea, eb, rev, row;
+  std::vector<uint32_t> sAdd, sMax; std::vector<double> sF64;   // base directed boundaries
+  std::vector<Rec> reg;                                          // region record per id
+  std::vector<Rec> btot;                                         // boundary-of totals (add, f64 only)
+  std::vector<std::vector<int>> nmOut;                           // non-mutual boundaries by source region
+  std::vector<std::map<int, Rec>> dm;                            // dm[x][w] = mutual boundaries x -> w
+  std::vector<int> ufParent, idOfRoot, repBase;  // union-find over base regions
+
+  void ufUnion(int r0, int r1, int r2) {
+    int a = find(repBase[r0]), b = find(repBase[r1]);
+    ufParent[b] = a; idOfRoot[a] = r2; repBase[r2] = a;
+  }
+
+  int find(int b) { while (ufParent[b] != b) { ufParent[b] = ufParent[ufParent[b]]; b = ufParent[b]; } return b; }
+  int cur(int base) { return idOfRoot[find(base)]; }
+  Rec edgeRec(int e) const {
+    Rec r; r.add.assign(sAdd.begin() + (size_t)e * LE.nAdd, sAdd.begin() + (size_t)(e + 1) * LE.nAdd);
+    r.mx.assign(sMax.begin() + (size_t)e * LE.nMax, sMax.begin() + (size_t)(e + 1) * LE.nMax);
+    r.f.assign(sF64.begin() + (size_t)e * LE.nF64, sF64.begin() + (size_t)(e + 1) * LE.nF64);
+    return r;
+  }
+  // does base region b still own a live entry when it sits inside current region `inside`?
+  bool active(int b, int inside) {
+    for (int e = row[b]; e < row[b + 1]; ++e)
+      if (rev[e] < 0 || cur(eb[e]) != inside) return true;
+    return false;
+  }
+};
+
+void put_rec(uint32_t*& p, const Rec& r) {
+  size_t na = r.add.size(), nm = r.mx.size();
+  if (na) memcpy(p, r.add.data(), 4 * na);
+  if (nm) memcpy(p + na, r.mx.data(), 4 * nm);
+  size_t off = na + nm + ((na + nm) & 1);
+  if (!r.f.empty()) memcpy(p + off, r.f.data(), 8 * r.f.size());
+  p += off + 2 * r.f.size();
+}
+
+}  // namespace
+
+extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint32_t* order,
+                                        double* sal, double* rows, int64_t* n_merges,
+                                        int64_t* n_featurized) {
+  if (!h || !rf || !order || !sal) return GLIA_E_ARG;
+  if (!h->built) return GLIA_E_STATE;
+  // order / sal / rows are always HOST buffers (the chain itself runs on the host)
+  if (rf->device != h->prm.device) { h->err = "forest lives on another device"; return GLIA_E_ARG; }
+  if (rf->mdim > h->fc.dim) { h->err = "forest uses more features than the row has"; return GLIA_E_ARG; }
+  const int li = glia_rf_label_index(rf, -1);  // BC_LABEL_MERGE, hmt/bc_label.hxx:11
+  if (li < 0) { h->err = "forest has no class -1"; return GLIA_E_ARG; }
+  CK(cudaSetDevice(h->prm.device));
+  cudaStream_t st = h->stream;
+  const int R = (int)h->R, E = (int)h->E, C = (int)h->C, dim = h->fc.dim;
+  if (n_merges) *n_merges = 0;
+  if (n_featurized) *n_featurized = 0;
+  if (R == 0) return GLIA_OK;
+  Greedy G;
+  G.h = h; G.LR = h->vp.reg; G.LE = h->vp.edge; G.R = R; G.E = E;
+  const RecLayout LR = G.LR, LE = G.LE;
+  // ---- download the finalised graph
+  std::vector<uint32_t> lab(R), cAdd((size_t)R * LR.nAdd), cMax((size_t)R * LR.nMax), aAdd((size_t)R * LE.nAdd);
+  std::vector<double> cF64((size_t)R * LR.nF64), aF64((size_t)R * LE.nF64);
+  std::vector<int> cand(C);
+  G.ea.resize(E); G.eb.resize(E); G.rev.resize(E); G.row.resize(R + 1);
+  G.sAdd.resize((size_t)E * LE.nAdd); G.sMax.resize((size_t)E * LE.nMax); G.sF64.resize((size_t)E * LE.nF64);
+  auto dl = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+    return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+  };
+  CK(dl(lab.data(), h->regLabel.p, 4 * (size_t)R));
+  CK(dl(cAdd.data(), h->cAdd.p, 4 * cAdd.size())); CK(dl(cMax.data(), h->cMax.p, 4 * cMax.size()));
+  CK(dl(cF64.data(), h->cF64.p, 8 * cF64.size()));
+  CK(dl(aAdd.data(), h->bAggAdd.p, 4 * aAdd.size())); CK(dl(aF64.data(), h->bAggF64.p, 8 * aF64.size()));
+  CK(dl(cand.data(), h->cand.p, 4 * (size_t)C));
+  CK(dl(G.ea.data(), h->ea.p, 4 * (size_t)E)); CK(dl(G.eb.data(), h->eb.p, 4 * (size_t)E));
+  CK(dl(G.rev.data(), h->rev.p, 4 * (size_t)E)); CK(dl(G.row.data(), h->row.p, 4 * (size_t)(R + 1)));
+  CK(dl(G.sAdd.data(), h->sAdd.p, 4 * G.sAdd.size())); CK(dl(G.sMax.data(), h->sMax.p, 4 * G.sMax.size()));
+  CK(dl(G.sF64.data(), h->sF64.p, 8 * G.sF64.size()));
+  // ---- initial candidates: featurise + score in bulk on the device
+  std::vector<double> sal0(C), rows0;
+  if (C) {
+    CK(h->rows.ensure(8 * (size_t)C * dim));
+    CK(h->sal.ensure(8 * (size_t)C));
+    int s = glia_featurize_init_device(h, nullptr, h->rows.as<double>());
+    if (s) return s;
+    s = glia_rf_score_device(rf, h->rows.as<double>(), C, dim, li, nullptr, h->sal.as<double>(), st);
+    h->launches++;
+    if (s) return s;
+    CK(dl(sal0.data(), h->sal.p, 8 * (size_t)C));
+    if (rows) { rows0.resize((size_t)C * dim); CK(dl(rows0.data(), h->rows.p, 8 * rows0.size())); }
+  }
+  CK(cudaStreamSynchronize(st));
+  // ---- host state
+  const int maxIds = 2 * R;
+  G.reg.resize(maxIds); G.btot.resize(maxIds); G.nmOut.resize(maxIds); G.dm.resize(maxIds);
+  G.ufParent.resize(R); G.idOfRoot.resize(R); G.repBase.assign(maxIds, 0);
+  for (int a = 0; a < R; ++a) {
+    G.ufParent[a] = a; G.idOfRoot[a] = a; G.repBase[a] = a;
+    Rec& r = G.reg[a]; r.init(LR);
+    std::copy(cAdd.begin() + (size_t)a * LR.nAdd, cAdd.begin() + (size_t)(a + 1) * LR.nAdd, r.add.begin());
+    std::copy(cMax.begin() + (size_t)a * LR.nMax, cMax.begin() + (size_t)(a + 1) * LR.nMax, r.mx.begin());
+    std::copy(cF64.begin() + (size_t)a * LR.nF64, cF64.begin() + (size_t)(a + 1) * LR.nF64, r.f.begin());
+    Rec& b = G.btot[a]; b.init(LE); b.mx.clear();
+    std::copy(aAdd.begin() + (size_t)a * LE.nAdd, aAdd.begin() + (size_t)(a + 1) * LE.nAdd, b.add.begin());
+    std::copy(aF64.begin() + (size_t)a * LE.nF64, aF64.begin() + (size_t)(a + 1) * LE.nF64, b.f.begin());
+    for (int e = G.row[a]; e < G.row[a + 1]; ++e) {
+      if (G.rev[e] < 0) G.nmOut[a].push_back(e);
+      else G.dm[a].emplace(G.eb[e], G.edgeRec(e));
+    }
+  }
+  std::map<Key, Item> table;
+  typedef std::tuple<double, unsigned long long, Key> QKey;
+  std::set<QKey> queue;
+  unsigned long long seq = 0;
+  for (int c = 0; c < C; ++c) {  // ascending (min,max) key order == candidate order
+    int e = cand[c];
+    Item it; it.sal = sal0[c]; it.seq = seq++;
+    if (rows) it.row.assign(rows0.begin() + (size_t)c * dim, rows0.begin() + (size_t)(c + 1) * dim);
+    Key k(G.ea[e], G.eb[e]);
+    queue.insert(QKey(it.sal, it.seq, k));
+    table.emplace(k, std::move(it));
+  }
+  rows0.clear(); rows0.shrink_to_fit();
+  long long nfeat = C;
+  const uint32_t maxLabel = lab[R - 1];
+  auto label_of = [&](int id) -> uint32_t { return id < R ? lab[id] : maxLabel + 1 + (uint32_t)(id - R); };
+  // staging (pinned) + device scratch for the per-merge batches
+  const int regW = LR.nAdd + LR.nMax + ((LR.nAdd + LR.nMax) & 1) + 2 * LR.nF64;
+  const int edgeW = LE.nAdd + LE.nMax + ((LE.nAdd + LE.nMax) & 1) + 2 * LE.nF64;
+  const int stageWords = 2 * regW + 4 * edgeW;
+  size_t capBatch = 0;
+  uint32_t* hStage = nullptr; double* hSal = nullptr; double* hRows = nullptr;
+  uint32_t* dStage = nullptr; double* dSal = nullptr; double* dRows = nullptr;
+  auto release = [&]() {
+    if (hStage) cudaFreeHost(hStage); if (hSal) cudaFreeHost(hSal); if (hRows) cudaFreeHost(hRows);
+    if (dStage) cudaFree(dStage); if (dSal) cudaFree(dSal); if (dRows) cudaFree(dRows);
+    hStage = nullptr; hSal = nullptr; hRows = nullptr; dStage = nullptr; dSal = nullptr; dRows = nullptr;
+  };
+  auto ensure_batch = [&](size_t m) -> cudaError_t {
+    if (m <= capBatch) return cudaSuccess;
+    release();
+    capBatch = std::max<size_t>(2 * m, 256);
+    cudaError_t e;
+    if ((e = cudaMallocHost((void**)&hStage, 4 * capBatch * stageWords)) != cudaSuccess) return e;
+    if ((e = cudaMallocHost((void**)&hSal, 8 * capBatch)) != cudaSuccess) return e;
+    if ((e = cudaMallocHost((void**)&hRows, 8 * capBatch * dim)) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&dStage, 4 * capBatch * stageWords)) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&dSal, 8 * capBatch)) != cudaSuccess) return e;
+    return cudaMalloc((void**)&dRows, 8 * capBatch * dim);
+  };
+  struct Guard { decltype(release)& r; ~Guard() { r(); } } guard{release};
+
+  int M = 0;
+  int nextId = R;
+  std::vector<uint32_t> best1, best2; std::vector<int> owner1;
+  auto top2 = [&](int X) {  // per max word: best, its owning neighbour (-1: non-mutual), second best
+    best1.assign(LE.nMax, 0); best2.assign(LE.nMax, 0); owner1.assign(LE.nMax, -2);
+    auto feed = [&](const uint32_t* mx, int own) {
+      for (int i = 0; i < LE.nMax; ++i) {
+        uint32_t v = mx[i];
+        if (v > best1[i]) { best2[i] = best1[i]; best1[i] = v; owner1[i] = own; }
+        else if (v > best2[i]) best2[i] = v;
+      }
+    };
+    for (auto& kv : G.dm[X]) feed(kv.second.mx.data(), kv.first);
+    for (int e : G.nmOut[X]) feed(G.sMax.data() + (size_t)e * LE.nMax, -1);
+  };
+  while (!table.empty()) {
+    // top: largest saliency, among equals the most recently inserted (boundary_table.hxx:47-52)
+    QKey q = *queue.rbegin();
+    Key k01 = std::get<2>(q);
+    auto it01 = table.find(k01);
+    const int r0 = k01.first, r1 = k01.second, r2 = nextId++;
+    order[3 * (size_t)M] = label_of(r0); order[3 * (size_t)M + 1] = label_of(r1); order[3 * (size_t)M + 2] = label_of(r2);
+    sal[M] = it01->second.sal;
+    if (rows) memcpy(rows + (size_t)M * dim, it01->second.row.data(), 8 * (size_t)dim);
+    ++M;
+    queue.erase(q);
+    table.erase(it01);
+    // ---- rmap.merge(r0, r1, r2) on the records
+    G.reg[r2] = G.reg[r0]; G.reg[r2].merge(G.reg[r1]);
+    Rec& bz = G.btot[r2]; bz = G.btot[r0];
+    {
+      const Rec& b1 = G.btot[r1];
+      const Rec& d01 = G.dm[r0][r1]; const Rec& d10 = G.dm[r1][r0];
+      for (int i = 0; i < LE.nAdd; ++i) bz.add[i] = bz.add[i] + b1.add[i] - d01.add[i] - d10.add[i];
+      for (int i = 0; i < LE.nF64; ++i) bz.f[i] = bz.f[i] + b1.f[i] - d01.f[i] - d10.f[i];
+    }
+    G.nmOut[r2] = std::move(G.nmOut[r0]);
+    G.nmOut[r2].insert(G.nmOut[r2].end(), G.nmOut[r1].begin(), G.nmOut[r1].end());
+    G.nmOut[r1].clear();
+    // keys touching r0 or r1, ascending; first encounter of each neighbour (boundary_table.hxx:127-166)
+    std::vector<std::pair<Key, int>> keys;
+    for (int r : {r0, r1})
+      for (auto& kv : G.dm[r]) {
+        int W = kv.first;
+        if (W == r0 || W == r1) continue;
+        keys.push_back({Key(std::min(W, r), std::max(W, r)), W});
+      }
+    std::sort(keys.begin(), keys.end());
+    std::vector<int> Ws;
+    {
+      std::set<int> seen;
+      for (auto& kw : keys) if (seen.insert(kw.second).second) Ws.push_back(kw.second);
+    }
+    // adjacency of r2 and of its neighbours
+    for (int W : Ws) {
+      Rec out; out.init(LE); Rec in; in.init(LE);
+      for (int r : {r0, r1}) {
+        auto f = G.dm[r].find(W);
+        if (f != G.dm[r].end()) out.merge(f->second);
+        auto g = G.dm[W].find(r);
+        if (g != G.dm[W].end()) { in.merge(g->second); G.dm[W].erase(g); }
+      }
+      G.dm[r2].emplace(W, std::move(out));
+      G.dm[W].emplace(r2, std::move(in));
+    }
+    G.dm[r0].clear(); G.dm[r1].clear();
+    G.ufUnion(r0, r1, r2);
+    // erase the stale table items
+    for (auto& kw : keys) {
+      auto t = table.find(kw.first);
+      if (t != table.end()) { queue.erase(QKey(t->second.sal, t->second.seq, kw.first)); table.erase(t); }
+    }
+    const size_t m = Ws.size();
+    if (!m) continue;
+    {
+      cudaError_t e = ensure_batch(m);
+      if (e != cudaSuccess) { h->err = std::string("merge_order_bc batch buffers: ") + cudaGetErrorString(e); return GLIA_E_CUDA; }
+    }
+    // ---- stage the six records of every new candidate (X = W, Y = r2)
+    std::unordered_map<int, std::vector<int>> nmByTarget;
+    for (int e : G.nmOut[r2]) { int t = G.cur(G.eb[e]); if (t != r2) nmByTarget[t].push_back(e); }
+    top2(r2);
+    std::vector<uint32_t> yb1 = best1, yb2 = best2; std::vector<int> yo1 = owner1;
+    uint32_t* p = hStage;
+    for (int W : Ws) {
+      const Rec& dWY = G.dm[W][r2]; const Rec& dYW = G.dm[r2][W];
+      put_rec(p, G.reg[W]);
+      put_rec(p, G.reg[r2]);
+      top2(W);
+      Rec bx = G.btot[W]; bx.mx = best1;
+      Rec by = G.btot[r2]; by.mx = yb1;
+      Rec bzz; bzz.init(LE);
+      for (int i = 0; i < LE.nAdd; ++i) bzz.add[i] = bx.add[i] + by.add[i] - dWY.add[i] - dYW.add[i];
+      for (int i = 0; i < LE.nF64; ++i) bzz.f[i] = bx.f[i] + by.f[i] - dWY.f[i] - dYW.f[i];
+      for (int i = 0; i < LE.nMax; ++i)
+        bzz.mx[i] = std::max(owner1[i] == r2 ? best2[i] : best1[i], yo1[i] == W ? yb2[i] : yb1[i]);
+      Rec pb = dWY; pb.merge(dYW);  // pair boundary (util/struct.hxx:10-16)
+      for (int e : G.nmOut[W]) if (G.cur(G.eb[e]) == r2 && G.active(G.eb[e], r2)) pb.merge(G.edgeRec(e));
+      auto nt = nmByTarget.find(W);
+      if (nt != nmByTarget.end()) for (int e : nt->second) if (G.active(G.eb[e], W)) pb.merge(G.edgeRec(e));
+      put_rec(p, bx); put_rec(p, by); put_rec(p, bzz); put_rec(p, pb);
+    }
+    CK(cudaMemcpyAsync(dStage, hStage, 4 * m * stageWords, cudaMemcpyHostToDevice, st));
+    merge_batch_kernel<<<(unsigned)((m * 32 + 127) / 128), 128, 0, st>>>(
+        h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->ntree, li, dRows, dSal);
+    h->launches++;
+    CK(cudaMemcpyAsync(hSal, dSal, 8 * m, cudaMemcpyDeviceToHost, st));
+    if (rows) CK(cudaMemcpyAsync(hRows, dRows, 8 * m * dim, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    nfeat += (long long)m;
+    for (size_t j = 0; j < m; ++j) {
+      Item it; it.sal = hSal[j]; it.seq = seq++;
+      if (rows) it.row.assign(hRows + j * dim, hRows + (j + 1) * dim);
+      Key k(Ws[j], r2);
+      queue.insert(QKey(it.sal, it.seq, k));
+      table.emplace(k, std::move(it));
+    }
+  }
+  if (n_merges) *n_merges = M;
+  if (n_featurized) *n_featurized = nfeat;
+  return GLIA_OK;
+}

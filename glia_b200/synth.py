@@ -104,7 +104,7 @@ def speckle_volume(shape, nlabels, seed=0, dyadic=True):
 
 
 def random_forest(ntree, mdim, max_depth=12, seed=0, nclass=2, orig_labels=(-1, 1), thr_pool=None,
-                  leaf_prob=0.15):
+                  leaf_prob=0.15, features=None):
     """Random forest in the rf_old / classRF array layout (ml/rf/ml_rf.h:97-157): per tree a
     padded block of nrnodes nodes; treemap 1-based child ids, nodestatus -1 = terminal,
     bestvar 1-based feature, nodeclass 1-based class.  thr_pool: optional [n, mdim] sample matrix
@@ -120,7 +120,7 @@ def random_forest(ntree, mdim, max_depth=12, seed=0, nclass=2, orig_labels=(-1, 
                 ns[k] = -1
                 nc[k] = int(rng.integers(1, nclass + 1))
                 continue
-            f = int(rng.integers(0, mdim))
+            f = int(rng.integers(0, mdim)) if features is None else int(features[rng.integers(0, len(features))])
             t = float(thr_pool[rng.integers(0, len(thr_pool)), f]) if thr_pool is not None else float(rng.random())
             ns[k], bv[k], xb[k] = 1, f + 1, t
             for side in range(2):

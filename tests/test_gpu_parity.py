@@ -198,3 +198,88 @@ def test_score_candidates_matches_oracle():
         cols = np.flatnonzero(rowg[c] != rowo[c])
         assert len(cols) > 0
         np.testing.assert_allclose(rowg[c], rowo[c], rtol=RTOL, atol=1e-12)
+
+
+# ---------------------------------------------------------------- bc_feat stage / merge order
+def quant_pred(row):
+    s = float(np.sum(np.abs(row[:20]))) * 3.7
+    return np.floor((s - np.floor(s)) * 8) / 8.0
+
+
+TREE_CASES = [
+    ((24, 28), 30, 1, False, {}),
+    ((31, 17), 12, 2, True, dict(normalize=True, use_log=True)),
+    ((9, 10, 11), 14, 4, False, {}),
+    ((8, 12, 10), 10, 5, True, dict(normalize=True, use_log=True)),
+    ((40, 60), 150, 12, False, dict(simple=True)),
+]
+
+
+@pytest.mark.parametrize("case", TREE_CASES)
+def test_bc_feat_stage_matches_oracle(case):
+    """hmt/main_bc_feat.cxx: rows for every merge of a given order (with and without saliency)."""
+    shape, nl, seed, use_mask, kw = case
+    lab, pb = synth.speckle_volume(shape, nl, seed=seed)
+    mask = (np.random.default_rng(seed + 50).random(shape) > 0.05).astype(np.uint32) if use_mask else None
+    co, cg = _cfg_pair(pb, **kw)
+    o = ol.Oracle(lab, pb, co, mask=mask)
+    res = o.greedy(fn=quant_pred)  # a tie-heavy order: unbalanced trees, non-mutual boundaries inside
+    g = api.MergeTreeBuilder(shape, cg).build(lab, pb, mask)
+    for sal in (None, res["sal"]):
+        ro = o.bc_feat(res["order"], sal=sal, init_sal=1.0, sal_bias=0.25)
+        rg = g.bc_feat(res["order"], sal=sal, init_sal=1.0, sal_bias=0.25)
+        assert ro.shape == rg.shape
+        np.testing.assert_allclose(rg, ro, rtol=RTOL, atol=1e-12)
+    # a partial order (prefix) is a forest, not a tree
+    k = len(res["order"]) // 2
+    np.testing.assert_allclose(g.bc_feat(res["order"][:k]), o.bc_feat(res["order"][:k]), rtol=RTOL, atol=1e-12)
+    with pytest.raises(api.GliaError):
+        bad = res["order"].copy(); bad[0, 0] = 4000000
+        g.bc_feat(bad)
+
+
+def _exact_columns(rowo, rowg):
+    return np.flatnonzero((rowo == rowg).all(axis=0))
+
+
+@pytest.mark.parametrize("case", TREE_CASES)
+def test_merge_order_bc_matches_oracle(case):
+    """hmt/main_merge_order_bc.cxx: full greedy chain; order, saliencies and -b rows."""
+    shape, nl, seed, use_mask, kw = case
+    lab, pb = synth.speckle_volume(shape, nl, seed=seed)
+    mask = (np.random.default_rng(seed + 50).random(shape) > 0.05).astype(np.uint32) if use_mask else None
+    co, cg = _cfg_pair(pb, **kw)
+    o = ol.Oracle(lab, pb, co, mask=mask)
+    g = api.MergeTreeBuilder(shape, cg).build(lab, pb, mask)
+    _, rowo = o.init_candidates()
+    _, rowg = g.init_candidates()
+    # forest over the columns that are bit-identical (everything but log/log2/pow terms), few
+    # trees and shallow => heavy saliency ties: the queue's tie-break order is exercised
+    cols = _exact_columns(rowo, rowg)
+    assert len(cols) >= 5
+    f = synth.random_forest(9, o.row_dim(), max_depth=4, seed=seed, thr_pool=rowo, features=cols)
+    orf, grf = ol.OracleRF.from_arrays(f, o.row_dim()), api.Forest.from_arrays(f, o.row_dim())
+    ro = o.greedy(rf=orf)
+    rg = g.merge_order_bc(grf, want_rows=True)
+    assert np.array_equal(rg["order"], ro["order"])
+    assert np.array_equal(rg["sal"], ro["sal"])
+    assert rg["n_featurized"] == ro["n_cand"]
+    np.testing.assert_allclose(rg["rows"], ro["rows"], rtol=RTOL, atol=1e-12)
+
+
+def test_merge_order_c1_voronoi():
+    """configs[0]: 512x512, ~2.2k superpixels: the full greedy run the reference does on CPU."""
+    lab, pb = synth.voronoi_volume((512, 512), 11, seed=1234)
+    co, cg = _cfg_pair(pb)
+    o = ol.Oracle(lab, pb, co)
+    g = api.MergeTreeBuilder((512, 512), cg).build(lab, pb)
+    _, rowo = o.init_candidates()
+    _, rowg = g.init_candidates()
+    cols = _exact_columns(rowo, rowg)
+    f = synth.random_forest(31, o.row_dim(), max_depth=6, seed=1, thr_pool=rowo, features=cols)
+    orf, grf = ol.OracleRF.from_arrays(f, o.row_dim()), api.Forest.from_arrays(f, o.row_dim())
+    ro = o.greedy(rf=orf)
+    rg = g.merge_order_bc(grf)
+    assert len(rg["order"]) == g.R - 1
+    assert np.array_equal(rg["order"], ro["order"])
+    assert np.array_equal(rg["sal"], ro["sal"])
