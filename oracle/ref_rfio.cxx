@@ -35,6 +35,34 @@ int glia_refrf_rewrite(const char* in_path, const char* out_path) {
   return 0;
 }
 
+// Writes a model the way training does: ml_rf_train.cxx:696-719 stores each native classRF
+// array TRANSPOSED in the Model (dims swapped) and writeModelToBinaryFile dumps it as is.
+// (A Model that came from readModelFromBinaryFile holds native arrays, so re-writing it is not
+// a supported round trip in the reference.)  Native: [ntree][nrnodes] (treemap [ntree][2*nrnodes]).
+int glia_refrf_write_native(const char* path, int ntree, int nrnodes, int nclass, int mtry,
+                            int* treemap, int* nodestatus, double* xbestsplit, int* bestvar,
+                            int* nodeclass, int* ndbigtree, int* orig_labels) {
+  rf_old::Model m;
+  m.nrnodes = nrnodes; m.ntree = ntree; m.mtry = mtry; m.nclass = nclass;
+  m.xbestsplit = rf_old::transpose(xbestsplit, ntree, nrnodes);
+  m.n_xbestsplit[0] = nrnodes; m.n_xbestsplit[1] = ntree;
+  m.treemap = rf_old::transpose(treemap, 2 * ntree, nrnodes);
+  m.n_treemap[0] = nrnodes; m.n_treemap[1] = 2 * ntree;
+  m.nodestatus = rf_old::transpose(nodestatus, ntree, nrnodes);
+  m.n_nodestatus[0] = nrnodes; m.n_nodestatus[1] = ntree;
+  m.nodeclass = rf_old::transpose(nodeclass, ntree, nrnodes);
+  m.n_nodeclass[0] = nrnodes; m.n_nodeclass[1] = ntree;
+  m.bestvar = rf_old::transpose(bestvar, ntree, nrnodes);
+  m.n_bestvar[0] = nrnodes; m.n_bestvar[1] = ntree;
+  m.ndbigtree = rf_old::transpose(ndbigtree, ntree, 1);
+  m.n_ndbigtree[0] = 1; m.n_ndbigtree[1] = ntree;
+  m.orig_labels = new int[nclass];  // ~Model deletes its arrays
+  std::memcpy(m.orig_labels, orig_labels, nclass * sizeof(int));
+  m.n_orig_labels[0] = nclass; m.n_orig_labels[1] = 1;
+  rf_old::writeModelToBinaryFile(path, m);
+  return 0;
+}
+
 int glia_refrf_sizeof_model() { return (int)sizeof(rf_old::Model); }
 
 }  // extern "C"

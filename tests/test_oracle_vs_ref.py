@@ -133,3 +133,82 @@ def test_nondyadic_within_tolerance():
     rk = ref["cand_keys"]
     keys, rows = o.init_candidates(swap=(rk[:, 0] > rk[:, 1]).astype(np.uint8))
     np.testing.assert_allclose(rows, ref["cand_rows"], rtol=1e-5, atol=1e-12)
+
+
+def test_rf_model_file_layout_pinned_by_reference_reader(tmp_path):
+    """rf_old binary layout: a file written by the oracle is read back by the reference's own
+    readModelFromBinaryFile (ml/rf/ml_rf_model.cxx:459-563), and a file re-written by the
+    reference's writer is read back by the oracle, array for array."""
+    import ctypes as C
+    import os
+    so = os.path.join(ol.ORACLE_DIR, "_ref", "libglia_refrf.so")
+    if not os.path.exists(so):
+        try:
+            ol.build_ref()
+        except Exception:
+            pytest.skip("oracle/_ref not available")
+    L = C.CDLL(so)
+    assert L.glia_refrf_sizeof_model() == 520
+    f = synth.random_forest(23, 11, max_depth=8, seed=5, nclass=3, orig_labels=(-1, 1, 2))
+    orf = ol.OracleRF.from_arrays(f, 11)
+    p1, p2 = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")
+    assert orf.save(p1) == 0
+    nt, nr, nc = C.c_int(), C.c_int(), C.c_int()
+    L.glia_refrf_read.argtypes = [C.c_char_p] + [C.POINTER(C.c_int)] * 3 + [C.c_void_p] * 7
+    L.glia_refrf_read(p1.encode(), C.byref(nt), C.byref(nr), C.byref(nc), *([None] * 7))
+    assert (nt.value, nr.value, nc.value) == (23, f["nodestatus"].shape[1], 3)
+    g = dict(treemap=np.zeros_like(f["treemap"]), nodestatus=np.zeros_like(f["nodestatus"]),
+             xbestsplit=np.zeros_like(f["xbestsplit"]), bestvar=np.zeros_like(f["bestvar"]),
+             nodeclass=np.zeros_like(f["nodeclass"]), ndbigtree=np.zeros_like(f["ndbigtree"]),
+             orig_labels=np.zeros_like(f["orig_labels"]))
+    L.glia_refrf_read(p1.encode(), C.byref(nt), C.byref(nr), C.byref(nc),
+                      *[g[k].ctypes.data_as(C.c_void_p) for k in ("treemap", "nodestatus", "xbestsplit", "bestvar",
+                                                                  "nodeclass", "ndbigtree", "orig_labels")])
+    for k in g:
+        assert np.array_equal(g[k], f[k]), k
+    # the other direction: a file written by the reference's writer the way training fills the
+    # Model (ml_rf_train.cxx:696-719) is read back by the oracle
+    L.glia_refrf_write_native.argtypes = [C.c_char_p] + [C.c_int] * 4 + [C.c_void_p] * 7
+    L.glia_refrf_write_native(p2.encode(), 23, nr.value, 3, 1,
+                              *[f[k].ctypes.data_as(C.c_void_p) for k in ("treemap", "nodestatus", "xbestsplit",
+                                                                          "bestvar", "nodeclass", "ndbigtree",
+                                                                          "orig_labels")])
+    back = ol.OracleRF.load(p2).arrays()
+    for k in g:
+        assert np.array_equal(back[k], f[k]), k
+
+
+def test_rf_oracle_agrees_with_sklearn_rule():
+    """Independent cross-check of the restated traversal (x <= t goes left, leaf class votes):
+    sklearn trees use the same rule."""
+    sk = pytest.importorskip("sklearn.ensemble")
+    rng = np.random.default_rng(0)
+    X = rng.random((400, 6)); y = np.where(X[:, 0] + 0.3 * X[:, 3] + 0.1 * rng.standard_normal(400) > 0.6, 1, -1)
+    clf = sk.RandomForestClassifier(n_estimators=15, max_depth=7, random_state=0).fit(X, y)
+    trees = [e.tree_ for e in clf.estimators_]
+    nr = max(t.node_count for t in trees)
+    f = dict(treemap=np.zeros((15, nr, 2), np.int32), nodestatus=np.zeros((15, nr), np.int32),
+             xbestsplit=np.zeros((15, nr)), bestvar=np.zeros((15, nr), np.int32),
+             nodeclass=np.zeros((15, nr), np.int32), ndbigtree=np.zeros(15, np.int32),
+             orig_labels=np.array([-1, 1], np.int32))
+    for i, t in enumerate(trees):
+        n = t.node_count
+        leaf = t.children_left == -1
+        f["treemap"][i, :n, 0] = np.where(leaf, 0, t.children_left + 1)
+        f["treemap"][i, :n, 1] = np.where(leaf, 0, t.children_right + 1)
+        f["nodestatus"][i, :n] = np.where(leaf, -1, 1)
+        f["xbestsplit"][i, :n] = t.threshold
+        f["bestvar"][i, :n] = np.where(leaf, 0, t.feature + 1)
+        f["nodeclass"][i, :n] = np.where(leaf, t.value[:, 0, :].argmax(axis=1) + 1, 0)
+        f["ndbigtree"][i] = n
+    orf = ol.OracleRF.from_arrays(f, 6)
+    Xt = rng.random((300, 6))
+    votes, _ = orf.predict(Xt)
+    # sklearn compares float32(x) <= threshold: feed float32-representable inputs
+    Xt = Xt.astype(np.float32).astype(np.float64)
+    votes, _ = orf.predict(Xt)
+    sk_votes = np.zeros_like(votes)
+    for e in clf.estimators_:
+        c = e.predict(Xt).astype(int)  # class index 0/1
+        sk_votes[np.arange(len(Xt)), c] += 1
+    assert np.array_equal(votes, sk_votes)
