@@ -24,6 +24,7 @@ WORKLOADS = {
     "c1": ((512, 512), 11, "2D 512x512, ~2.2k superpixels (BASELINE.json configs[0])"),
     "c2": ((4096, 4096), 13, "2D 4096x4096 synthetic EM slice, ~100k superpixels (BASELINE.json configs[1])"),
     "c3": ((2048, 2048), 13, "2D 2048x2048 slices, ~25k superpixels each (BASELINE.json configs[2])"),
+    "c4s": ((512, 512, 512), 10, "3D 512^3 synthetic EM volume, ~137k supervoxels (profiling-size cut of configs[3])"),
     "c4": ((1024, 1024, 1024), 10, "3D 1024^3 synthetic EM volume, ~1.09M supervoxels (BASELINE.json configs[3])"),
 }
 THR = (0.2, 0.5, 0.8)

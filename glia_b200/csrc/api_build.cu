@@ -2,9 +2,12 @@
 #include <string.h>
 #include <algorithm>
 #include <vector>
+#include <stdlib.h>
 #include "handle.cuh"
+#include "voxel_fast.cuh"
 
 namespace glia {
+cudaError_t launch_voxel_pass_fast(const FastParams& P, cudaStream_t st);
 cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
@@ -101,7 +104,42 @@ extern "C" int glia_b200_build(glia_handle* h, const uint32_t* labels, const uin
   P.overflow = (int*)h->scalars.p + 12;
   // ---- voxel pass
   CK(cudaEventRecord(h->ev[6], st));
-  CK(launch_voxel_pass_generic(P, h->vc, st));
+  {
+    const char* force = getenv("GLIA_B200_FORCE_GENERIC");
+    const bool fast = !(force && force[0] == '1') && !P.mask && prm.n_rimg == 1 && prm.n_rlimg == 0 &&
+                      prm.n_bimg == 1 && prm.n_thr <= 3 && h->vc.reg[0].data == P.pb &&
+                      h->vc.edge[0].data == P.pb && h->vc.reg[0].bins <= 16 && h->vc.edge[0].bins <= 16;
+    h->usedFast = fast;
+    if (fast) {
+      FastParams F;
+      memset(&F, 0, sizeof(F));
+      F.labels = P.labels; F.pb = P.pb; F.ndim = P.ndim; F.X = P.X; F.Y = P.Y; F.Z = P.Z;
+      F.zBegin = P.zBegin; F.zEnd = P.zEnd; F.zBuf0 = P.zBuf0;
+      if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
+      F.TZ = 32;
+      F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);
+      F.tilesY = (P.Y + F.warpsY - 1) / F.warpsY;
+      F.tilesZ = (P.zEnd - P.zBegin + F.TZ - 1) / F.TZ;
+      F.nThr = P.nThr;
+      for (int t = 0; t < P.nThr; ++t) F.thr_up[t] = P.thr_up[t];
+      const Channel& rc = h->vc.reg[0]; const Channel& ec = h->vc.edge[0];
+      F.rBins = rc.bins; F.eBins = ec.bins;
+      F.rLo = rc.lo_dn; F.rHi = rc.hi_up; F.eLo = ec.lo_dn; F.eHi = ec.hi_up;
+      F.rInv = (float)(rc.bins / (prm.rimg[0].hi - prm.rimg[0].lo));
+      F.eInv = (float)(ec.bins / (prm.bimg[0].hi - prm.bimg[0].lo));
+      for (int i = 0; i < 16; ++i) { F.rBound[i] = rc.bound_up[i < rc.bins ? i : rc.bins - 1]; F.eBound[i] = ec.bound_up[i < ec.bins ? i : ec.bins - 1]; }
+      F.sameSpec = rc.bins == ec.bins && rc.lo_dn == ec.lo_dn && rc.hi_up == ec.hi_up &&
+                   memcmp(rc.bound_up, ec.bound_up, sizeof(float) * rc.bins) == 0;
+      F.reg = P.reg; F.edge = P.edge; F.labelBound = P.labelBound;
+      F.regAdd = P.regAdd; F.regMax = P.regMax; F.regF64 = P.regF64;
+      F.edgeCap = P.edgeCap; F.edgeKeys = P.edgeKeys; F.edgeAdd = P.edgeAdd; F.edgeMax = P.edgeMax; F.edgeF64 = P.edgeF64;
+      F.overflow = P.overflow;
+      F.regSlots = 128; F.edgeSlots = 512;
+      CK(launch_voxel_pass_fast(F, st));
+    } else {
+      CK(launch_voxel_pass_generic(P, h->vc, st));
+    }
+  }
   h->launches++;
   CK(cudaEventRecord(h->ev[1], st));
   int ovf = 0;

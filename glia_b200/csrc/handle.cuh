@@ -61,6 +61,7 @@ struct glia_handle {
   double ms[5] = {-1, -1, -1, -1, -1};
   long long launches = 0;
   bool built = false;
+  bool usedFast = false;
 
   // kernel-axis geometry (2D runs as X x 1 x rows)
   int KX = 0, KY = 0, KZ = 0;

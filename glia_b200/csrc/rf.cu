@@ -14,6 +14,7 @@
 // scores one candidate; all lanes of a warp walk the same tree at the same time, so the upper
 // levels are broadcast fetches.  Trees whose nodes fit are staged in shared memory.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <queue>
 #include "handle.cuh"
@@ -57,6 +58,51 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
   }
 }
 
+
+// v2: a CTA scores RF_CPB candidates whose rows are staged ONCE in shared memory (one coalesced
+// copy; the v1 kernel re-streamed them from DRAM ~85 times, profiles/r1_v1_ncu_rf.txt); four
+// threads share a candidate and split the trees, two trees in flight per thread; sibling pairs
+// are 32-byte aligned so that one L2 sector serves either outcome of a split.
+#define RF_CPB 64
+__global__ void __launch_bounds__(256)
+rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, int ntree,
+                     int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
+                     double* __restrict__ prob) {
+  extern __shared__ __align__(16) double srow[];
+  const size_t c0 = (size_t)blockIdx.x * RF_CPB;
+  const int ncand = (int)min((size_t)RF_CPB, N - c0);
+  // coalesced copy of the CTA's rows (contiguous in X) into padded shared rows
+  for (int i = threadIdx.x; i < ncand * D; i += blockDim.x) {
+    int c = i / D, f = i - c * D;
+    srow[c * ldRow + f] = X[c0 * D + i];
+  }
+  __syncthreads();
+  const int cand = threadIdx.x >> 2, slice = threadIdx.x & 3;
+  int hits = 0;
+  if (cand < ncand) {
+    const double* x = srow + cand * ldRow;
+    int t = slice;
+    for (; t + 4 < ntree; t += 8) {  // two trees in flight
+      int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4);
+      RfNode na = nodes[ka], nb = nodes[kb];
+      while (na.feat >= 0 || nb.feat >= 0) {
+        if (na.feat >= 0) { ka = na.left + (x[na.feat] <= na.thr ? 0 : 1); na = nodes[ka]; }
+        if (nb.feat >= 0) { kb = nb.left + (x[nb.feat] <= nb.thr ? 0 : 1); nb = nodes[kb]; }
+      }
+      hits += (na.left == labelIdx) + (nb.left == labelIdx);
+    }
+    for (; t < ntree; t += 4) {
+      int k = __ldg(treeOff + t);
+      RfNode nd = nodes[k];
+      while (nd.feat >= 0) { k = nd.left + (x[nd.feat] <= nd.thr ? 0 : 1); nd = nodes[k]; }
+      hits += (nd.left == labelIdx);
+    }
+  }
+  hits += __shfl_xor_sync(0xffffffffu, hits, 1);
+  hits += __shfl_xor_sync(0xffffffffu, hits, 2);
+  if (cand < ncand && slice == 0) prob[c0 + cand] = (double)hits / (double)ntree;
+}
+
 }  // namespace glia
 
 using namespace glia;
@@ -69,9 +115,11 @@ static int rf_build_device(glia_rf* m) {
   for (int t = 0; t < m->ntree; ++t) {
     const size_t o = (size_t)t * nr;
     const int* tm = m->treemap.data() + 2 * o;
-    treeOff[t] = (int)nodes.size();
+    if (nodes.size() & 1) nodes.push_back(RfNode{0.0, 0, -1});
+    treeOff[t] = (int)nodes.size();  // even: sibling pairs stay 32-byte aligned
     std::queue<std::pair<int, int>> q;  // (original node, new index)
     nodes.push_back(RfNode{0.0, 0, -1});
+    nodes.push_back(RfNode{0.0, 0, -1});  // pad
     q.push({0, treeOff[t]});
     int visited = 0;
     while (!q.empty()) {
@@ -247,9 +295,24 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
   if (dVotes)
     rf_score_kernel<true><<<blocks, 128, 128 * m->nclass * sizeof(int), st>>>(
         (const RfNode*)m->d_nodes, m->d_treeOff, m->ntree, m->nclass, labelIdx, dX, N, D, dVotes, dProb);
-  else
-    rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->ntree,
-                                                   m->nclass, labelIdx, dX, N, D, nullptr, dProb);
+  else {
+    int ldRow = D | 1;  // odd stride (in doubles): rows start on different banks
+    size_t smem = sizeof(double) * (size_t)RF_CPB * ldRow;
+    if (smem <= 200 * 1024) {
+      static bool attr = false;
+      if (!attr) {
+        cudaFuncSetAttribute(rf_score_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        const char* co = getenv("GLIA_B200_RF_CARVEOUT");  // percent of the SM's L1/shared array given to shared memory
+        if (co) cudaFuncSetAttribute(rf_score_smem_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(co));
+        attr = true;
+      }
+      rf_score_smem_kernel<<<(unsigned)((N + RF_CPB - 1) / RF_CPB), 256, smem, st>>>(
+          (const RfNode*)m->d_nodes, m->d_treeOff, m->ntree, labelIdx, dX, N, D, ldRow, dProb);
+    } else {
+      rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->ntree,
+                                                     m->nclass, labelIdx, dX, N, D, nullptr, dProb);
+    }
+  }
   return cudaGetLastError() == cudaSuccess ? GLIA_OK : GLIA_E_CUDA;
 }
 
