@@ -54,7 +54,9 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_init_candidates", "glia_b200_score_candidates", "glia_b200_merge_order_bc",
            "glia_b200_bc_feat", "glia_b200_rf_load", "glia_b200_rf_from_arrays",
            "glia_b200_rf_destroy", "glia_b200_rf_info", "glia_b200_rf_score", "glia_b200_last_ms",
-           "glia_b200_launch_count"]
+           "glia_b200_launch_count", "glia_b200_build_partial", "glia_b200_raw_region_tables",
+           "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
+           "glia_b200_import_edges", "glia_b200_finalize_edges", "glia_b200_synth_voronoi"]
 
 
 def lib():
@@ -92,6 +94,17 @@ def lib():
         L.glia_b200_last_ms.restype = C.c_double
         L.glia_b200_launch_count.argtypes = [vp]
         L.glia_b200_launch_count.restype = C.c_int64
+        i64p = C.POINTER(C.c_int64)
+        vpp = C.POINTER(vp)
+        L.glia_b200_build_partial.argtypes = [vp, vp, vp, vp]
+        L.glia_b200_raw_region_tables.argtypes = [vp, vpp, vpp, vpp, i64p, i64p, i64p]
+        L.glia_b200_finalize_regions.argtypes = [vp, i64p]
+        L.glia_b200_edge_interest.argtypes = [vp, C.c_int, vpp, i64p]
+        L.glia_b200_export_edges.argtypes = [vp, C.c_int, i64p, vpp, C.POINTER(C.c_int)]
+        L.glia_b200_import_edges.argtypes = [vp, vp, C.c_int64, C.c_int]
+        L.glia_b200_finalize_edges.argtypes = [vp, C.c_int64, C.c_int64]
+        L.glia_b200_synth_voronoi.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_int, C.c_uint32, vp, vp, vp,
+                                              C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -331,3 +344,50 @@ class MergeTreeBuilder:
         rows = np.zeros((n, self.row_dim(sal is not None)))
         self._check(lib().glia_b200_bc_feat(self.h, _addr(order), n, _addr(s), init_sal, sal_bias, _addr(rows)))
         return rows
+
+    # ---- multi-GPU pieces (include/glia_b200.h "multi-GPU"; driven by glia_b200/parallel.py) ----
+    def _counts(self):
+        v = [C.c_int64() for _ in range(3)]
+        self._check(lib().glia_b200_counts(self.h, *[C.byref(x) for x in v]))
+        self.R, self.E, self.Cn = (x.value for x in v)
+
+    def build_partial(self, labels, pb, mask=None):
+        if not self.device_pointers:
+            labels = np.ascontiguousarray(labels, np.uint32)
+            pb = np.ascontiguousarray(pb, np.float32)
+            mask = None if mask is None else np.ascontiguousarray(mask, np.uint32)
+            self._keep += [labels, pb, mask]
+        self._check(lib().glia_b200_build_partial(self.h, _addr(labels), _addr(mask), _addr(pb)))
+        return self
+
+    def raw_region_tables(self):
+        """[(device address, word count)] for the add (u32), max (u32) and f64 parts."""
+        p = [C.c_void_p() for _ in range(3)]
+        n = [C.c_int64() for _ in range(3)]
+        self._check(lib().glia_b200_raw_region_tables(self.h, *[C.byref(x) for x in p], *[C.byref(x) for x in n]))
+        return [(x.value or 0, y.value) for x, y in zip(p, n)]
+
+    def finalize_regions(self):
+        r = C.c_int64()
+        self._check(lib().glia_b200_finalize_regions(self.h, C.byref(r)))
+        self.R = r.value
+        return self.R
+
+    def edge_interest(self, world):
+        p, n = C.c_void_p(), C.c_int64()
+        self._check(lib().glia_b200_edge_interest(self.h, world, C.byref(p), C.byref(n)))
+        return p.value or 0, n.value
+
+    def export_edges(self, world):
+        counts = (C.c_int64 * world)()
+        p, rb = C.c_void_p(), C.c_int()
+        self._check(lib().glia_b200_export_edges(self.h, world, counts, C.byref(p), C.byref(rb)))
+        return list(counts), p.value or 0, rb.value
+
+    def import_edges(self, ptr, n, clear_first=True):
+        self._check(lib().glia_b200_import_edges(self.h, C.c_void_p(int(ptr)) if ptr else None, n, int(clear_first)))
+
+    def finalize_edges(self, lo, hi):
+        self._check(lib().glia_b200_finalize_edges(self.h, lo, hi))
+        self._counts()
+        return self

@@ -21,8 +21,8 @@ using namespace glia;
 #define CK(expr) GLIA_CUDA_CHECK(h, expr)
 static uint64_t pow2ceil(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
 
-extern "C" int glia_b200_build(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
-                               const float* pb) {
+// inputs -> device, table initialisation, voxel pass (raw tables).  Leaves the stream running.
+int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb) {
   if (!h || !labels || !pb) return GLIA_E_ARG;
   const glia_params& prm = h->prm;
   for (int i = 0; i < prm.n_rimg; ++i) if (!prm.rimg[i].data) { h->err = "rimg data null"; return GLIA_E_ARG; }
@@ -154,12 +154,17 @@ extern "C" int glia_b200_build(glia_handle* h, const uint32_t* labels, const uin
   }
   break;
   }
-  // ---- graph
-  if (prm.z_end > 0 && (P.zBegin > 0 || P.zEnd < P.Z)) {
-    // partial slab: the caller reduces the raw tables across ranks, then calls
-    // glia_b200_finalize (multi-GPU path)
-    h->err = "slab built; reduce raw tables then finalize";
-  }
+  h->partial = true;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_build(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
+                               const float* pb) {
+  int s = glia_build_raw(h, labels, mask, pb);
+  if (s != GLIA_OK) return s;
+  cudaStream_t st = h->stream;
+  // ---- graph (a handle created for a z-slab sees only its own planes: multi-GPU callers use
+  // glia_b200_build_partial + the exchange of shard.cu instead)
   s = glia_finalize_graph(h);
   if (s != GLIA_OK) return s;
   CK(cudaEventRecord(h->ev[2], st));

@@ -101,7 +101,8 @@ __global__ void reverse_edges_kernel(const int* __restrict__ ea, const int* __re
 
 struct IsCandidate {
   const int* ea; const int* eb; const int* rev;
-  __device__ bool operator()(int e) const { return ea[e] < eb[e] && rev[e] >= 0; }
+  int lo, hi;  // owned region-index range (multi-GPU: a candidate belongs to the owner of its smaller end)
+  __device__ bool operator()(int e) const { int a = ea[e]; return a < eb[e] && rev[e] >= 0 && a >= lo && a < hi; }
 };
 
 // Per-region aggregate over all of its directed boundaries (entries of a base region):
@@ -111,11 +112,12 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
                                           const uint32_t* __restrict__ sMax,
                                           const double* __restrict__ sF64,
                                           uint32_t* __restrict__ aAdd, uint32_t* __restrict__ aMax,
-                                          double* __restrict__ aF64) {
+                                          double* __restrict__ aF64, long long lo, long long hi) {
   long long r = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (r >= R) return;
   int e0 = row[r], e1 = row[r + 1];
+  (void)lo; (void)hi;  // every region whose boundaries are complete here (owned or neighbour of owned) is used
   for (int i = lane; i < L.nAdd; i += 32) {
     uint32_t s = 0;
     for (int e = e0; e < e1; ++e) s += sAdd[(size_t)e * L.nAdd + i];
@@ -140,8 +142,18 @@ using namespace glia;
 #define CK(expr) GLIA_CUDA_CHECK(h, expr)
 static inline unsigned nblk(long long n, int per) { return (unsigned)((n + per - 1) / per); }
 
+int glia_finalize_regions(glia_handle* h);
+int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi);
+
 // Builds the finalised graph from the raw tables.  Returns a GLIA_* status.
 int glia_finalize_graph(glia_handle* h) {
+  int s = glia_finalize_regions(h);
+  if (s != GLIA_OK) return s;
+  return glia_finalize_edges(h, 0, h->R);
+}
+
+// regions: presence -> dense index in ascending label order, compact records
+int glia_finalize_regions(glia_handle* h) {
   cudaStream_t st = h->stream;
   const VoxParams& P = h->vp;
   const uint32_t LB = P.labelBound;
@@ -178,7 +190,22 @@ int glia_finalize_graph(glia_handle* h) {
       h->regMax.as<uint32_t>(), h->regF64.as<double>(), h->regLabel.as<uint32_t>(),
       h->cAdd.as<uint32_t>(), h->cMax.as<uint32_t>(), h->cF64.as<double>());
   h->launches++;
+  CK(cudaGetLastError());
+  return GLIA_OK;
+}
 
+// directed boundaries of the local table -> CSR, reverse links, candidates whose smaller end lies
+// in [ownLo, ownHi), per-region boundary aggregate (identity outside the owned range)
+int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
+  cudaStream_t st = h->stream;
+  const VoxParams& P = h->vp;
+  const uint32_t LB = P.labelBound;
+  const long long R = h->R;
+  size_t tmpBytes = 0;
+  CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));
+  unsigned long long* dCounter = h->scalars.as<unsigned long long>();
+  int* dNumSel = (int*)(dCounter + 1);
+  int* dErr = (int*)(dCounter + 2);
   // ---- directed boundaries: compact, sort by (a,b) index pair
   // Upper bound on E is not known before compaction: count first with a null-output pass
   // would cost a second sweep, so size the outputs by the table capacity bound instead.
@@ -236,7 +263,7 @@ int glia_finalize_graph(glia_handle* h) {
     reverse_edges_kernel<<<nblk(E, 256), 256, 0, st>>>(h->ea.as<int>(), h->eb.as<int>(),
                                                        h->row.as<int>(), E, h->rev.as<int>());
     h->launches++;
-    IsCandidate pred{h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>()};
+    IsCandidate pred{h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>(), (int)ownLo, (int)ownHi};
     cub::CountingInputIterator<int> it(0);
     tmpBytes = 0;
     CK(cub::DeviceSelect::If(nullptr, tmpBytes, it, h->cand.as<int>(), dNumSel, (int)E, pred, st));
@@ -256,7 +283,7 @@ int glia_finalize_graph(glia_handle* h) {
     boundary_aggregate_kernel<<<nblk(R * 32, 256), 256, 0, st>>>(
         h->row.as<int>(), R, P.edge, h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
         h->sF64.as<double>(), h->bAggAdd.as<uint32_t>(), h->bAggMax.as<uint32_t>(),
-        h->bAggF64.as<double>());
+        h->bAggF64.as<double>(), ownLo, ownHi);
     h->launches++;
   }
   CK(cudaGetLastError());

@@ -61,6 +61,7 @@ struct glia_handle {
   double ms[5] = {-1, -1, -1, -1, -1};
   long long launches = 0;
   bool built = false;
+  bool partial = false;  // raw tables valid (glia_b200_build_partial / glia_b200_build)
   bool usedFast = false;
 
   // kernel-axis geometry (2D runs as X x 1 x rows)
@@ -82,4 +83,5 @@ struct glia_handle {
   glia::DevBuf sAdd, sMax, sF64, ea, eb, row, rev, cand;  // directed boundaries, CSR by a
   glia::DevBuf bAggAdd, bAggMax, bAggF64;                 // per-region sum over its boundaries
   glia::DevBuf cubTmp, scalars, rows, sal, keysOut;
+  glia::DevBuf interest, exportBuf, exportCursor;         // multi-GPU exchange (shard.cu)
 };

@@ -1,0 +1,235 @@
+// Multi-GPU (z-slab) support: the pieces of glia_b200_build split so that the partial tables of
+// the voxel pass can be combined across ranks.
+//
+// The reference has no distributed path (one process, util/mp.hxx OpenMP only); what is kept is
+// its result: every voxel is owned by exactly one slab, so the integer statistics add exactly.
+//   1. glia_b200_build_partial      voxel pass over the owned planes (halo planes supply labels)
+//   2. all-reduce of the dense per-label tables (sum / max / sum) by the caller
+//   3. glia_b200_finalize_regions   label -> dense region index (identical on every rank)
+//   4. glia_b200_edge_interest      which ranks need the boundaries of region x: the owner of x
+//                                   and the owners of every neighbour of x   (all-reduce max)
+//   5. glia_b200_export_edges       packed boundary records bucketed by destination rank
+//   6. all-to-all by the caller, glia_b200_import_edges merges equal label pairs (the "reduce
+//      keyed by label pair")
+//   7. glia_b200_finalize_edges     CSR + candidates whose smaller end lies in the owned range
+// A region index r is owned by rank min(world-1, r / ceil(R/world)).
+#include <algorithm>
+#include "handle.cuh"
+
+int glia_finalize_regions(glia_handle* h);
+int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi);
+int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);
+
+namespace glia {
+
+__device__ __forceinline__ int owner_of(uint32_t r, uint32_t chunk, int world) {
+  int o = (int)(r / chunk);
+  return o < world ? o : world - 1;
+}
+
+__global__ void edge_interest_kernel(const unsigned long long* __restrict__ keys, uint64_t cap,
+                                     const uint32_t* __restrict__ rank, uint32_t chunk, int world,
+                                     unsigned char* __restrict__ interest) {
+  uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (i >= cap) return;
+  unsigned long long k = keys[i];
+  if (k == EDGE_EMPTY) return;
+  uint32_t ra = rank[(uint32_t)(k >> 32)], rb = rank[(uint32_t)k];
+  int oa = owner_of(ra, chunk, world), ob = owner_of(rb, chunk, world);
+  interest[(size_t)ra * world + oa] = 1;
+  interest[(size_t)ra * world + ob] = 1;
+  interest[(size_t)rb * world + oa] = 1;
+}
+
+// pass 0: count records per destination; pass 1: write them (cursor = running position)
+template <int PASS>
+__global__ void export_edges_kernel(const unsigned long long* __restrict__ keys, uint64_t cap,
+                                    const uint32_t* __restrict__ rank,
+                                    const unsigned char* __restrict__ interest, int world,
+                                    RecLayout L, const uint32_t* __restrict__ gAdd,
+                                    const uint32_t* __restrict__ gMax, const double* __restrict__ gF64,
+                                    unsigned long long* __restrict__ cursor, int recWords,
+                                    uint32_t* __restrict__ out) {
+  uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (i >= cap) return;
+  unsigned long long k = keys[i];
+  if (k == EDGE_EMPTY) return;
+  uint32_t ra = rank[(uint32_t)(k >> 32)];
+  const int padW = (L.nAdd + L.nMax) & 1;
+  for (int d = 0; d < world; ++d) {
+    if (!interest[(size_t)ra * world + d]) continue;
+    unsigned long long pos = atomicAdd(cursor + d, 1ull);
+    if (PASS == 0) continue;
+    uint32_t* o = out + (size_t)pos * recWords;
+    o[0] = (uint32_t)k; o[1] = (uint32_t)(k >> 32);
+    for (int w = 0; w < L.nAdd; ++w) o[2 + w] = gAdd[(size_t)i * L.nAdd + w];
+    for (int w = 0; w < L.nMax; ++w) o[2 + L.nAdd + w] = gMax[(size_t)i * L.nMax + w];
+    if (padW) o[2 + L.nAdd + L.nMax] = 0;
+    double* f = (double*)(o + 2 + L.nAdd + L.nMax + padW);
+    for (int w = 0; w < L.nF64; ++w) f[w] = gF64[(size_t)i * L.nF64 + w];
+  }
+}
+
+__global__ void import_edges_kernel(const uint32_t* __restrict__ in, long long n, int recWords,
+                                    RecLayout L, unsigned long long* __restrict__ keys, uint64_t cap,
+                                    uint32_t* __restrict__ gAdd, uint32_t* __restrict__ gMax,
+                                    double* __restrict__ gF64, int* __restrict__ overflow) {
+  long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const uint32_t* p = in + (size_t)r * recWords;
+  const unsigned long long key = ((unsigned long long)p[1] << 32) | p[0];
+  const uint64_t mask = cap - 1;
+  uint64_t hsh = mix64(key) & mask;
+  long long slot = -1;
+  for (uint64_t probe = 0; probe < cap; ++probe) {
+    unsigned long long cur = keys[hsh];
+    if (cur == EDGE_EMPTY) cur = atomicCAS(keys + hsh, EDGE_EMPTY, key);
+    if (cur == key || cur == EDGE_EMPTY) { slot = (long long)hsh; break; }
+    hsh = (hsh + 1) & mask;
+  }
+  if (slot < 0) { atomicExch(overflow, 1); return; }
+  const int padW = (L.nAdd + L.nMax) & 1;
+  for (int w = 0; w < L.nAdd; ++w) { uint32_t v = p[2 + w]; if (v) atomicAdd(gAdd + (size_t)slot * L.nAdd + w, v); }
+  for (int w = 0; w < L.nMax; ++w) { uint32_t v = p[2 + L.nAdd + w]; if (v) atomicMax(gMax + (size_t)slot * L.nMax + w, v); }
+  const double* f = (const double*)(p + 2 + L.nAdd + L.nMax + padW);
+  for (int w = 0; w < L.nF64; ++w) atomicAdd(gF64 + (size_t)slot * L.nF64 + w, f[w]);
+}
+
+}  // namespace glia
+
+using namespace glia;
+#define CK(expr) GLIA_CUDA_CHECK(h, expr)
+static inline unsigned nblk(unsigned long long n, int per) { return (unsigned)((n + per - 1) / per); }
+static int rec_words(const RecLayout& L) { return 2 + L.nAdd + L.nMax + ((L.nAdd + L.nMax) & 1) + 2 * L.nF64; }
+
+extern "C" int glia_b200_build_partial(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb) {
+  if (!h || !labels || !pb) return GLIA_E_ARG;
+  if (h->prm.label_bound == 0) { h->err = "build_partial needs label_bound (identical on every rank)"; return GLIA_E_ARG; }
+  int s = glia_build_raw(h, labels, mask, pb);
+  if (s != GLIA_OK) return s;
+  CK(cudaStreamSynchronize(h->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev[6], h->ev[1]); h->ms[0] = ms;
+  cudaEventElapsedTime(&ms, h->ev[0], h->ev[6]); h->ms[4] = ms;
+  h->partial = true;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_raw_region_tables(glia_handle* h, void** add, void** mx, void** f64, int64_t* nAdd,
+                                           int64_t* nMax, int64_t* nF64) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  const VoxParams& P = h->vp;
+  if (add) *add = h->regAdd.p;
+  if (mx) *mx = h->regMax.p;
+  if (f64) *f64 = h->regF64.p;
+  if (nAdd) *nAdd = (int64_t)P.labelBound * P.reg.nAdd;
+  if (nMax) *nMax = (int64_t)P.labelBound * P.reg.nMax;
+  if (nF64) *nF64 = (int64_t)P.labelBound * P.reg.nF64;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_finalize_regions(glia_handle* h, int64_t* R) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  int s = glia_finalize_regions(h);
+  if (s != GLIA_OK) return s;
+  if (R) *R = h->R;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_edge_interest(glia_handle* h, int world, void** mask, int64_t* bytes) {
+  if (!h || world < 1 || world > 64) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  const VoxParams& P = h->vp;
+  const size_t n = (size_t)std::max<long long>(h->R, 1) * world;
+  CK(h->interest.ensure(n));
+  CK(cudaMemsetAsync(h->interest.p, 0, n, h->stream));
+  const uint32_t chunk = (uint32_t)std::max<long long>(1, (h->R + world - 1) / world);
+  edge_interest_kernel<<<nblk(P.edgeCap, 256), 256, 0, h->stream>>>(
+      (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), chunk, world,
+      h->interest.as<unsigned char>());
+  h->launches += 2;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  if (mask) *mask = h->interest.p;
+  if (bytes) *bytes = (int64_t)h->R * world;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_export_edges(glia_handle* h, int world, int64_t* counts, void** buf, int* rec_bytes) {
+  if (!h || world < 1 || world > 64 || !counts) return GLIA_E_ARG;
+  if (!h->partial || !h->interest.p) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  const VoxParams& P = h->vp;
+  cudaStream_t st = h->stream;
+  const int rw = rec_words(P.edge);
+  CK(h->exportCursor.ensure(8 * 64));
+  unsigned long long* cursor = h->exportCursor.as<unsigned long long>();
+  CK(cudaMemsetAsync(cursor, 0, 8 * 64, st));
+  export_edges_kernel<0><<<nblk(P.edgeCap, 256), 256, 0, st>>>(
+      (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), h->interest.as<unsigned char>(),
+      world, P.edge, nullptr, nullptr, nullptr, cursor, rw, nullptr);
+  unsigned long long cnt[64], off[64], total = 0;
+  CK(cudaMemcpyAsync(cnt, cursor, 8 * world, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  for (int d = 0; d < world; ++d) { off[d] = total; total += cnt[d]; counts[d] = (int64_t)cnt[d]; }
+  CK(h->exportBuf.ensure(4 * (size_t)rw * (size_t)std::max<unsigned long long>(total, 1)));
+  CK(cudaMemcpyAsync(cursor, off, 8 * world, cudaMemcpyHostToDevice, st));
+  export_edges_kernel<1><<<nblk(P.edgeCap, 256), 256, 0, st>>>(
+      (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), h->interest.as<unsigned char>(),
+      world, P.edge, h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), cursor, rw,
+      h->exportBuf.as<uint32_t>());
+  h->launches += 3;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  if (buf) *buf = h->exportBuf.p;
+  if (rec_bytes) *rec_bytes = 4 * rw;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_import_edges(glia_handle* h, const void* buf, int64_t n, int clear_first) {
+  if (!h || n < 0 || (n > 0 && !buf)) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  const VoxParams& P = h->vp;
+  cudaStream_t st = h->stream;
+  if (clear_first) {
+    const size_t cap = (size_t)P.edgeCap;
+    CK(cudaMemsetAsync(h->edgeKeys.p, 0xFF, 8 * cap, st));
+    CK(cudaMemsetAsync(h->edgeAdd.p, 0, 4 * cap * P.edge.nAdd, st));
+    CK(cudaMemsetAsync(h->edgeMax.p, 0, 4 * cap * P.edge.nMax, st));
+    CK(cudaMemsetAsync(h->edgeF64.p, 0, 8 * cap * P.edge.nF64, st));
+    CK(cudaMemsetAsync(P.overflow, 0, 4, st));
+    h->launches += 5;
+  }
+  if (n > 0) {
+    import_edges_kernel<<<nblk((unsigned long long)n, 256), 256, 0, st>>>(
+        (const uint32_t*)buf, n, rec_words(P.edge), P.edge, (unsigned long long*)h->edgeKeys.p, P.edgeCap,
+        h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), P.overflow);
+    h->launches++;
+  }
+  int ovf = 0;
+  CK(cudaMemcpyAsync(&ovf, P.overflow, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (ovf) { h->err = "directed-boundary table full during import: raise edge_capacity"; return GLIA_E_CAPACITY; }
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_finalize_edges(glia_handle* h, int64_t own_lo, int64_t own_hi) {
+  if (!h || own_lo < 0 || own_hi < own_lo) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  CK(cudaEventRecord(h->ev[1], h->stream));
+  int s = glia_finalize_edges(h, own_lo, std::min<long long>(own_hi, h->R));
+  if (s != GLIA_OK) return s;
+  CK(cudaEventRecord(h->ev[2], h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]); h->ms[1] = ms;
+  h->built = true;
+  h->err.clear();
+  return GLIA_OK;
+}

@@ -123,6 +123,27 @@ GLIA_API int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint32_
 GLIA_API int glia_b200_bc_feat(glia_handle* h, const uint32_t* order /*[n][3]*/, int64_t n,
                       const double* sal_in, double init_sal, double sal_bias, double* rows);
 
+/* ---- multi-GPU: z-slab sharding (no counterpart in the reference, which is single-process;
+ * preserves its results because every voxel is owned by exactly one slab).  One process and one
+ * handle per GPU, created with z_begin/z_end/halo_* and a label_bound common to all ranks.  Call
+ * order (glia_b200/parallel.py drives it over torch.distributed / NCCL):
+ *   build_partial -> all-reduce raw_region_tables (add: sum, max: unsigned max, f64: sum)
+ *   -> finalize_regions -> edge_interest (all-reduce max over the byte mask)
+ *   -> export_edges -> all-to-all of the per-destination record runs -> import_edges(clear_first=1)
+ *   -> finalize_edges(own_lo, own_hi) -> init_candidates / score_candidates on the owned candidates.
+ * Region index r (ascending label order, identical on all ranks) is owned by rank
+ * min(world-1, r / ceil(R/world)); a candidate (a,b), a<b, belongs to the owner of a.
+ * All returned pointers are DEVICE pointers owned by the handle. */
+GLIA_API int glia_b200_build_partial(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);
+GLIA_API int glia_b200_raw_region_tables(glia_handle* h, void** add, void** mx, void** f64, int64_t* n_add,
+                                         int64_t* n_max, int64_t* n_f64);
+GLIA_API int glia_b200_finalize_regions(glia_handle* h, int64_t* R);
+GLIA_API int glia_b200_edge_interest(glia_handle* h, int world, void** mask, int64_t* bytes);
+/* counts [world]: records for each destination rank, stored back to back in *buf in rank order. */
+GLIA_API int glia_b200_export_edges(glia_handle* h, int world, int64_t* counts, void** buf, int* rec_bytes);
+GLIA_API int glia_b200_import_edges(glia_handle* h, const void* buf, int64_t n, int clear_first);
+GLIA_API int glia_b200_finalize_edges(glia_handle* h, int64_t own_lo, int64_t own_hi);
+
 /* ---- random forest ---- */
 GLIA_API int glia_b200_rf_load(const char* path, int device, glia_rf** out);
 /* Native layouts after readModelFromBinaryFile's transposes (ml_rf_model.cxx:542-557):
