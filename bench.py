@@ -28,6 +28,8 @@ WORKLOADS = {
     "c4": ((1024, 1024, 1024), 10, "3D 1024^3 synthetic EM volume, ~1.09M supervoxels (BASELINE.json configs[3])"),
 }
 THR = (0.2, 0.5, 0.8)
+RF_SWEEP = dict(n=10_000_000, d=50, ntree=255, desc="RF scoring sweep: 255-tree forest over 10M merge candidates "
+                "with 50-dim bc features (BASELINE.json configs[4])")
 
 
 def load_peaks():
@@ -178,13 +180,17 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("GLIA_BENCH_WORKLOAD", "c2"), choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("GLIA_BENCH_WORKLOAD", "c2"),
+                    choices=sorted(WORKLOADS) + ["c5"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "c5":
+        import bench_modes
+        return bench_modes.run_rf_sweep(args, rank, world, local_rank)
     shape, cell, desc = WORKLOADS[args.workload]
     nd = len(shape)
     nvox = int(np.prod(shape))
@@ -218,10 +224,11 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    if nd == 3 and world > 1:
+        import bench_modes
+        return bench_modes.run_slab(args, rank, world, local_rank, dist)
     L = api.lib()
     import ctypes as C
-    L.glia_b200_synth_voronoi.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_void_p,
-                                          C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
     stream = torch.cuda.current_stream().cuda_stream
 
     # ---- synthetic inputs resident in HBM: NSETS distinct slices/volumes per rank, rotated so that
@@ -346,7 +353,7 @@ def main():
             "candidates_per_s": cands_all / (elapsed_ms * 1e-3),
             "stage_ms": {"table_init": kern_ms[4], "voxel_pass": kern_ms[0], "graph": kern_ms[1], "featurize": kern_ms[2],
                          "rf_score": kern_ms[3]},
-            "roofline": {"bound": "hbm", "kernel": "voxel_pass_generic", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "voxel_pass_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes},
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}

@@ -56,7 +56,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_rf_destroy", "glia_b200_rf_info", "glia_b200_rf_score", "glia_b200_last_ms",
            "glia_b200_launch_count", "glia_b200_build_partial", "glia_b200_raw_region_tables",
            "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
-           "glia_b200_import_edges", "glia_b200_finalize_edges", "glia_b200_synth_voronoi"]
+           "glia_b200_import_edges", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
+           "glia_b200_synth_voronoi_slab"]
 
 
 def lib():
@@ -105,6 +106,8 @@ def lib():
         L.glia_b200_finalize_edges.argtypes = [vp, C.c_int64, C.c_int64]
         L.glia_b200_synth_voronoi.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_int, C.c_uint32, vp, vp, vp,
                                               C.POINTER(C.c_uint64)]
+        L.glia_b200_synth_voronoi_slab.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_int, C.c_int, vp, vp,
+                                                   vp, C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 

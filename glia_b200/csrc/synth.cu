@@ -13,11 +13,14 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
 }
 
 __global__ void synth_voronoi_kernel(int nd, int X, int Y, int Z, int cell, uint32_t seed,
-                                     int ncx, int ncy, int ncz, uint32_t* __restrict__ labels,
-                                     float* __restrict__ pb) {
-  size_t n = (size_t)X * Y * Z;
-  for (size_t lin = blockIdx.x * (size_t)blockDim.x + threadIdx.x; lin < n;
-       lin += (size_t)gridDim.x * blockDim.x) {
+                                     int ncx, int ncy, int ncz, int zOff, int nzOut,
+                                     uint32_t* __restrict__ labels, float* __restrict__ pb) {
+  // writes planes [zOff, zOff + nzOut) of the X x Y x Z volume (a z-slab, or everything)
+  size_t n = (size_t)X * Y * nzOut;
+  const size_t linOff = (size_t)X * Y * zOff;
+  for (size_t out = blockIdx.x * (size_t)blockDim.x + threadIdx.x; out < n;
+       out += (size_t)gridDim.x * blockDim.x) {
+    const size_t lin = out + linOff;
     int x = (int)(lin % X); size_t r = lin / X;
     int y = (int)(r % Y), z = (int)(r / Y);
     int c[3] = {x / cell, y / cell, z / cell};
@@ -49,8 +52,8 @@ __global__ void synth_voronoi_kernel(int nd, int X, int Y, int Z, int cell, uint
     double u = (double)uh / 4294967296.0;
     double val = 0.8 * exp(-(d2v - d1) / 2.0) + 0.2 * u;
     val = val < 0.0 ? 0.0 : (val > 1.0 ? 1.0 : val);
-    labels[lin] = (uint32_t)(lab + 1);
-    pb[lin] = (float)(floor(255.0 * val) / 256.0);
+    labels[out] = (uint32_t)(lab + 1);
+    pb[out] = (float)(floor(255.0 * val) / 256.0);
   }
 }
 
@@ -66,6 +69,19 @@ extern "C" GLIA_API int glia_b200_synth_voronoi(int ndim, const int* dims, int c
   int ncx = (X + cell - 1) / cell, ncy = (Y + cell - 1) / cell, ncz = ndim == 3 ? (Z + cell - 1) / cell : 1;
   if (n_cells) *n_cells = (uint64_t)ncx * ncy * ncz;
   glia::synth_voronoi_kernel<<<148 * 16, 256, 0, (cudaStream_t)stream>>>(ndim, X, Y, Z, cell, seed, ncx, ncy,
-                                                                         ncz, labels, pb);
+                                                                         ncz, 0, Z, labels, pb);
+  return cudaGetLastError() == cudaSuccess ? GLIA_OK : GLIA_E_CUDA;
+}
+
+// Planes [z0, z0 + nz) of the same 3D volume (what one rank of the z-slab path holds, halo included).
+extern "C" GLIA_API int glia_b200_synth_voronoi_slab(const int* dims, int cell, uint32_t seed, int z0, int nz,
+                                                     uint32_t* labels, float* pb, void* stream,
+                                                     uint64_t* n_cells) {
+  if (!dims || cell <= 0 || !labels || !pb || z0 < 0 || nz <= 0 || z0 + nz > dims[2]) return GLIA_E_ARG;
+  int X = dims[0], Y = dims[1], Z = dims[2];
+  int ncx = (X + cell - 1) / cell, ncy = (Y + cell - 1) / cell, ncz = (Z + cell - 1) / cell;
+  if (n_cells) *n_cells = (uint64_t)ncx * ncy * ncz;
+  glia::synth_voronoi_kernel<<<148 * 16, 256, 0, (cudaStream_t)stream>>>(3, X, Y, Z, cell, seed, ncx, ncy, ncz,
+                                                                         z0, nz, labels, pb);
   return cudaGetLastError() == cudaSuccess ? GLIA_OK : GLIA_E_CUDA;
 }

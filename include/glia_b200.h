@@ -173,6 +173,9 @@ GLIA_API int64_t glia_b200_launch_count(const glia_handle* h);
  * glia_b200/synth.py::voronoi_volume.  dims: x (fastest), y, z. */
 GLIA_API int glia_b200_synth_voronoi(int ndim, const int* dims, int cell, uint32_t seed,
                                      uint32_t* labels, float* pb, void* stream, uint64_t* n_cells);
+/* planes [z0, z0+nz) of the same 3D volume: one rank's z-slab with its halo */
+GLIA_API int glia_b200_synth_voronoi_slab(const int* dims, int cell, uint32_t seed, int z0, int nz,
+                                          uint32_t* labels, float* pb, void* stream, uint64_t* n_cells);
 
 #ifdef __cplusplus
 }
