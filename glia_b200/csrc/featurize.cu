@@ -52,6 +52,114 @@ init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant_
   featurize_row(F, rx, ry, rz, bx, by, bz, pb, nullptr, rows + (size_t)c * F.dim);
 }
 
+// ---- v2: the x1 / x2 blocks of a row depend on ONE base region only, and each region takes part in
+// ~2 deg candidates, so they are computed once per region (region_blocks_kernel) and copied; a
+// candidate thread is left with x0 (differences, pair boundary) and x3 (merged region).  Same
+// device functions, same operation order: rows are bit-identical to init_candidates_kernel's
+// (3 instead of 9 entropy evaluations per candidate; log2 was ~60 % of the v1 kernel,
+// profiles/r1_v3_ncu_c4s.txt).
+// block layout: [0, xi) = push_region output, [xi] = area, [xi+1] = perim (normalised, before --logs)
+__global__ void __launch_bounds__(128)
+region_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G, int xi,
+                     double* __restrict__ blk) {
+  long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (r >= G.R) return;
+  const RecLayout LR = F.reg, LE = F.edge;
+  RecSingle rx{G.cAdd + (size_t)r * LR.nAdd, G.cMax + (size_t)r * LR.nMax, G.cF64 + (size_t)r * LR.nF64};
+  RecSingle bx{G.aAdd + (size_t)r * LE.nAdd, G.aMax + (size_t)r * LE.nMax, G.aF64 + (size_t)r * LE.nF64};
+  ShapeFeat s;
+  shape_feat(F, rx, bx, s);
+  double* o = blk + (size_t)r * (xi + 2);
+  push_region(F, s, rx, bx, nullptr, o);
+  o[xi] = s.area; o[xi + 1] = s.perim;
+}
+
+__global__ void __launch_bounds__(128)
+init_candidates_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G, int xi,
+                              const double* __restrict__ blk, uint32_t* __restrict__ keys,
+                              double* __restrict__ rows) {
+  long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (c >= G.C) return;
+  const int e = G.cand[c], rv = G.rev[e];
+  const int a = G.ea[e], b = G.eb[e];
+  if (keys) { keys[2 * c] = G.regLabel[a]; keys[2 * c + 1] = G.regLabel[b]; }
+  if (!rows) return;
+  const RecLayout LR = F.reg, LE = F.edge;
+  RecSingle rx{G.cAdd + (size_t)a * LR.nAdd, G.cMax + (size_t)a * LR.nMax, G.cF64 + (size_t)a * LR.nF64};
+  RecSingle ry{G.cAdd + (size_t)b * LR.nAdd, G.cMax + (size_t)b * LR.nMax, G.cF64 + (size_t)b * LR.nF64};
+  RecSum2 rz{rx, ry};
+  RecSingle pe{G.sAdd + (size_t)e * LE.nAdd, G.sMax + (size_t)e * LE.nMax, G.sF64 + (size_t)e * LE.nF64};
+  RecSingle pr{G.sAdd + (size_t)rv * LE.nAdd, G.sMax + (size_t)rv * LE.nMax, G.sF64 + (size_t)rv * LE.nF64};
+  RecSum2 pb{pe, pr};  // pair boundary b(X,Y) = (a->b) u (b->a)   (util/struct.hxx:10-16)
+  RecBoundaryZ bz;
+  bz.pa = G.aAdd + (size_t)a * LE.nAdd; bz.qa = G.aAdd + (size_t)b * LE.nAdd; bz.ea = pe.a; bz.ra = pr.a;
+  for (int i = 0; i < LE.nMax; ++i) bz.mxw[i] = 0;
+  for (int i = 0; i < LE.nF64; ++i) bz.f[i] = 0.0;
+  for (int side = 0; side < 2; ++side) {  // entries(Z), region.hxx:66-75
+    int r = side ? b : a;
+    for (int k = G.row[r]; k < G.row[r + 1]; ++k) {
+      if (k == e || k == rv) continue;
+      for (int i = 0; i < LE.nMax; ++i) bz.mxw[i] = max(bz.mxw[i], G.sMax[(size_t)k * LE.nMax + i]);
+      for (int i = 0; i < LE.nF64; ++i) bz.f[i] += G.sF64[(size_t)k * LE.nF64 + i];
+    }
+  }
+  const int ld = xi + 2;
+  const double* A = blk + (size_t)a * ld;
+  const double* B = blk + (size_t)b * ld;
+  const bool swp = A[xi] > B[xi];  // strict >, hmt/main_merge_order_bc.cxx:77-80
+  const double* B1 = swp ? B : A;
+  const double* B2 = swp ? A : B;
+  const double a1 = B1[xi], a2 = B2[xi], p1 = B1[xi + 1], p2 = B2[xi + 1];
+  const int T = F.nThr, lg = F.useLog;
+  const uint32_t nb = pb.add(0), nX = rx.add(0), nY = ry.add(0);
+  double* p = rows + (size_t)c * F.dim;
+  const double areaDiff = fabs(a1 - a2), perimDiff = fabs(p1 - p2);
+  const double bl = sdivide(ceil(nb / 2.0), F.normLen, 0.0);
+  *p++ = lg ? slog(areaDiff, 0) : areaDiff;
+  *p++ = sdivide(areaDiff, a1, 0.0);
+  *p++ = sdivide(areaDiff, a2, 0.0);
+  *p++ = lg ? slog(perimDiff, 0) : perimDiff;
+  *p++ = sdivide(perimDiff, p1, 0.0);
+  *p++ = sdivide(perimDiff, p2, 0.0);
+  *p++ = lg ? slog(bl, 0) : bl;
+  *p++ = sdivide(bl, a1, 0.0);
+  *p++ = sdivide(bl, a2, 0.0);
+  *p++ = sdivide(bl, p1, 0.0);
+  *p++ = sdivide(bl, p2, 0.0);
+  double vbl[GLIA_MAX_THR];
+  for (int t = 0; t < T; ++t) vbl[t] = sdivide(ceil(pb.add(1 + t) / 2.0), F.normLen, 0.0);
+  for (int t = 0; t < T; ++t) *p++ = lg ? slog(vbl[t], 0) : vbl[t];
+  for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], bl, 0.0);
+  for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], p1, 0.0);
+  for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], p2, 0.0);
+  const int off0 = 4 + F.D + 2 * T;  // first image feature inside a block
+  for (int i = 0; i < F.nR; ++i) {
+    double l1, x2;
+    const double* g1 = A + off0 + 5 * i;
+    const double* g2 = B + off0 + 5 * i;
+    hist_dists(rx, nX, ry, nY, F.rBins[i], F.rAdd[i], l1, x2);
+    *p++ = l1; *p++ = x2;
+    for (int k = 0; k < 5; ++k) *p++ = fabs(g1[k] - g2[k]);  // entropy, mean, stddev, min, max
+  }
+  for (int i = 0; i < F.nRL; ++i) {
+    double l1, x2;
+    hist_dists(rx, nX, ry, nY, F.rlBins[i], F.rlAdd[i], l1, x2);
+    *p++ = l1; *p++ = x2; *p++ = fabs(A[off0 + 5 * F.nR + i] - B[off0 + 5 * F.nR + i]);
+  }
+  ImgFeat g;
+  for (int k = 0; k < F.nB; ++k) {
+    img_feat(pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g);
+    *p++ = g.entropy; *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
+  }
+  for (int k = 0; k < xi; ++k) *p++ = B1[k];
+  for (int k = 0; k < xi; ++k) *p++ = B2[k];
+  ShapeFeat sz;
+  RecSingle bxr{bz.pa, nullptr, nullptr};
+  (void)bxr;
+  shape_feat(F, rz, bz, sz);
+  push_region(F, sz, rz, bz, nullptr, p);
+}
+
 }  // namespace glia
 
 using namespace glia;
@@ -73,7 +181,16 @@ int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows) {
   if (h->C == 0) return GLIA_OK;
   GraphView G = glia_graph_view(h);
   unsigned blocks = (unsigned)((h->C + 127) / 128);
-  init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, dKeys, dRows);
+  const glia_params& c = h->prm;
+  const int xi = c.ndim + 4 + 2 * c.n_thr + 5 * c.n_rimg + c.n_rlimg + 5 * c.n_bimg;
+  if (h->fc.simple || !dRows) {
+    init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, dKeys, dRows);
+  } else {
+    GLIA_CUDA_CHECK(h, h->regBlocks.ensure(8 * (size_t)(h->R + 1) * (xi + 2)));
+    region_blocks_kernel<<<(unsigned)((h->R + 127) / 128), 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>());
+    init_candidates_blocks_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>(), dKeys, dRows);
+    h->launches++;
+  }
   h->launches++;
   GLIA_CUDA_CHECK(h, cudaGetLastError());
   return GLIA_OK;

@@ -83,5 +83,6 @@ struct glia_handle {
   glia::DevBuf sAdd, sMax, sF64, ea, eb, row, rev, cand;  // directed boundaries, CSR by a
   glia::DevBuf bAggAdd, bAggMax, bAggF64;                 // per-region sum over its boundaries
   glia::DevBuf cubTmp, scalars, rows, sal, keysOut;
+  glia::DevBuf regBlocks;                                 // per-region x1/x2 row blocks (featurize.cu)
   glia::DevBuf interest, exportBuf, exportCursor;         // multi-GPU exchange (shard.cu)
 };
