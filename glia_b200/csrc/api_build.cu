@@ -8,6 +8,7 @@
 
 namespace glia {
 cudaError_t launch_voxel_pass_fast(const FastParams& P, cudaStream_t st);
+cudaError_t launch_voxel_pass_runs(const FastParams& P, cudaStream_t st);
 cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
@@ -116,7 +117,13 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.labels = P.labels; F.pb = P.pb; F.ndim = P.ndim; F.X = P.X; F.Y = P.Y; F.Z = P.Z;
       F.zBegin = P.zBegin; F.zEnd = P.zEnd; F.zBuf0 = P.zBuf0;
       if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
-      F.TZ = 32;
+      // GLIA_B200_VOXEL=runs selects the experimental v4 kernel (register runs + warp-segment flush,
+      // voxel_runs.cu: parity-green but slower, profiles/r1_v4_notes.txt); default is v3
+      const char* vsel = getenv("GLIA_B200_VOXEL");
+      const bool useRuns = vsel && vsel[0] == 'r';
+      const char* tzs = getenv("GLIA_B200_TZ");
+      F.TZ = tzs ? atoi(tzs) : (useRuns ? (P.ndim == 3 ? 64 : 32) : 32);
+      if (F.TZ < 1) F.TZ = 32;
       F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);
       F.tilesY = (P.Y + F.warpsY - 1) / F.warpsY;
       F.tilesZ = (P.zEnd - P.zBegin + F.TZ - 1) / F.TZ;
@@ -135,7 +142,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.edgeCap = P.edgeCap; F.edgeKeys = P.edgeKeys; F.edgeAdd = P.edgeAdd; F.edgeMax = P.edgeMax; F.edgeF64 = P.edgeF64;
       F.overflow = P.overflow;
       F.regSlots = 128; F.edgeSlots = 512;
-      CK(launch_voxel_pass_fast(F, st));
+      if (useRuns) CK(launch_voxel_pass_runs(F, st)); else CK(launch_voxel_pass_fast(F, st));
     } else {
       CK(launch_voxel_pass_generic(P, h->vc, st));
     }

@@ -1,3 +1,6 @@
+// EXPERIMENTAL (GLIA_B200_VOXEL=runs; parity-green, currently 2.3x slower than voxel_fast.cu - the
+// warp flushes nearly every step because ONE lane with a second finished run triggers it; see
+// profiles/r1_v4_notes.txt for the measurements and the per-lane queue that should fix it).
 // K1+K3+K4 fused, v4 "runs" (default hmt configuration: one image = the boundary-probability map
 // as region image, boundary image and threshold source; <= 16 bins, <= 3 thresholds, no mask).
 // Same results as voxel_pass_generic / voxel_pass_fast; reference semantics:
@@ -14,8 +17,8 @@
 //     counts, sum, sum^2, min, max, bbox evidence;
 //   * along x: a finished run is parked in a second register set ("pending"); when any lane has
 //     to park a second one, the WHOLE warp flushes its pending runs together: neighbouring lanes
-//     whose pending runs carry the same label (pair) form a segment, integers are combined with
-//     redux.sync over the segment mask, doubles with a 5-step segmented shuffle reduction, and only
+//     whose pending runs carry the same label (pair) form a segment, integers and doubles are combined with
+//     a 5-step segmented shuffle reduction (redux.sync with per-lane masks is emulated), and only
 //     the segment head issues global RED operations (native f64 add / u32 max in L2).
 // No shared memory, no per-CTA tables, no hash lookups for regions (records are indexed by label);
 // boundary records are found by the segment head in the global open-addressing table.
@@ -75,11 +78,20 @@ __device__ __forceinline__ uint32_t segment_mask(bool head, int lane, int& end) 
   return (0xffffffffu >> (31 - end)) & (0xffffffffu << start);
 }
 
-__device__ __forceinline__ void seg_sum2(double& s, double& s2, int lane, int end) {
+// Segmented reductions towards the segment head by shuffles (redux.sync with per-lane masks is
+// emulated by a loop over the distinct masks - 25x slower here, profiles/r1_v4_notes.txt).
+// After the 5 steps lane i holds the combination of lanes [i, end]; only heads use it.
+#define SEG_REDUCE_BEGIN for (int d_ = 1; d_ < 32; d_ <<= 1) { const bool ok_ = lane + d_ <= end;
+#define SEG_ADD(v) { auto t_ = __shfl_down_sync(0xffffffffu, v, d_); if (ok_) v += t_; }
+#define SEG_MAX(v) { uint32_t t_ = __shfl_down_sync(0xffffffffu, v, d_); if (ok_) v = max(v, t_); }
+#define SEG_REDUCE_END }
+
+// 16 x 4-bit bins -> 8 words of 2 x 16-bit bins (a segment sums at most 32 x 15 per bin)
+__device__ __forceinline__ void widen_hist(uint32_t hlo, uint32_t hhi, uint32_t (&w)[8]) {
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    double t = __shfl_down_sync(0xffffffffu, s, d), t2 = __shfl_down_sync(0xffffffffu, s2, d);
-    if (lane + d <= end) { s += t; s2 += t2; }
+  for (int j = 0; j < 4; ++j) {
+    w[j] = ((hlo >> (8 * j)) & 0xFu) | (((hlo >> (8 * j + 4)) & 0xFu) << 16);
+    w[4 + j] = ((hhi >> (8 * j)) & 0xFu) | (((hhi >> (8 * j + 4)) & 0xFu) << 16);
   }
 }
 
@@ -91,43 +103,43 @@ __device__ __forceinline__ void flush_regions(const FastParams& P, RegAcc& r, in
   int end;
   const uint32_t seg = segment_mask(lane == 0 || !valid || !pv || pl != r.label, lane, end);
   const bool head = valid && (seg & ((1u << lane) - 1)) == 0;
-  uint32_t* ga = nullptr; uint32_t* gm = nullptr; double* gf = nullptr;
-  if (head) {
-    if (r.label >= P.labelBound) atomicExch(P.overflow, 2);
-    else {
-      ga = P.regAdd + (size_t)r.label * P.reg.nAdd;
-      gm = P.regMax + (size_t)r.label * P.reg.nMax;
-      gf = P.regF64 + (size_t)r.label * P.reg.nF64;
-    }
-  }
-  const uint32_t c = __reduce_add_sync(seg, r.cnt);
-  if (ga) { atomicAdd(ga, c & 0xFFFFu); if (c >> 16) atomicAdd(ga + 1, c >> 16); }
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const uint32_t v = ((k < 8 ? r.hlo : r.hhi) >> (4 * (k & 7))) & 15u;
-    const uint32_t t = __reduce_add_sync(seg, v);
-    if (ga && t) atomicAdd(ga + 2 + k, t);
-  }
+  // bbox along x / y from ballots: first / last lane of the segment that saw an outside neighbour
+  const uint32_t f0 = __ballot_sync(0xffffffffu, valid && (r.flags & 1u)) & seg;
+  const uint32_t f1 = __ballot_sync(0xffffffffu, valid && (r.flags & 2u)) & seg;
+  const uint32_t f2 = __ballot_sync(0xffffffffu, valid && (r.flags & 4u)) & seg;
+  const uint32_t f3 = __ballot_sync(0xffffffffu, valid && (r.flags & 8u)) & seg;
+  uint32_t w[8];
+  widen_hist(r.hlo, r.hhi, w);
+  uint32_t c = r.cnt, kmin = r.kmin, kmax = r.kmax, z0 = r.czmin, z1 = r.czmax;
   double s = r.s, s2 = r.s2;
-  seg_sum2(s, s2, lane, end);
-  if (gf) { atomicAdd(gf, s); atomicAdd(gf + 1, s2); }
-  const uint32_t kmin = __reduce_max_sync(seg, r.kmin), kmax = __reduce_max_sync(seg, r.kmax);
-  const uint32_t x0 = __reduce_max_sync(seg, (r.flags & 1u) ? ~(uint32_t)gx : 0u);
-  const uint32_t x1 = __reduce_max_sync(seg, (r.flags & 2u) ? (uint32_t)gx + 1u : 0u);
-  const uint32_t y0 = __reduce_max_sync(seg, (r.flags & 4u) ? ~(uint32_t)gy : 0u);
-  const uint32_t y1 = __reduce_max_sync(seg, (r.flags & 8u) ? (uint32_t)gy + 1u : 0u);
-  const uint32_t z0 = __reduce_max_sync(seg, r.czmin), z1 = __reduce_max_sync(seg, r.czmax);
-  if (gm) {
-    if (x0) atomicMax(gm + 0, x0);
-    if (y0) atomicMax(gm + 1, y0);
-    if (z0) atomicMax(gm + 2, z0);
-    if (x1) atomicMax(gm + 3, x1);
-    if (y1) atomicMax(gm + 4, y1);
-    if (z1) atomicMax(gm + 5, z1);
-    if (kmin) atomicMax(gm + 6, kmin);
-    if (kmax) atomicMax(gm + 7, kmax);
-  }
+  SEG_REDUCE_BEGIN
+    SEG_ADD(c) SEG_ADD(s) SEG_ADD(s2)
+    SEG_ADD(w[0]) SEG_ADD(w[1]) SEG_ADD(w[2]) SEG_ADD(w[3]) SEG_ADD(w[4]) SEG_ADD(w[5]) SEG_ADD(w[6]) SEG_ADD(w[7])
+    SEG_MAX(kmin) SEG_MAX(kmax) SEG_MAX(z0) SEG_MAX(z1)
+  SEG_REDUCE_END
   r.cnt = 0;
+  if (!head) return;
+  if (r.label >= P.labelBound) { atomicExch(P.overflow, 2); return; }
+  uint32_t* ga = P.regAdd + (size_t)r.label * P.reg.nAdd;
+  uint32_t* gm = P.regMax + (size_t)r.label * P.reg.nMax;
+  double* gf = P.regF64 + (size_t)r.label * P.reg.nF64;
+  atomicAdd(ga, c & 0xFFFFu);
+  if (c >> 16) atomicAdd(ga + 1, c >> 16);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (w[j] & 0xFFFFu) atomicAdd(ga + 2 + 2 * j, w[j] & 0xFFFFu);
+    if (w[j] >> 16) atomicAdd(ga + 3 + 2 * j, w[j] >> 16);
+  }
+  atomicAdd(gf, s); atomicAdd(gf + 1, s2);
+  const int x0lane = gx - lane;
+  if (f0) atomicMax(gm + 0, ~(uint32_t)(x0lane + __ffs(f0) - 1));
+  if (f2) atomicMax(gm + 1, ~(uint32_t)gy);
+  if (z0) atomicMax(gm + 2, z0);
+  if (f1) atomicMax(gm + 3, (uint32_t)(x0lane + 31 - __clz(f1)) + 1u);
+  if (f3) atomicMax(gm + 4, (uint32_t)gy + 1u);
+  if (z1) atomicMax(gm + 5, z1);
+  if (kmin) atomicMax(gm + 6, kmin);
+  if (kmax) atomicMax(gm + 7, kmax);
 }
 
 __device__ __forceinline__ void flush_edges(const FastParams& P, EdgeAcc& e, int lane) {
@@ -137,34 +149,38 @@ __device__ __forceinline__ void flush_edges(const FastParams& P, EdgeAcc& e, int
   int end;
   const uint32_t seg = segment_mask(lane == 0 || !valid || !pv || pa != e.a || pb != e.b, lane, end);
   const bool head = valid && (seg & ((1u << lane) - 1)) == 0;
-  uint32_t* ga = nullptr; uint32_t* gm = nullptr; double* gf = nullptr;
-  if (head) {
-    const long long g = edge_slot(P, ((unsigned long long)e.a << 32) | e.b);
-    if (g >= 0) {
-      ga = P.edgeAdd + (size_t)g * P.edge.nAdd;
-      gm = P.edgeMax + (size_t)g * P.edge.nMax;
-      gf = P.edgeF64 + (size_t)g * P.edge.nF64;
-    }
-  }
-  const uint32_t c = __reduce_add_sync(seg, e.cnt & 0xFFu);
-  if (ga) atomicAdd(ga, c);
-#pragma unroll
-  for (int t = 0; t < 3; ++t) {
-    const uint32_t v = __reduce_add_sync(seg, (e.cnt >> (8 * (t + 1))) & 0xFFu);  // type/feat.hxx:498
-    if (ga && t < P.nThr && v) atomicAdd(ga + 1 + t, v);
-  }
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const uint32_t v = ((k < 8 ? e.hlo : e.hhi) >> (4 * (k & 7))) & 15u;
-    const uint32_t t = __reduce_add_sync(seg, v);
-    if (ga && t) atomicAdd(ga + 1 + P.nThr + k, t);
-  }
+  uint32_t w[8];
+  widen_hist(e.hlo, e.hhi, w);
+  uint32_t c01 = (e.cnt & 0xFFu) | ((e.cnt & 0xFF00u) << 8);            // voxels | thr0 << 16
+  uint32_t c23 = ((e.cnt >> 16) & 0xFFu) | ((e.cnt >> 24) << 16);        // thr1 | thr2 << 16
+  uint32_t kmin = e.kmin, kmax = e.kmax;
   double s = e.s, s2 = e.s2;
-  seg_sum2(s, s2, lane, end);
-  if (gf) { atomicAdd(gf, s); atomicAdd(gf + 1, s2); }
-  const uint32_t kmin = __reduce_max_sync(seg, e.kmin), kmax = __reduce_max_sync(seg, e.kmax);
-  if (gm) { if (kmin) atomicMax(gm + 0, kmin); if (kmax) atomicMax(gm + 1, kmax); }
+  SEG_REDUCE_BEGIN
+    SEG_ADD(c01) SEG_ADD(c23) SEG_ADD(s) SEG_ADD(s2)
+    SEG_ADD(w[0]) SEG_ADD(w[1]) SEG_ADD(w[2]) SEG_ADD(w[3]) SEG_ADD(w[4]) SEG_ADD(w[5]) SEG_ADD(w[6]) SEG_ADD(w[7])
+    SEG_MAX(kmin) SEG_MAX(kmax)
+  SEG_REDUCE_END
+  const uint32_t ea = e.a, eb = e.b;
   e.cnt = 0;
+  if (!head) return;
+  const long long g = edge_slot(P, ((unsigned long long)ea << 32) | eb);
+  if (g < 0) return;
+  uint32_t* ga = P.edgeAdd + (size_t)g * P.edge.nAdd;
+  uint32_t* gm = P.edgeMax + (size_t)g * P.edge.nMax;
+  double* gf = P.edgeF64 + (size_t)g * P.edge.nF64;
+  atomicAdd(ga, c01 & 0xFFFFu);
+  if (P.nThr > 0 && (c01 >> 16)) atomicAdd(ga + 1, c01 >> 16);  // type/feat.hxx:498
+  if (P.nThr > 1 && (c23 & 0xFFFFu)) atomicAdd(ga + 2, c23 & 0xFFFFu);
+  if (P.nThr > 2 && (c23 >> 16)) atomicAdd(ga + 3, c23 >> 16);
+  uint32_t* gh = ga + 1 + P.nThr;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (w[j] & 0xFFFFu) atomicAdd(gh + 2 * j, w[j] & 0xFFFFu);
+    if (w[j] >> 16) atomicAdd(gh + 2 * j + 1, w[j] >> 16);
+  }
+  atomicAdd(gf, s); atomicAdd(gf + 1, s2);
+  if (kmin) atomicMax(gm + 0, kmin);
+  if (kmax) atomicMax(gm + 1, kmax);
 }
 
 }  // namespace
