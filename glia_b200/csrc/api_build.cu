@@ -76,7 +76,9 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
   size_t owned = (size_t)P.X * P.Y * (size_t)(P.zEnd - P.zBegin);
   uint64_t cap = prm.edge_capacity;
   if (cap == 0) {
-    uint64_t est = std::min<uint64_t>(owned, 16ull * LB);
+    // directed boundaries per region: ~5.7 in 2D, ~13.8 in 3D (synthetic EM); the table is
+    // grown x4 and the pass re-run if this guess is too small
+    uint64_t est = std::min<uint64_t>(owned, (P.ndim == 2 ? 8ull : 16ull) * LB);
     cap = pow2ceil(est + est / 2 + 1024);
   } else cap = pow2ceil(cap);
   const uint64_t capMax = pow2ceil(2 * (uint64_t)owned + 1024);

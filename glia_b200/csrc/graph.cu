@@ -140,6 +140,21 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
 using namespace glia;
 
 #define CK(expr) GLIA_CUDA_CHECK(h, expr)
+#include <chrono>
+#include <stdio.h>
+#include <stdlib.h>
+// GLIA_B200_TRACE=1: host-side wall clock of each finalisation phase (stream synchronised) on stderr
+struct PhaseTrace {
+  bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
+  PhaseTrace(cudaStream_t s) : on(getenv("GLIA_B200_TRACE") != nullptr), st(s) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
+  void mark(const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[glia trace] %-28s %8.1f us\n", what, std::chrono::duration<double, std::micro>(t1 - t0).count());
+    t0 = t1;
+  }
+};
 static inline unsigned nblk(long long n, int per) { return (unsigned)((n + per - 1) / per); }
 
 int glia_finalize_regions(glia_handle* h);
@@ -155,6 +170,7 @@ int glia_finalize_graph(glia_handle* h) {
 // regions: presence -> dense index in ascending label order, compact records
 int glia_finalize_regions(glia_handle* h) {
   cudaStream_t st = h->stream;
+  PhaseTrace tr(st);
   const VoxParams& P = h->vp;
   const uint32_t LB = P.labelBound;
   // scalars: [0] edge counter (u64), [1] cand count (int as u64 slot), [2] err flag
@@ -181,6 +197,7 @@ int glia_finalize_regions(glia_handle* h) {
   CK(cudaStreamSynchronize(st));
   h->R = (long long)lastRank + lastFlag;
   const long long R = h->R;
+  tr.mark("regions: mark+scan+readback");
   CK(h->regLabel.ensure(4 * (size_t)(R + 1)));
   CK(h->cAdd.ensure(4 * (size_t)(R + 1) * P.reg.nAdd));
   CK(h->cMax.ensure(4 * (size_t)(R + 1) * P.reg.nMax));
@@ -191,6 +208,7 @@ int glia_finalize_regions(glia_handle* h) {
       h->cAdd.as<uint32_t>(), h->cMax.as<uint32_t>(), h->cF64.as<double>());
   h->launches++;
   CK(cudaGetLastError());
+  tr.mark("regions: gather");
   return GLIA_OK;
 }
 
@@ -202,6 +220,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   const uint32_t LB = P.labelBound;
   const long long R = h->R;
   size_t tmpBytes = 0;
+  PhaseTrace tr(st);
   CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));
   unsigned long long* dCounter = h->scalars.as<unsigned long long>();
   int* dNumSel = (int*)(dCounter + 1);
@@ -225,6 +244,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   if (E64 > 0x7fffffffull) { h->err = "more than 2^31 directed boundaries"; return GLIA_E_ARG; }
   h->E = (long long)E64;
   const long long E = h->E;
+  tr.mark("edges: compact+readback");
   CK(h->eKeySorted.ensure(8 * (size_t)(E + 1)));
   CK(h->eSlotSorted.ensure(4 * (size_t)(E + 1)));
   int rbits = 1; while ((1ll << rbits) < R + 1) ++rbits;
@@ -240,6 +260,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
                                        h->eSlotSorted.as<uint32_t>(), (int)E, 0, endBit, st));
     h->launches += 8;
   }
+  tr.mark("edges: radix sort");
   CK(h->ea.ensure(4 * (size_t)(E + 1)));
   CK(h->eb.ensure(4 * (size_t)(E + 1)));
   CK(h->rev.ensure(4 * (size_t)(E + 1)));
@@ -255,6 +276,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
         h->sF64.as<double>());
     h->launches++;
   }
+  tr.mark("edges: gather records");
   csr_rows_kernel<<<nblk(R + 1, 256), 256, 0, st>>>(h->ea.as<int>(), E, R, h->row.as<int>());
   h->launches++;
   CK(h->cand.ensure(4 * (size_t)(E + 1)));
@@ -275,6 +297,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
     CK(cudaStreamSynchronize(st));
     h->C = c;
   }
+  tr.mark("edges: csr+rev+select");
   // ---- per-region aggregate over its boundaries
   CK(h->bAggAdd.ensure(4 * (size_t)(R + 1) * P.edge.nAdd));
   CK(h->bAggMax.ensure(4 * (size_t)(R + 1) * (P.edge.nMax + 1)));
@@ -287,5 +310,6 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
     h->launches++;
   }
   CK(cudaGetLastError());
+  tr.mark("edges: boundary aggregate");
   return GLIA_OK;
 }

@@ -77,19 +77,29 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
     srow[c * ldRow + f] = X[c0 * D + i];
   }
   __syncthreads();
-  const int cand = threadIdx.x >> 2, slice = threadIdx.x & 3;
+  // v3 mapping: a warp = 32 candidates walking the SAME trees (lane = candidate), the 8 warps of
+  // the CTA = 2 candidate halves x 4 tree slices.  The upper levels of a tree are then one or two
+  // 32-byte sectors per warp-level fetch instead of 4 trees x 8 candidates worth of sectors
+  // (v2 mapped 4 lanes to one candidate; L1 wavefronts were the limiter, profiles/r1_v3_ncu_c4s.txt).
+  __shared__ int svote[RF_CPB];
+  if (threadIdx.x < RF_CPB) svote[threadIdx.x] = 0;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cand = (warp & 1) * 32 + lane, slice = warp >> 1;
   int hits = 0;
   if (cand < ncand) {
     const double* x = srow + cand * ldRow;
     int t = slice;
-    for (; t + 4 < ntree; t += 8) {  // two trees in flight
-      int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4);
-      RfNode na = nodes[ka], nb = nodes[kb];
-      while (na.feat >= 0 || nb.feat >= 0) {
+    for (; t + 12 < ntree; t += 16) {  // four trees in flight
+      int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4), kc = __ldg(treeOff + t + 8), kd = __ldg(treeOff + t + 12);
+      RfNode na = nodes[ka], nb = nodes[kb], nc = nodes[kc], nd = nodes[kd];
+      while (na.feat >= 0 || nb.feat >= 0 || nc.feat >= 0 || nd.feat >= 0) {
         if (na.feat >= 0) { ka = na.left + (x[na.feat] <= na.thr ? 0 : 1); na = nodes[ka]; }
         if (nb.feat >= 0) { kb = nb.left + (x[nb.feat] <= nb.thr ? 0 : 1); nb = nodes[kb]; }
+        if (nc.feat >= 0) { kc = nc.left + (x[nc.feat] <= nc.thr ? 0 : 1); nc = nodes[kc]; }
+        if (nd.feat >= 0) { kd = nd.left + (x[nd.feat] <= nd.thr ? 0 : 1); nd = nodes[kd]; }
       }
-      hits += (na.left == labelIdx) + (nb.left == labelIdx);
+      hits += (na.left == labelIdx) + (nb.left == labelIdx) + (nc.left == labelIdx) + (nd.left == labelIdx);
     }
     for (; t < ntree; t += 4) {
       int k = __ldg(treeOff + t);
@@ -97,10 +107,10 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
       while (nd.feat >= 0) { k = nd.left + (x[nd.feat] <= nd.thr ? 0 : 1); nd = nodes[k]; }
       hits += (nd.left == labelIdx);
     }
+    atomicAdd(&svote[cand], hits);
   }
-  hits += __shfl_xor_sync(0xffffffffu, hits, 1);
-  hits += __shfl_xor_sync(0xffffffffu, hits, 2);
-  if (cand < ncand && slice == 0) prob[c0 + cand] = (double)hits / (double)ntree;
+  __syncthreads();
+  if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)ntree;
 }
 
 }  // namespace glia
