@@ -57,7 +57,7 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_launch_count", "glia_b200_build_partial", "glia_b200_raw_region_tables",
            "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
            "glia_b200_import_edges", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
-           "glia_b200_synth_voronoi_slab"]
+           "glia_b200_synth_voronoi_slab", "glia_b200_set_image"]
 
 
 def lib():
@@ -108,6 +108,7 @@ def lib():
                                               C.POINTER(C.c_uint64)]
         L.glia_b200_synth_voronoi_slab.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_int, C.c_int, vp, vp,
                                                    vp, C.POINTER(C.c_uint64)]
+        L.glia_b200_set_image.argtypes = [vp, C.c_int, C.c_int, vp]
         _lib = L
     return _lib
 
@@ -262,6 +263,13 @@ class MergeTreeBuilder:
             self.close()
         except Exception:
             pass
+
+    def set_image(self, kind, i, data):
+        """Re-point image i of kind 0 (rimg) / 1 (rlimg) / 2 (bimg) at another buffer of the same extent."""
+        if not self.device_pointers:
+            data = np.ascontiguousarray(data, np.float32)
+            self._keep.append(data)
+        self._check(lib().glia_b200_set_image(self.h, kind, i, _addr(data)))
 
     def build(self, labels, pb, mask=None):
         if not self.device_pointers:

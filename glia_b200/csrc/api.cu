@@ -144,8 +144,21 @@ extern "C" void glia_b200_destroy(glia_handle* h) {
   for (auto b : bufs) b->release();
   for (auto& b : h->inImg) b.release();
   for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);
+  if (h->copyStream) { for (int i = 0; i < 4; ++i) cudaEventDestroy(h->evCopy[i]); cudaStreamDestroy(h->copyStream); }
   if (h->ownStream) cudaStreamDestroy(h->stream);
   delete h;
+}
+
+// Re-points one configured image at a new buffer of the same extent (a handle is reused for a
+// stream of slices/volumes: only the data changes, the histogram specs stay).
+extern "C" int glia_b200_set_image(glia_handle* h, int kind, int i, const float* data) {
+  if (!h || !data || i < 0) return GLIA_E_ARG;
+  glia_params& p = h->prm;
+  if (kind == 0 && i < p.n_rimg) p.rimg[i].data = data;
+  else if (kind == 1 && i < p.n_rlimg) p.rlimg[i].data = data;
+  else if (kind == 2 && i < p.n_bimg) p.bimg[i].data = data;
+  else return GLIA_E_ARG;
+  return GLIA_OK;
 }
 
 extern "C" const char* glia_b200_last_error(const glia_handle* h) { return h ? h->err.c_str() : "null handle"; }

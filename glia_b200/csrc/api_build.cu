@@ -41,8 +41,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
     if (prm.device_pointers) { *out = src; return GLIA_OK; }
     for (auto& s : staged) if (s.first == src) { *out = s.second; return GLIA_OK; }
     CK(buf.ensure(bytes));
-    CK(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, st));
-    staged.push_back({src, buf.p});
+    staged.push_back({src, buf.p});  // copied below, in z-chunks that overlap the voxel pass
     *out = buf.p;
     return GLIA_OK;
   };
@@ -57,6 +56,31 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
   for (int i = 0; i < prm.n_rlimg; ++i, ++ch) { if ((s = dev_of(prm.rlimg[i].data, 4 * n, h->inImg[nextImg++], &d))) return s; h->vc.reg[ch].data = (const float*)d; }
   for (int i = 0; i < prm.n_bimg; ++i) { if ((s = dev_of(prm.bimg[i].data, 4 * n, h->inImg[nextImg++], &d))) return s; h->vc.edge[i].data = (const float*)d; }
 
+  // Host inputs: the upload is cut into z-chunks on a copy stream; the voxel pass of chunk k starts
+  // when chunks <= k+1 have arrived (it reads one plane beyond its own), so PCIe and SMs overlap.
+  const size_t plane = (size_t)P.X * P.Y;
+  int nChunks = 1;
+  if (!staged.empty() && prm.label_bound != 0 && 4 * n >= (16u << 20) && P.zEnd - P.zBegin >= 64) nChunks = 4;
+  int zCut[5];
+  for (int k = 0; k <= nChunks; ++k) zCut[k] = P.zBegin + (int)(((long long)(P.zEnd - P.zBegin) * k) / nChunks);
+  if (!staged.empty()) {
+    if (nChunks == 1) {
+      for (auto& c : staged) CK(cudaMemcpyAsync((void*)c.second, c.first, 4 * n, cudaMemcpyHostToDevice, st));
+    } else {
+      if (!h->copyStream) {
+        CK(cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
+        for (int k = 0; k < 4; ++k) CK(cudaEventCreateWithFlags(&h->evCopy[k], cudaEventDisableTiming));
+      }
+      for (int k = 0; k < nChunks; ++k) {
+        const size_t p0 = k == 0 ? 0 : (size_t)(zCut[k] - P.zBuf0);
+        const size_t p1 = k == nChunks - 1 ? (size_t)P.zBufN : (size_t)(zCut[k + 1] - P.zBuf0);
+        for (auto& c : staged)
+          CK(cudaMemcpyAsync((char*)c.second + 4 * plane * p0, (const char*)c.first + 4 * plane * p0,
+                             4 * plane * (p1 - p0), cudaMemcpyHostToDevice, h->copyStream));
+        CK(cudaEventRecord(h->evCopy[k], h->copyStream));
+      }
+    }
+  }
   CK(cudaEventRecord(h->ev[0], st));
   CK(h->scalars.ensure(64));
   // ---- label bound
@@ -144,12 +168,23 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.edgeCap = P.edgeCap; F.edgeKeys = P.edgeKeys; F.edgeAdd = P.edgeAdd; F.edgeMax = P.edgeMax; F.edgeF64 = P.edgeF64;
       F.overflow = P.overflow;
       F.regSlots = 128; F.edgeSlots = 512;
-      if (useRuns) CK(launch_voxel_pass_runs(F, st)); else CK(launch_voxel_pass_fast(F, st));
+      for (int k = 0; k < nChunks; ++k) {
+        if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));
+        F.zBegin = zCut[k]; F.zEnd = zCut[k + 1];
+        F.tilesZ = (F.zEnd - F.zBegin + F.TZ - 1) / F.TZ;
+        if (useRuns) CK(launch_voxel_pass_runs(F, st)); else CK(launch_voxel_pass_fast(F, st));
+      }
     } else {
-      CK(launch_voxel_pass_generic(P, h->vc, st));
+      for (int k = 0; k < nChunks; ++k) {
+        if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));
+        VoxParams Pk = P;
+        Pk.zBegin = zCut[k]; Pk.zEnd = zCut[k + 1];
+        Pk.tilesZ = (Pk.zEnd - Pk.zBegin + Pk.TZ - 1) / Pk.TZ;
+        CK(launch_voxel_pass_generic(Pk, h->vc, st));
+      }
     }
   }
-  h->launches++;
+  h->launches += nChunks;
   CK(cudaEventRecord(h->ev[1], st));
   int ovf = 0;
   CK(cudaMemcpyAsync(&ovf, P.overflow, 4, cudaMemcpyDeviceToHost, st));

@@ -58,6 +58,8 @@ struct glia_handle {
   cudaStream_t stream = nullptr;
   bool ownStream = false;
   cudaEvent_t ev[8];
+  cudaStream_t copyStream = nullptr;  // chunked upload of host inputs (api_build.cu)
+  cudaEvent_t evCopy[4];
   double ms[5] = {-1, -1, -1, -1, -1};
   long long launches = 0;
   bool built = false;

@@ -88,6 +88,10 @@ typedef struct glia_rf glia_rf;
 GLIA_API int glia_b200_create(const glia_params* p, glia_handle** out);
 GLIA_API void glia_b200_destroy(glia_handle* h);
 GLIA_API const char* glia_b200_last_error(const glia_handle* h);
+/* Re-point a configured image (kind 0: rimg, 1: rlimg, 2: bimg; index i) at another buffer of the same
+ * extent before the next glia_b200_build: one handle serves a stream of slices / volumes, as the
+ * reference's per-image process loop does (gadget/python/script_util.py:6-23). */
+GLIA_API int glia_b200_set_image(glia_handle* h, int kind, int i, const float* data);
 
 /* RAG + base statistics.  labels/mask: uint32 volumes (mask may be NULL); pb: float32. */
 GLIA_API int glia_b200_build(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);

@@ -297,3 +297,46 @@ def test_generic_and_fast_voxel_kernels_agree(monkeypatch):
     monkeypatch.delenv("GLIA_B200_FORCE_GENERIC")
     for g in (g1, g2):
         _compare_graph(o, g, co)
+
+
+def _same_graph(g1, g2):
+    assert (g1.R, g1.E, g1.Cn) == (g2.R, g2.E, g2.Cn)
+    r1, r2 = g1.regions(), g2.regions()
+    for k in r1:
+        assert np.array_equal(r1[k], r2[k]), k
+    e1, e2 = g1.edges(), g2.edges()
+    for k in e1:
+        assert np.array_equal(e1[k], e2[k]), k
+    for f in ("region_stats", "edge_stats"):
+        s1, s2 = getattr(g1, f)(0), getattr(g2, f)(0)
+        for k in s1:
+            assert np.array_equal(s1[k], s2[k]), (f, k)
+
+
+@pytest.mark.parametrize("shape,cell,masked", [((2080, 2048), 13, False), ((72, 250, 260), 9, False),
+                                               ((2051, 2048), 17, True)])
+def test_chunked_upload_equals_single_copy(shape, cell, masked):
+    """Host inputs >= 16 MB with a known label bound are uploaded in z-chunks that overlap the voxel
+    pass (api_build.cu); the result must equal the single-copy path (label_bound = 0 scans the labels
+    first, which disables chunking) bit for bit, for the fast and the generic (mask) kernels."""
+    lab, pb = synth.voronoi_volume(shape, cell, seed=21)
+    mask = (np.random.RandomState(1).rand(*shape) > 0.02).astype(np.uint32) if masked else None
+    cfg = api.FeatureConfig(rimgs=[(pb, 16, 0.0, 1.0)], bimgs=[(pb, 16, 0.0, 1.0)])
+    g1 = api.MergeTreeBuilder(shape, cfg).build(lab, pb, mask)
+    g2 = api.MergeTreeBuilder(shape, cfg, label_bound=int(lab.max()) + 1).build(lab, pb, mask)
+    _same_graph(g1, g2)
+    k1, rows1 = g1.init_candidates()
+    k2, rows2 = g2.init_candidates()
+    assert np.array_equal(k1, k2) and np.array_equal(rows1, rows2)
+
+
+def test_set_image_rebinds_inputs():
+    """One handle reused for a stream of slices (glia_b200_set_image) == a fresh handle per slice."""
+    shape = (96, 128)
+    la, pa = synth.voronoi_volume(shape, 9, seed=1)
+    lb_, pb_ = synth.voronoi_volume(shape, 9, seed=2)
+    cfg = lambda p: api.FeatureConfig(rimgs=[(p, 16, 0.0, 1.0)], bimgs=[(p, 16, 0.0, 1.0)])
+    g = api.MergeTreeBuilder(shape, cfg(pa)).build(la, pa)
+    g.set_image(0, 0, pb_); g.set_image(2, 0, pb_)
+    g.build(lb_, pb_)
+    _same_graph(g, api.MergeTreeBuilder(shape, cfg(pb_)).build(lb_, pb_))
