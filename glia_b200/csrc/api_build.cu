@@ -9,6 +9,7 @@
 namespace glia {
 cudaError_t launch_voxel_pass_fast(const FastParams& P, cudaStream_t st);
 cudaError_t launch_voxel_pass_runs(const FastParams& P, cudaStream_t st);
+cudaError_t launch_voxel_pass_rq(const FastParams& P, cudaStream_t st);
 cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
@@ -147,6 +148,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       // voxel_runs.cu: parity-green but slower, profiles/r1_v4_notes.txt); default is v3
       const char* vsel = getenv("GLIA_B200_VOXEL");
       const bool useRuns = vsel && vsel[0] == 'r';
+      const bool useRq = vsel && vsel[0] == 'q';  // GLIA_B200_VOXEL=queue: v5 run queue (voxel_rq.cu), experimental
       const char* tzs = getenv("GLIA_B200_TZ");
       F.TZ = tzs ? atoi(tzs) : (useRuns ? (P.ndim == 3 ? 64 : 32) : 32);
       if (F.TZ < 1) F.TZ = 32;
@@ -172,7 +174,9 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
         if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));
         F.zBegin = zCut[k]; F.zEnd = zCut[k + 1];
         F.tilesZ = (F.zEnd - F.zBegin + F.TZ - 1) / F.TZ;
-        if (useRuns) CK(launch_voxel_pass_runs(F, st)); else CK(launch_voxel_pass_fast(F, st));
+        if (useRuns) CK(launch_voxel_pass_runs(F, st));
+        else if (useRq) CK(launch_voxel_pass_rq(F, st));
+        else CK(launch_voxel_pass_fast(F, st));
       }
     } else {
       for (int k = 0; k < nChunks; ++k) {
