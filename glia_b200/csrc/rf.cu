@@ -113,6 +113,62 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
   if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)ntree;
 }
 
+
+// v4: 8-byte nodes {float(threshold), left << 8 | feature} and float rows in shared memory.  Rounding to
+// float (round-to-nearest, monotone) keeps the order: f(x) < f(t) => x < t and f(x) > f(t) => x > t, so
+// the float compare decides every split except when both round to the same float (ties, or values within
+// one float ulp); only then the exact doubles (row in global memory, threshold side array) are compared,
+// which keeps the votes bit-exact.  Half the node bytes = half the L1/L2 sectors per warp-level fetch.
+struct __align__(8) RfNode8 { float thr; uint32_t w; };  // w = left << 8 | feature (255 = leaf, left = class)
+#define RF8_CPB 64
+#define RF8_STEP(n, k)                                                                         \
+  { const int f_ = (int)(n.w & 255u); const float xf_ = x[f_];                                  \
+    bool le_ = xf_ < n.thr;                                                                     \
+    if (!(xf_ < n.thr) && !(xf_ > n.thr)) le_ = __ldg(xg + f_) <= __ldg(thr64 + k);             \
+    k = (int)(n.w >> 8) + (le_ ? 0 : 1); n = nodes[k]; }
+__global__ void __launch_bounds__(256)
+rf_score_f32_kernel(const RfNode8* __restrict__ nodes, const double* __restrict__ thr64,
+                    const int* __restrict__ treeOff, int ntree, int labelIdx,
+                    const double* __restrict__ X, size_t N, int D, int ldRow, double* __restrict__ prob) {
+  extern __shared__ __align__(16) float frow[];
+  __shared__ int svote[RF8_CPB];
+  const size_t c0 = (size_t)blockIdx.x * RF8_CPB;
+  const int ncand = (int)min((size_t)RF8_CPB, N - c0);
+  for (int i = threadIdx.x; i < ncand * D; i += blockDim.x) {
+    int c = i / D, f = i - c * D;
+    frow[c * ldRow + f] = (float)X[c0 * D + i];
+  }
+  if (threadIdx.x < RF8_CPB) svote[threadIdx.x] = 0;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cand = (warp & 1) * 32 + lane, slice = warp >> 1;  // warp = 32 candidates on the same trees
+  if (cand < ncand) {
+    const float* x = frow + cand * ldRow;
+    const double* xg = X + (c0 + cand) * (size_t)D;
+    int hits = 0, t = slice;
+    for (; t + 12 < ntree; t += 16) {  // four trees in flight
+      int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4), kc = __ldg(treeOff + t + 8), kd = __ldg(treeOff + t + 12);
+      RfNode8 na = nodes[ka], nb = nodes[kb], nc = nodes[kc], nd = nodes[kd];
+      while ((na.w & 255u) != 255u || (nb.w & 255u) != 255u || (nc.w & 255u) != 255u || (nd.w & 255u) != 255u) {
+        if ((na.w & 255u) != 255u) RF8_STEP(na, ka)
+        if ((nb.w & 255u) != 255u) RF8_STEP(nb, kb)
+        if ((nc.w & 255u) != 255u) RF8_STEP(nc, kc)
+        if ((nd.w & 255u) != 255u) RF8_STEP(nd, kd)
+      }
+      hits += ((int)(na.w >> 8) == labelIdx) + ((int)(nb.w >> 8) == labelIdx) + ((int)(nc.w >> 8) == labelIdx) + ((int)(nd.w >> 8) == labelIdx);
+    }
+    for (; t < ntree; t += 4) {
+      int k = __ldg(treeOff + t);
+      RfNode8 n = nodes[k];
+      while ((n.w & 255u) != 255u) RF8_STEP(n, k)
+      hits += ((int)(n.w >> 8) == labelIdx);
+    }
+    atomicAdd(&svote[cand], hits);
+  }
+  __syncthreads();
+  if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)ntree;
+}
+
 }  // namespace glia
 
 using namespace glia;
@@ -160,6 +216,21 @@ static int rf_build_device(glia_rf* m) {
   if (cudaMalloc((void**)&m->d_treeOff, 4 * treeOff.size()) != cudaSuccess) return GLIA_E_CUDA;
   if (cudaMemcpy(m->d_nodes, nodes.data(), sizeof(RfNode) * nodes.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
   if (cudaMemcpy(m->d_treeOff, treeOff.data(), 4 * treeOff.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+  // 8-byte nodes + exact thresholds for rf_score_f32_kernel (features < 255, node ids < 2^24)
+  if (m->mdim <= 254 && nodes.size() < (1u << 24)) {
+    std::vector<RfNode8> n8(nodes.size());
+    std::vector<double> thr(nodes.size());
+    for (size_t i = 0; i < nodes.size(); ++i) {
+      thr[i] = nodes[i].thr;
+      n8[i].thr = (float)nodes[i].thr;
+      n8[i].w = nodes[i].feat >= 0 ? ((uint32_t)nodes[i].left << 8) | (uint32_t)nodes[i].feat
+                                   : ((uint32_t)nodes[i].left << 8) | 255u;
+    }
+    if (cudaMalloc(&m->d_nodes8, sizeof(RfNode8) * n8.size()) != cudaSuccess) return GLIA_E_CUDA;
+    if (cudaMalloc((void**)&m->d_thr, 8 * thr.size()) != cudaSuccess) return GLIA_E_CUDA;
+    if (cudaMemcpy(m->d_nodes8, n8.data(), sizeof(RfNode8) * n8.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+    if (cudaMemcpy(m->d_thr, thr.data(), 8 * thr.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+  }
   return GLIA_OK;
 }
 
@@ -280,6 +351,8 @@ extern "C" void glia_b200_rf_destroy(glia_rf* m) {
   if (!m) return;
   if (m->d_nodes) cudaFree(m->d_nodes);
   if (m->d_treeOff) cudaFree(m->d_treeOff);
+  if (m->d_nodes8) cudaFree(m->d_nodes8);
+  if (m->d_thr) cudaFree(m->d_thr);
   delete m;
 }
 
@@ -305,7 +378,15 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
   if (dVotes)
     rf_score_kernel<true><<<blocks, 128, 128 * m->nclass * sizeof(int), st>>>(
         (const RfNode*)m->d_nodes, m->d_treeOff, m->ntree, m->nclass, labelIdx, dX, N, D, dVotes, dProb);
-  else {
+  else if (m->d_nodes8 && getenv("GLIA_B200_RF_F32") &&  // experiment: exact, but 23 % slower than the 16-byte kernel on C5
+             sizeof(float) * (size_t)RF8_CPB * (D | 1) <= 200 * 1024) {
+    const int ldRow = D | 1;  // odd stride: the 32 candidates of a warp read one feature from 32 banks
+    const size_t smem = sizeof(float) * (size_t)RF8_CPB * ldRow;
+    static bool attr8 = false;
+    if (!attr8) { cudaFuncSetAttribute(rf_score_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr8 = true; }
+    rf_score_f32_kernel<<<(unsigned)((N + RF8_CPB - 1) / RF8_CPB), 256, smem, st>>>(
+        (const RfNode8*)m->d_nodes8, m->d_thr, m->d_treeOff, m->ntree, labelIdx, dX, N, D, ldRow, dProb);
+  } else {
     int ldRow = D | 1;  // odd stride (in doubles): rows start on different banks
     size_t smem = sizeof(double) * (size_t)RF_CPB * ldRow;
     if (smem <= 200 * 1024) {
