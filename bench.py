@@ -32,6 +32,11 @@ RF_SWEEP = dict(n=10_000_000, d=50, ntree=255, desc="RF scoring sweep: 255-tree 
                 "with 50-dim bc features (BASELINE.json configs[4])")
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE voxel_pass_fast launch, from the committed
+# `ncu --set full` captures (profiles/r1_final_ncu_c2.txt, profiles/r1_v3_ncu_c4s.txt); None = not captured
+VOXEL_PASS_TRAFFIC = {"c2": 298.95e6 + 81.93e6, "c4s": 1.884e9 + 0.378e9}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -377,7 +382,7 @@ def main():
             "stage_ms": {"table_init": kern_ms[4], "voxel_pass": kern_ms[0], "graph": kern_ms[1], "featurize": kern_ms[2],
                          "rf_score": kern_ms[3]},
             "roofline": {"bound": "hbm", "kernel": "voxel_pass_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": VOXEL_PASS_TRAFFIC.get(args.workload), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes},
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
     if not args.no_cpu_baseline and world == 1:
