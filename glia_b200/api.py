@@ -57,7 +57,7 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_launch_count", "glia_b200_build_partial", "glia_b200_raw_region_tables",
            "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
            "glia_b200_import_edges", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
-           "glia_b200_synth_voronoi_slab", "glia_b200_set_image"]
+           "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble"]
 
 
 def lib():
@@ -109,6 +109,7 @@ def lib():
         L.glia_b200_synth_voronoi_slab.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_int, C.c_int, vp, vp,
                                                    vp, C.POINTER(C.c_uint64)]
         L.glia_b200_set_image.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.glia_b200_rf_ensemble.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(vp)]
         _lib = L
     return _lib
 
@@ -168,6 +169,17 @@ class Forest:
                                             C.byref(h))
         if st:
             raise GliaError(st)
+        return cls(h)
+
+    @classmethod
+    def ensemble(cls, forests, dim0, dim1, threshold):
+        """alg::EnsembleRandomForest + ThresholdModelDistributor (alg/rf.hxx:63-98, type/function.hxx:71-85):
+        model 0 if x[dim1] < threshold, else 1 if x[dim0] < threshold, else 2."""
+        arr = (C.c_void_p * len(forests))(*[f.h for f in forests])
+        h = C.c_void_p()
+        st = lib().glia_b200_rf_ensemble(arr, len(forests), dim0, dim1, threshold, C.byref(h))
+        if st:
+            raise GliaError(st, "rf_ensemble")
         return cls(h)
 
     def predict(self, X, label=-1, want_votes=True):

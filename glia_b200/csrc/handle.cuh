@@ -39,6 +39,22 @@ struct FeatCfg {
 
 }  // namespace glia
 
+// alg::EnsembleRandomForest + opt::ThresholdModelDistributor (alg/rf.hxx:63-98, type/function.hxx:71-85):
+// a row picks model 0 if x[dim1] < thr, else 1 if x[dim0] < thr, else 2; the trees of all models
+// are concatenated on the device and a candidate walks the tree range [tb[m], te[m]) of its model.
+struct RfDist {
+  int n;            // 1 = plain forest
+  int dim0, dim1;
+  double thr;
+  int tb[3], te[3];
+  __host__ __device__ int pick(const double* x) const {
+    if (n <= 1) return 0;
+    if (x[dim1] < thr) return 0;
+    if (x[dim0] < thr) return 1;
+    return 2;
+  }
+};
+
 struct glia_rf {
   int device = 0;
   int ntree = 0, nrnodes = 0, nclass = 0, mdim = 0;
@@ -51,6 +67,7 @@ struct glia_rf {
   void* d_nodes8 = nullptr;      // 8-byte nodes {float threshold, left << 8 | feature} (rf.cu v4)
   double* d_thr = nullptr;       // exact thresholds, same indexing as d_nodes8
   int maxDepth = 0;
+  RfDist dist = {1, 0, 0, 0.0, {0, 0, 0}, {0, 0, 0}};  // dist.te[0] = ntree for a plain forest
 };
 
 struct glia_handle {

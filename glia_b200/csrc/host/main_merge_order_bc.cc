@@ -10,20 +10,33 @@ int main(int argc, char** argv) {
   if (!a.parse(argc, argv) || a.has("help")) {
     std::cerr << "Usage: merge_order_bc --bct 1 --bcm MODEL -s SEG --pb PB [--rbi IMG --rbb BINS --rbl LO --rbu HI]...\n"
                  "       [--rli/--rlb/--rll/--rlu] [--ri/--rb/--rl/--ru] [--bi/--bb/--bl/--bu] [--bt T...] [-m MASK]\n"
-                 "       [-n 0|1] [-l 0|1] [--simpf 0|1] -o ORDER [--sal SAL] [-b BCFEAT] [--device N]\n"
+                 "       [--bcm M1 --bcm M2 --bcmd DIM0 DIM1 THR] [-n 0|1] [-l 0|1] [--simpf 0|1] -o ORDER [--sal SAL] [-b BCFEAT] [--device N]\n"
                  "Images: .npy, .mha, .mhd (raw).\n";
     return a.has("help") ? EXIT_SUCCESS : EXIT_FAILURE;
   }
   a.require("bct"); a.require("bcm"); a.require("mergeOrder");
   if (atoi(a.str("bct").c_str()) != 1) gh::perr("Error: only --bct 1 (random forest) is supported by this build");
-  if (a.strs("bcm").size() != 1) gh::perr("Error: ensemble models (--bcmd) are not supported by this build");
+  const std::vector<std::string> bcm = a.strs("bcm");
+  const std::vector<double> bcmd = a.nums("bcmd");
+  if (bcm.size() > 3) gh::perr("Error: at most three --bcm models");
+  if (bcm.size() > 1 && bcmd.size() != 3) gh::perr("Error: incorrect boundary classifier model distributor args...");  // main_merge_order_bc.cxx:103-104
   gh::HmtInputs in;
   gh::setup_inputs(a, in);
   gh::Handle H;
   gh::build_graph(in, H);
   glia_rf* rf = nullptr;
-  int st = glia_b200_rf_load(a.str("bcm").c_str(), in.prm.device, &rf);
-  if (st != GLIA_OK) gh::perr("Error: cannot read model file " + a.str("bcm"));
+  int st = GLIA_OK;
+  if (bcm.size() == 1) {
+    st = glia_b200_rf_load(bcm[0].c_str(), in.prm.device, &rf);
+    if (st != GLIA_OK) gh::perr("Error: cannot read model file " + bcm[0]);
+  } else {  // alg::EnsembleRandomForest, main_merge_order_bc.cxx:102-109
+    glia_rf* sub[3] = {nullptr, nullptr, nullptr};
+    for (size_t i = 0; i < bcm.size(); ++i)
+      if (glia_b200_rf_load(bcm[i].c_str(), in.prm.device, &sub[i]) != GLIA_OK) gh::perr("Error: cannot read model file " + bcm[i]);
+    st = glia_b200_rf_ensemble(sub, (int)bcm.size(), (int)bcmd[0], (int)bcmd[1], bcmd[2], &rf);
+    for (size_t i = 0; i < bcm.size(); ++i) glia_b200_rf_destroy(sub[i]);
+    if (st != GLIA_OK) gh::perr("Error: cannot combine the boundary classifier models");
+  }
   int64_t R = 0, E = 0, C = 0;
   H.check(glia_b200_counts(H.h, &R, &E, &C), "glia_b200_counts");
   const int dim = glia_b200_row_dim(H.h, 0);

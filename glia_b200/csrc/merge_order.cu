@@ -34,7 +34,7 @@ struct __align__(16) RfNode16 { double thr; int left; int feat; };  // == RfNode
 __global__ void __launch_bounds__(128)
 merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __restrict__ stage,
                    int stageWords, const RfNode16* __restrict__ nodes,
-                   const int* __restrict__ treeOff, int ntree, int labelIdx,
+                   const int* __restrict__ treeOff, const RfDist dist, int labelIdx,
                    double* __restrict__ rows, double* __restrict__ sal) {
   int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (w >= m) return;
@@ -58,7 +58,8 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
   }
   __syncwarp();
   int hits = 0;
-  for (int t = lane; t < ntree; t += 32) {
+  const int mdl = dist.pick(row), tb = dist.tb[mdl], ntree = dist.te[mdl] - tb;  // alg/rf.hxx:97-98
+  for (int t = tb + lane; t < tb + ntree; t += 32) {
     int k = treeOff[t];
     RfNode16 nd = nodes[k];
     while (nd.feat >= 0) {
@@ -352,7 +353,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     }
     CK(cudaMemcpyAsync(dStage, hStage, 4 * m * stageWords, cudaMemcpyHostToDevice, st));
     merge_batch_kernel<<<(unsigned)((m * 32 + 127) / 128), 128, 0, st>>>(
-        h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->ntree, li, dRows, dSal);
+        h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, dSal);
     h->launches++;
     CK(cudaMemcpyAsync(hSal, dSal, 8 * m, cudaMemcpyDeviceToHost, st));
     if (rows) CK(cudaMemcpyAsync(hRows, dRows, 8 * m * dim, cudaMemcpyDeviceToHost, st));

@@ -16,6 +16,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <queue>
 #include "handle.cuh"
 
@@ -30,7 +31,7 @@ struct __align__(16) RfNode {
 // votesOut: [N][nclass] or null.  Dynamic smem: blockDim.x * nclass ints when votesOut.
 template <bool WANT_VOTES>
 __global__ void __launch_bounds__(128)
-rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, int ntree,
+rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, const RfDist dist,
                 int nclass, int labelIdx, const double* __restrict__ X, size_t N, int D,
                 int* __restrict__ votesOut, double* __restrict__ prob) {
   extern __shared__ int svotes[];
@@ -41,7 +42,8 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
     for (int c = 0; c < nclass; ++c) svotes[c * blockDim.x + threadIdx.x] = 0;
   int hits = 0;
   if (active) {
-    for (int t = 0; t < ntree; ++t) {
+    const int mdl = dist.pick(x), tb = dist.tb[mdl], ntree = dist.te[mdl] - tb;
+    for (int t = tb; t < tb + ntree; ++t) {
       int k = __ldg(treeOff + t);
       RfNode nd = nodes[k];
       while (nd.feat >= 0) {
@@ -65,7 +67,7 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
 // are 32-byte aligned so that one L2 sector serves either outcome of a split.
 #define RF_CPB 64
 __global__ void __launch_bounds__(256)
-rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, int ntree,
+rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, const RfDist dist,
                      int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
                      double* __restrict__ prob) {
   extern __shared__ __align__(16) double srow[];
@@ -82,6 +84,7 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
   // 32-byte sectors per warp-level fetch instead of 4 trees x 8 candidates worth of sectors
   // (v2 mapped 4 lanes to one candidate; L1 wavefronts were the limiter, profiles/r1_v3_ncu_c4s.txt).
   __shared__ int svote[RF_CPB];
+  __shared__ int sntree[RF_CPB];
   if (threadIdx.x < RF_CPB) svote[threadIdx.x] = 0;
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -89,7 +92,9 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
   int hits = 0;
   if (cand < ncand) {
     const double* x = srow + cand * ldRow;
-    int t = slice;
+    const int mdl = dist.pick(x), ntree = dist.te[mdl];
+    if (slice == 0) sntree[cand] = ntree - dist.tb[mdl];
+    int t = dist.tb[mdl] + slice;
     for (; t + 12 < ntree; t += 16) {  // four trees in flight
       int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4), kc = __ldg(treeOff + t + 8), kd = __ldg(treeOff + t + 12);
       RfNode na = nodes[ka], nb = nodes[kb], nc = nodes[kc], nd = nodes[kd];
@@ -110,7 +115,7 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
     atomicAdd(&svote[cand], hits);
   }
   __syncthreads();
-  if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)ntree;
+  if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)sntree[threadIdx.x];
 }
 
 
@@ -211,6 +216,7 @@ static int rf_build_device(glia_rf* m) {
   }
   treeOff[m->ntree] = (int)nodes.size();
   m->totalNodes = (int)nodes.size();
+  if (m->dist.n <= 1) { m->dist.n = 1; m->dist.tb[0] = 0; m->dist.te[0] = m->ntree; }
   if (cudaSetDevice(m->device) != cudaSuccess) return GLIA_E_CUDA;
   if (cudaMalloc(&m->d_nodes, sizeof(RfNode) * nodes.size()) != cudaSuccess) return GLIA_E_CUDA;
   if (cudaMalloc((void**)&m->d_treeOff, 4 * treeOff.size()) != cudaSuccess) return GLIA_E_CUDA;
@@ -252,6 +258,48 @@ extern "C" int glia_b200_rf_from_arrays(int ntree, int nrnodes, int nclass, int 
   m->nodeclass.assign(nodeclass, nodeclass + n);
   if (ndbigtree) m->ndbigtree.assign(ndbigtree, ndbigtree + ntree);
   m->orig_labels.assign(orig_labels, orig_labels + nclass);
+  int st = rf_build_device(m);
+  if (st != GLIA_OK) { glia_b200_rf_destroy(m); return st; }
+  *out = m;
+  return GLIA_OK;
+}
+
+// alg::EnsembleRandomForest (alg/rf.hxx:63-98) with opt::ThresholdModelDistributor
+// (type/function.hxx:71-85; --bcm m0 m1 m2 --bcmd dim0 dim1 thr, hmt/main_merge_order_bc.cxx:103-109):
+// the models' trees are concatenated into one device forest, a row walks the range of its model.
+extern "C" int glia_b200_rf_ensemble(const glia_rf* const* models, int n, int dim0, int dim1,
+                                     double threshold, glia_rf** out) {
+  if (!models || !out || n < 1 || n > 3 || dim0 < 0 || dim1 < 0) return GLIA_E_ARG;
+  for (int i = 0; i < n; ++i) {
+    if (!models[i] || models[i]->dist.n != 1 || models[i]->device != models[0]->device ||
+        models[i]->nclass != models[0]->nclass || models[i]->orig_labels != models[0]->orig_labels)
+      return GLIA_E_ARG;  // one label table for all models
+  }
+  glia_rf* m = new glia_rf();
+  m->device = models[0]->device; m->nclass = models[0]->nclass; m->orig_labels = models[0]->orig_labels;
+  int nr = 0, nt = 0;
+  for (int i = 0; i < n; ++i) { nr = std::max(nr, models[i]->nrnodes); nt += models[i]->ntree; m->mdim = std::max(m->mdim, models[i]->mdim); }
+  m->mdim = std::max(m->mdim, std::max(dim0, dim1) + 1);
+  m->nrnodes = nr; m->ntree = nt;
+  const size_t tot = (size_t)nt * nr;
+  m->treemap.assign(2 * tot, 0); m->nodestatus.assign(tot, 0); m->xbestsplit.assign(tot, 0.0);
+  m->bestvar.assign(tot, 0); m->nodeclass.assign(tot, 0);
+  m->dist.n = n; m->dist.dim0 = dim0; m->dist.dim1 = dim1; m->dist.thr = threshold;
+  int t0 = 0;
+  for (int i = 0; i < n; ++i) {
+    const glia_rf* s = models[i];
+    for (int t = 0; t < s->ntree; ++t) {
+      const size_t so = (size_t)t * s->nrnodes, d = (size_t)(t0 + t) * nr;
+      for (int k = 0; k < s->nrnodes; ++k) {
+        m->treemap[2 * (d + k)] = s->treemap[2 * (so + k)]; m->treemap[2 * (d + k) + 1] = s->treemap[2 * (so + k) + 1];
+        m->nodestatus[d + k] = s->nodestatus[so + k]; m->xbestsplit[d + k] = s->xbestsplit[so + k];
+        m->bestvar[d + k] = s->bestvar[so + k]; m->nodeclass[d + k] = s->nodeclass[so + k];
+      }
+      // a tree shorter than the padded stride: its unused nodes are never reached (node 0 is the root)
+    }
+    m->dist.tb[i] = t0; t0 += s->ntree; m->dist.te[i] = t0;
+  }
+  for (int i = n; i < 3; ++i) { m->dist.tb[i] = m->dist.tb[n - 1]; m->dist.te[i] = m->dist.te[n - 1]; }
   int st = rf_build_device(m);
   if (st != GLIA_OK) { glia_b200_rf_destroy(m); return st; }
   *out = m;
@@ -377,8 +425,8 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
   unsigned blocks = (unsigned)((N + 127) / 128);
   if (dVotes)
     rf_score_kernel<true><<<blocks, 128, 128 * m->nclass * sizeof(int), st>>>(
-        (const RfNode*)m->d_nodes, m->d_treeOff, m->ntree, m->nclass, labelIdx, dX, N, D, dVotes, dProb);
-  else if (m->d_nodes8 && getenv("GLIA_B200_RF_F32") &&  // experiment: exact, but 23 % slower than the 16-byte kernel on C5
+        (const RfNode*)m->d_nodes, m->d_treeOff, m->dist, m->nclass, labelIdx, dX, N, D, dVotes, dProb);
+  else if (m->d_nodes8 && m->dist.n == 1 && getenv("GLIA_B200_RF_F32") &&  // experiment: exact, but 23 % slower than the 16-byte kernel on C5
              sizeof(float) * (size_t)RF8_CPB * (D | 1) <= 200 * 1024) {
     const int ldRow = D | 1;  // odd stride: the 32 candidates of a warp read one feature from 32 banks
     const size_t smem = sizeof(float) * (size_t)RF8_CPB * ldRow;
@@ -398,9 +446,9 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
         attr = true;
       }
       rf_score_smem_kernel<<<(unsigned)((N + RF_CPB - 1) / RF_CPB), 256, smem, st>>>(
-          (const RfNode*)m->d_nodes, m->d_treeOff, m->ntree, labelIdx, dX, N, D, ldRow, dProb);
+          (const RfNode*)m->d_nodes, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
     } else {
-      rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->ntree,
+      rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist,
                                                      m->nclass, labelIdx, dX, N, D, nullptr, dProb);
     }
   }

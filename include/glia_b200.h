@@ -130,7 +130,7 @@ GLIA_API int glia_b200_bc_feat(glia_handle* h, const uint32_t* order /*[n][3]*/,
 /* ---- multi-GPU: z-slab sharding (no counterpart in the reference, which is single-process;
  * preserves its results because every voxel is owned by exactly one slab).  One process and one
  * handle per GPU, created with z_begin/z_end/halo_* and a label_bound common to all ranks.  Call
- * order (glia_b200/parallel.py drives it over torch.distributed / NCCL):
+ * order (glia_b200/parallel.py drives it with NCCL collectives):
  *   build_partial -> all-reduce raw_region_tables (add: sum, max: unsigned max, f64: sum)
  *   -> finalize_regions -> edge_interest (all-reduce max over the byte mask)
  *   -> export_edges -> all-to-all of the per-destination record runs -> import_edges(clear_first=1)
@@ -156,6 +156,12 @@ GLIA_API int glia_b200_rf_from_arrays(int ntree, int nrnodes, int nclass, int md
                              const int* nodestatus, const double* xbestsplit, const int* bestvar,
                              const int* nodeclass, const int* ndbigtree, const int* orig_labels,
                              int device, glia_rf** out);
+/* alg::EnsembleRandomForest with opt::ThresholdModelDistributor (alg/rf.hxx:63-98,
+ * type/function.hxx:71-85; --bcm m0 m1 m2 --bcmd dim0 dim1 thr): a row x is scored by model 0 if
+ * x[dim1] < threshold, else by model 1 if x[dim0] < threshold, else by model 2.  n = 1..3 models on one
+ * device with identical class labels; the result is an independent forest (the inputs may be destroyed). */
+GLIA_API int glia_b200_rf_ensemble(const glia_rf* const* models, int n, int dim0, int dim1, double threshold,
+                                   glia_rf** out);
 GLIA_API void glia_b200_rf_destroy(glia_rf* m);
 GLIA_API int glia_b200_rf_info(const glia_rf* m, int* ntree, int* nrnodes, int* nclass, int* mdim);
 /* X [N][D] row-major doubles (x[m + i*mdim], ml/rf/rf.hxx:362-365).  votes [N][nclass] int

@@ -363,3 +363,54 @@ def test_rf_float_filter_is_exact_on_near_ties(monkeypatch):
     assert np.array_equal(po, pg3)
     vg, pg2 = grf.predict(X, want_votes=True)  # 16-byte double nodes
     assert np.array_equal(po, pg) and np.array_equal(po, pg2) and np.array_equal(vo, vg)
+
+
+def _ensemble_pick(x, dim0, dim1, thr):
+    """opt::ThresholdModelDistributor (type/function.hxx:71-85), restated for the checker."""
+    return 0 if x[dim1] < thr else (1 if x[dim0] < thr else 2)
+
+
+def test_rf_ensemble_matches_reference_rule():
+    """alg::EnsembleRandomForest (alg/rf.hxx:63-98): per-row model choice, then that model's votes."""
+    rng = np.random.default_rng(11)
+    d, n = 23, 5000
+    X = rng.random((n, d))
+    X[:200, 4] = 0.5; X[200:400, 9] = 0.5  # rows exactly on the distributor threshold (strict <)
+    fs = [synth.random_forest(nt, d, max_depth=9, seed=s, thr_pool=X[:300]) for nt, s in ((17, 1), (31, 2), (8, 3))]
+    ofs = [ol.OracleRF.from_arrays(f, d) for f in fs]
+    gfs = [api.Forest.from_arrays(f, d) for f in fs]
+    ens = api.Forest.ensemble(gfs, 4, 9, 0.5)
+    pick = np.array([_ensemble_pick(x, 4, 9, 0.5) for x in X])
+    assert set(pick) == {0, 1, 2}
+    votes = np.stack([o.predict(X)[0] for o in ofs]); probs = np.stack([o.predict(X)[1] for o in ofs])
+    vo, po = votes[pick, np.arange(n)], probs[pick, np.arange(n)]
+    vg, pg = ens.predict(X)
+    _, pg2 = ens.predict(X, want_votes=False)
+    assert np.array_equal(vo, vg) and np.array_equal(po, pg) and np.array_equal(po, pg2)
+    two = api.Forest.ensemble(gfs[:2], 4, 9, 0.5)  # index 2 does not exist: clamped to the last model
+    _, p2 = two.predict(X, want_votes=False)
+    assert np.array_equal(p2, probs[np.minimum(pick, 1), np.arange(n)])
+
+
+def test_merge_order_with_ensemble_matches_oracle():
+    """--bcm m0 m1 m2 --bcmd dim0 dim1 thr (hmt/main_merge_order_bc.cxx:102-109) through the greedy chain."""
+    shape = (26, 30)
+    lab, pb = synth.speckle_volume(shape, 40, seed=8)
+    co, cg = _cfg_pair(pb)
+    o = ol.Oracle(lab, pb, co)
+    g = api.MergeTreeBuilder(shape, cg).build(lab, pb)
+    _, rowo = o.init_candidates()
+    _, rowg = g.init_candidates()
+    cols = _exact_columns(rowo, rowg)
+    dim = o.row_dim()
+    fs = [synth.random_forest(7, dim, max_depth=4, seed=s, thr_pool=rowo, features=cols) for s in (1, 2, 3)]
+    ofs = [ol.OracleRF.from_arrays(f, dim) for f in fs]
+    d0, d1 = int(cols[0]), int(cols[1])
+    thr = float(np.median(rowo[:, d1]))
+    ens = api.Forest.ensemble([api.Forest.from_arrays(f, dim) for f in fs], d0, d1, thr)
+    fn = lambda x: float(ofs[_ensemble_pick(x, d0, d1, thr)].predict(x[None, :])[1][0])
+    ro = o.greedy(fn=fn)
+    rg = g.merge_order_bc(ens, want_rows=True)
+    assert np.array_equal(rg["order"], ro["order"]) and np.array_equal(rg["sal"], ro["sal"])
+    sal = g.score_candidates(ens)
+    assert np.array_equal(sal, np.array([fn(r) for r in rowg]))
