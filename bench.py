@@ -19,6 +19,29 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its version banner on
+# stdout when NCCL_DEBUG is VERSION or WARN), so file descriptor 1 points at stderr while the benchmark
+# runs and is restored by emit() for the result line.
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    global _STDOUT_FD
+    sys.stdout.flush()
+    if _STDOUT_FD is not None:
+        os.dup2(_STDOUT_FD, 1)
+        os.close(_STDOUT_FD)
+        _STDOUT_FD = None
+    print(json.dumps(line), flush=True)
+
 WORKLOADS = {
     # name: (shape in numpy order, cell, description)
     "c1": ((512, 512), 11, "2D 512x512, ~2.2k superpixels (BASELINE.json configs[0])"),
@@ -53,11 +76,18 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
+        self.t0 = self.t1 = None
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -66,7 +96,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def stop(self):
         if not self.proc:
@@ -79,7 +109,18 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        # samples inside the timed region; the sampler runs from before the warm-up steps (same load), so
+        # when the region is shorter than nvidia-smi's sampling period the closest warm-up samples are used
+        lines, window = self.lines, "timed region"
+        if self.t0 is not None and self.t1 is not None:
+            inside = [x for x in lines if self.t0 - 0.01 <= x[0] <= self.t1 + 0.03]
+            if len(inside) >= 2:
+                lines = inside
+            else:
+                lines = sorted(lines, key=lambda x: abs(x[0] - 0.5 * (self.t0 + self.t1)))[:5]
+                window = "timed region shorter than the sampling period: nearest samples (warm-up, same load)"
+        self.window = window
+        for _, ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 8:
                 continue
@@ -91,7 +132,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "window": getattr(self, "window", "")}
 
 
 def make_forest(api, synth, torch, dim, ndim, device):
@@ -190,11 +231,13 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.workload == "c5":
         import bench_modes
+        bench_modes.emit = emit
         return bench_modes.run_rf_sweep(args, rank, world, local_rank)
     shape, cell, desc = WORKLOADS[args.workload]
     nd = len(shape)
@@ -217,7 +260,7 @@ def main():
                 "cpu_baseline": {"value": r["mvox_s"], "unit": "Mvoxels/s", "cores": r["cores"], "kind": r["kind"],
                                  "sample": r["sample"]},
                 "e2e": {"value": r["mvox_s"], "unit": "Mvoxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import torch
@@ -231,6 +274,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     if nd == 3 and world > 1:
         import bench_modes
+        bench_modes.emit = emit
         return bench_modes.run_slab(args, rank, world, local_rank, dist)
     L = api.lib()
     import ctypes as C
@@ -279,14 +323,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for i in range(max(args.warmup, nsets)):  # every rotating input/handle is touched before timing
         step(i)
-    sampler = ClockSampler(local_rank)
     launches0 = sum(b.launch_count() for b in builders)
     kern_ms = np.zeros(5)
     cands = 0
     barrier()
-    sampler.start()
+    sampler.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
@@ -295,6 +340,7 @@ def main():
         cands += b.Cn
     e1.record()
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop()
     elapsed_ms = e0.elapsed_time(e1)
     if world > 1:
@@ -389,7 +435,7 @@ def main():
         r = cpu_reference(args.workload, forest_arrays, 1, 0)
         line["cpu_baseline"] = {"value": r["mvox_s"], "unit": "Mvoxels/s", "cores": r["cores"], "kind": r["kind"],
                                 "sample": r["sample"], "candidates_per_s": r["cand_s"]}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -15,6 +15,10 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 
 
+def emit(line):  # replaced by bench.py's emit (which restores the real stdout first)
+    print(json.dumps(line), flush=True)
+
+
 def _max_over_ranks(torch, dist, world, dev, x):
     if world == 1:
         return float(x)
@@ -72,15 +76,16 @@ def run_slab(args, rank, world, local_rank, dist):
         dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = B.ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         step()
-    sampler = B.ClockSampler(local_rank)
     launches0 = b.launch_count()
     acc = dict(voxel_ms=0.0, exchange_ms=0.0, graph_ms=0.0)
     feat_ms = rf_ms = 0.0
     sent = 0
     barrier()
-    sampler.start()
+    sampler.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
@@ -93,6 +98,7 @@ def run_slab(args, rank, world, local_rank, dist):
         feat_ms += ms[2]; rf_ms += ms[3]
     e1.record()
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop()
     elapsed_ms = _max_over_ranks(torch, dist, world, dev, e0.elapsed_time(e1))
     cands = _sum_over_ranks(torch, dist, world, dev, b.Cn)
@@ -148,7 +154,7 @@ def run_slab(args, rank, world, local_rank, dist):
                              "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": alg},
                 "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
-        print(json.dumps(line))
+        emit(line)
     b.close()
     dist.destroy_process_group()
     return 0
@@ -187,12 +193,12 @@ def run_rf_sweep(args, rank, world, local_rank):
         v = n * len(ts) / sum(ts)
         cores = os.cpu_count() or 1
         sample = "%d rows x %d features per step, classForest restatement (oracle/rf_oracle.c), OpenMP over rows" % (n, d)
-        print(json.dumps({"impl": "reference", "metric": metric, "value": v, "unit": "candidates/s", "n_gpus": args.gpus,
+        emit({"impl": "reference", "metric": metric, "value": v, "unit": "candidates/s", "n_gpus": args.gpus,
                           "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * sum(ts) / len(ts),
                           "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                           "data": "synthetic", "config": {"workload": "c5: " + S["desc"], "sample": sample},
                           "cpu_baseline": {"value": v, "unit": "candidates/s", "cores": cores, "kind": "port", "sample": sample},
-                          "e2e": {"value": v, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+                          "e2e": {"value": v, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
         return 0
     import torch
     import torch.distributed as dist
@@ -221,17 +227,19 @@ def run_rf_sweep(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = B.ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         step()
-    sampler = B.ClockSampler(local_rank)
     barrier()
-    sampler.start()
+    sampler.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop()
     elapsed_ms = _max_over_ranks(torch, dist, world, dev, e0.elapsed_time(e1))
     value = n_all * args.steps / (elapsed_ms * 1e-3)
@@ -274,7 +282,7 @@ def run_rf_sweep(args, rank, world, local_rank):
             t0 = time.perf_counter(); orf.predict(Xs, threads=os.cpu_count() or 1); dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": ns / dt, "unit": "candidates/s", "cores": os.cpu_count() or 1, "kind": "port",
                                     "sample": "%d rows, classForest restatement (oracle/rf_oracle.c), OpenMP over rows" % ns}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

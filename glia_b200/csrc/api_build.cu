@@ -103,8 +103,12 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
   if (cap == 0) {
     // directed boundaries per region: ~5.7 in 2D, ~13.8 in 3D (synthetic EM); the table is
     // grown x4 and the pass re-run if this guess is too small
-    uint64_t est = std::min<uint64_t>(owned, (P.ndim == 2 ? 8ull : 16ull) * LB);
+    uint64_t est = (P.ndim == 2 ? 8ull : 16ull) * LB;
+    // a z-slab sees (and, after the exchange, owns) its share of the boundaries plus those near its faces
+    if (P.zEnd - P.zBegin < P.Z) est = 2 * est * (uint64_t)(P.zEnd - P.zBegin) / (uint64_t)P.Z + 4096;
+    est = std::min<uint64_t>(owned, est);
     cap = pow2ceil(est + est / 2 + 1024);
+    if (cap < h->capHint) cap = h->capHint;
   } else cap = pow2ceil(cap);
   const uint64_t capMax = pow2ceil(2 * (uint64_t)owned + 1024);
   if (cap > capMax) cap = capMax;
@@ -198,6 +202,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
     if (prm.edge_capacity != 0 || cap >= capMax) { h->err = "directed-boundary table full: raise edge_capacity"; return GLIA_E_CAPACITY; }
     cap *= 4;
     if (cap > capMax) cap = capMax;
+    h->capHint = cap;
     continue;
   }
   break;

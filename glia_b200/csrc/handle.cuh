@@ -47,6 +47,8 @@ struct RfDist {
   int dim0, dim1;
   double thr;
   int tb[3], te[3];
+  __host__ __device__ int begin(int m) const { return m == 0 ? tb[0] : (m == 1 ? tb[1] : tb[2]); }
+  __host__ __device__ int end(int m) const { return m == 0 ? te[0] : (m == 1 ? te[1] : te[2]); }
   __host__ __device__ int pick(const double* x) const {
     if (n <= 1) return 0;
     if (x[dim1] < thr) return 0;
@@ -83,6 +85,7 @@ struct glia_handle {
   bool built = false;
   bool partial = false;  // raw tables valid (glia_b200_build_partial / glia_b200_build)
   bool usedFast = false;
+  uint64_t capHint = 0;  // boundary-table capacity that turned out to be needed (grown tables are kept)
 
   // kernel-axis geometry (2D runs as X x 1 x rows)
   int KX = 0, KY = 0, KZ = 0;

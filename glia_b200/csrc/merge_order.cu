@@ -58,7 +58,7 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
   }
   __syncwarp();
   int hits = 0;
-  const int mdl = dist.pick(row), tb = dist.tb[mdl], ntree = dist.te[mdl] - tb;  // alg/rf.hxx:97-98
+  const int mdl = dist.pick(row), tb = dist.begin(mdl), ntree = dist.end(mdl) - tb;  // alg/rf.hxx:97-98
   for (int t = tb + lane; t < tb + ntree; t += 32) {
     int k = treeOff[t];
     RfNode16 nd = nodes[k];

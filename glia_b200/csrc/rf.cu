@@ -42,7 +42,7 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
     for (int c = 0; c < nclass; ++c) svotes[c * blockDim.x + threadIdx.x] = 0;
   int hits = 0;
   if (active) {
-    const int mdl = dist.pick(x), tb = dist.tb[mdl], ntree = dist.te[mdl] - tb;
+    const int mdl = dist.pick(x), tb = dist.begin(mdl), ntree = dist.end(mdl) - tb;
     for (int t = tb; t < tb + ntree; ++t) {
       int k = __ldg(treeOff + t);
       RfNode nd = nodes[k];
@@ -66,6 +66,7 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
 // threads share a candidate and split the trees, two trees in flight per thread; sibling pairs
 // are 32-byte aligned so that one L2 sector serves either outcome of a split.
 #define RF_CPB 64
+template <bool ENS>  // ENS: model ensemble, the tree range depends on the row (alg/rf.hxx:97-98)
 __global__ void __launch_bounds__(256)
 rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, const RfDist dist,
                      int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
@@ -92,9 +93,10 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
   int hits = 0;
   if (cand < ncand) {
     const double* x = srow + cand * ldRow;
-    const int mdl = dist.pick(x), ntree = dist.te[mdl];
-    if (slice == 0) sntree[cand] = ntree - dist.tb[mdl];
-    int t = dist.tb[mdl] + slice;
+    const int mdl = ENS ? dist.pick(x) : 0;
+    const int tbeg = ENS ? dist.begin(mdl) : 0, ntree = ENS ? dist.end(mdl) : dist.te[0];  // uniform when !ENS
+    if (slice == 0) sntree[cand] = ntree - tbeg;
+    int t = tbeg + slice;
     for (; t + 12 < ntree; t += 16) {  // four trees in flight
       int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4), kc = __ldg(treeOff + t + 8), kd = __ldg(treeOff + t + 12);
       RfNode na = nodes[ka], nb = nodes[kb], nc = nodes[kc], nd = nodes[kd];
@@ -440,13 +442,15 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
     if (smem <= 200 * 1024) {
       static bool attr = false;
       if (!attr) {
-        cudaFuncSetAttribute(rf_score_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        const char* co = getenv("GLIA_B200_RF_CARVEOUT");  // percent of the SM's L1/shared array given to shared memory
-        if (co) cudaFuncSetAttribute(rf_score_smem_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(co));
+        cudaFuncSetAttribute(rf_score_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(rf_score_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr = true;
       }
-      rf_score_smem_kernel<<<(unsigned)((N + RF_CPB - 1) / RF_CPB), 256, smem, st>>>(
-          (const RfNode*)m->d_nodes, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+      const unsigned nb = (unsigned)((N + RF_CPB - 1) / RF_CPB);
+      if (m->dist.n > 1)
+        rf_score_smem_kernel<true><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+      else
+        rf_score_smem_kernel<false><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
     } else {
       rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist,
                                                      m->nclass, labelIdx, dX, N, D, nullptr, dProb);

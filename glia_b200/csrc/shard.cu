@@ -194,27 +194,43 @@ extern "C" int glia_b200_import_edges(glia_handle* h, const void* buf, int64_t n
   if (!h || n < 0 || (n > 0 && !buf)) return GLIA_E_ARG;
   if (!h->partial) return GLIA_E_STATE;
   CK(cudaSetDevice(h->prm.device));
-  const VoxParams& P = h->vp;
   cudaStream_t st = h->stream;
-  if (clear_first) {
-    const size_t cap = (size_t)P.edgeCap;
-    CK(cudaMemsetAsync(h->edgeKeys.p, 0xFF, 8 * cap, st));
-    CK(cudaMemsetAsync(h->edgeAdd.p, 0, 4 * cap * P.edge.nAdd, st));
-    CK(cudaMemsetAsync(h->edgeMax.p, 0, 4 * cap * P.edge.nMax, st));
-    CK(cudaMemsetAsync(h->edgeF64.p, 0, 8 * cap * P.edge.nF64, st));
-    CK(cudaMemsetAsync(P.overflow, 0, 4, st));
-    h->launches += 5;
+  VoxParams& PW = h->vp;
+  for (;;) {
+    const size_t cap = (size_t)PW.edgeCap;
+    if (clear_first) {
+      CK(cudaMemsetAsync(h->edgeKeys.p, 0xFF, 8 * cap, st));
+      CK(cudaMemsetAsync(h->edgeAdd.p, 0, 4 * cap * PW.edge.nAdd, st));
+      CK(cudaMemsetAsync(h->edgeMax.p, 0, 4 * cap * PW.edge.nMax, st));
+      CK(cudaMemsetAsync(h->edgeF64.p, 0, 8 * cap * PW.edge.nF64, st));
+      CK(cudaMemsetAsync(PW.overflow, 0, 4, st));
+      h->launches += 5;
+    }
+    if (n > 0) {
+      import_edges_kernel<<<nblk((unsigned long long)n, 256), 256, 0, st>>>(
+          (const uint32_t*)buf, n, rec_words(PW.edge), PW.edge, (unsigned long long*)h->edgeKeys.p, PW.edgeCap,
+          h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), PW.overflow);
+      h->launches++;
+    }
+    int ovf = 0;
+    CK(cudaMemcpyAsync(&ovf, PW.overflow, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (!ovf) break;
+    // owned + neighbour boundaries do not fit (labels far from spatial order): the table is rebuilt
+    // from the import buffer alone, so it can simply be enlarged and the import repeated
+    if (!clear_first || h->prm.edge_capacity != 0) {
+      h->err = "directed-boundary table full during import: raise edge_capacity"; return GLIA_E_CAPACITY;
+    }
+    const uint64_t ncap = PW.edgeCap * 4;
+    CK(h->edgeKeys.ensure(8 * (size_t)ncap));
+    CK(h->edgeAdd.ensure(4 * (size_t)ncap * PW.edge.nAdd));
+    CK(h->edgeMax.ensure(4 * (size_t)ncap * std::max(1, PW.edge.nMax)));
+    CK(h->edgeF64.ensure(8 * (size_t)ncap * std::max(1, PW.edge.nF64)));
+    PW.edgeCap = ncap;
+    h->capHint = ncap;
+    PW.edgeKeys = (unsigned long long*)h->edgeKeys.p;
+    PW.edgeAdd = h->edgeAdd.as<uint32_t>(); PW.edgeMax = h->edgeMax.as<uint32_t>(); PW.edgeF64 = h->edgeF64.as<double>();
   }
-  if (n > 0) {
-    import_edges_kernel<<<nblk((unsigned long long)n, 256), 256, 0, st>>>(
-        (const uint32_t*)buf, n, rec_words(P.edge), P.edge, (unsigned long long*)h->edgeKeys.p, P.edgeCap,
-        h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), P.overflow);
-    h->launches++;
-  }
-  int ovf = 0;
-  CK(cudaMemcpyAsync(&ovf, P.overflow, 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  if (ovf) { h->err = "directed-boundary table full during import: raise edge_capacity"; return GLIA_E_CAPACITY; }
   return GLIA_OK;
 }
 
