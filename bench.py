@@ -37,6 +37,11 @@ def emit(line):
     global _STDOUT_FD
     sys.stdout.flush()
     if _STDOUT_FD is not None:
+        try:  # C-level stdio of the libraries (NCCL's printf banner) is still buffered: push it to stderr now
+            import ctypes
+            ctypes.CDLL(None).fflush(None)
+        except Exception:
+            pass
         os.dup2(_STDOUT_FD, 1)
         os.close(_STDOUT_FD)
         _STDOUT_FD = None
