@@ -56,7 +56,7 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_rf_destroy", "glia_b200_rf_info", "glia_b200_rf_score", "glia_b200_last_ms",
            "glia_b200_launch_count", "glia_b200_build_partial", "glia_b200_raw_region_tables",
            "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
-           "glia_b200_import_edges", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
+           "glia_b200_import_edges", "glia_b200_table_load", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
            "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble"]
 
 
@@ -101,8 +101,9 @@ def lib():
         L.glia_b200_raw_region_tables.argtypes = [vp, vpp, vpp, vpp, i64p, i64p, i64p]
         L.glia_b200_finalize_regions.argtypes = [vp, i64p]
         L.glia_b200_edge_interest.argtypes = [vp, C.c_int, vpp, i64p]
-        L.glia_b200_export_edges.argtypes = [vp, C.c_int, i64p, vpp, C.POINTER(C.c_int)]
+        L.glia_b200_export_edges.argtypes = [vp, C.c_int, C.c_int, i64p, vpp, C.POINTER(C.c_int)]
         L.glia_b200_import_edges.argtypes = [vp, vp, C.c_int64, C.c_int]
+        L.glia_b200_table_load.argtypes = [vp, i64p, i64p]
         L.glia_b200_finalize_edges.argtypes = [vp, C.c_int64, C.c_int64]
         L.glia_b200_synth_voronoi.argtypes = [C.c_int, C.POINTER(C.c_int), C.c_int, C.c_uint32, vp, vp, vp,
                                               C.POINTER(C.c_uint64)]
@@ -401,11 +402,16 @@ class MergeTreeBuilder:
         self._check(lib().glia_b200_edge_interest(self.h, world, C.byref(p), C.byref(n)))
         return p.value or 0, n.value
 
-    def export_edges(self, world):
+    def export_edges(self, world, self_rank=-1):
         counts = (C.c_int64 * world)()
         p, rb = C.c_void_p(), C.c_int()
-        self._check(lib().glia_b200_export_edges(self.h, world, counts, C.byref(p), C.byref(rb)))
+        self._check(lib().glia_b200_export_edges(self.h, world, self_rank, counts, C.byref(p), C.byref(rb)))
         return list(counts), p.value or 0, rb.value
+
+    def table_load(self):
+        o, c = C.c_int64(), C.c_int64()
+        self._check(lib().glia_b200_table_load(self.h, C.byref(o), C.byref(c)))
+        return o.value, c.value
 
     def import_edges(self, ptr, n, clear_first=True):
         self._check(lib().glia_b200_import_edges(self.h, C.c_void_p(int(ptr)) if ptr else None, n, int(clear_first)))

@@ -85,6 +85,7 @@ struct glia_handle {
   bool built = false;
   bool partial = false;  // raw tables valid (glia_b200_build_partial / glia_b200_build)
   bool usedFast = false;
+  long long tableOccupied = 0;  // occupied slots of the boundary table at the last export (shard.cu)
   uint64_t capHint = 0;  // boundary-table capacity that turned out to be needed (grown tables are kept)
 
   // kernel-axis geometry (2D runs as X x 1 x rows)

@@ -49,15 +49,18 @@ __global__ void export_edges_kernel(const unsigned long long* __restrict__ keys,
                                     RecLayout L, const uint32_t* __restrict__ gAdd,
                                     const uint32_t* __restrict__ gMax, const double* __restrict__ gF64,
                                     unsigned long long* __restrict__ cursor, int recWords,
-                                    uint32_t* __restrict__ out) {
+                                    uint32_t* __restrict__ out, int skipRank) {
   uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (i >= cap) return;
-  unsigned long long k = keys[i];
+  unsigned long long k = (i < cap) ? keys[i] : EDGE_EMPTY;
+  if (PASS == 0) {  // cursor[64] = occupied slots of the table (one atomic per block)
+    int occ = __syncthreads_count(k != EDGE_EMPTY);
+    if (threadIdx.x == 0 && occ) atomicAdd(cursor + 64, (unsigned long long)occ);
+  }
   if (k == EDGE_EMPTY) return;
   uint32_t ra = rank[(uint32_t)(k >> 32)];
   const int padW = (L.nAdd + L.nMax) & 1;
   for (int d = 0; d < world; ++d) {
-    if (!interest[(size_t)ra * world + d]) continue;
+    if (d == skipRank || !interest[(size_t)ra * world + d]) continue;
     unsigned long long pos = atomicAdd(cursor + d, 1ull);
     if (PASS == 0) continue;
     uint32_t* o = out + (size_t)pos * recWords;
@@ -159,34 +162,44 @@ extern "C" int glia_b200_edge_interest(glia_handle* h, int world, void** mask, i
   return GLIA_OK;
 }
 
-extern "C" int glia_b200_export_edges(glia_handle* h, int world, int64_t* counts, void** buf, int* rec_bytes) {
+extern "C" int glia_b200_export_edges(glia_handle* h, int world, int self_rank, int64_t* counts, void** buf,
+                                      int* rec_bytes) {
   if (!h || world < 1 || world > 64 || !counts) return GLIA_E_ARG;
   if (!h->partial || !h->interest.p) return GLIA_E_STATE;
   CK(cudaSetDevice(h->prm.device));
   const VoxParams& P = h->vp;
   cudaStream_t st = h->stream;
   const int rw = rec_words(P.edge);
-  CK(h->exportCursor.ensure(8 * 64));
+  CK(h->exportCursor.ensure(8 * 65));
   unsigned long long* cursor = h->exportCursor.as<unsigned long long>();
-  CK(cudaMemsetAsync(cursor, 0, 8 * 64, st));
+  CK(cudaMemsetAsync(cursor, 0, 8 * 65, st));
   export_edges_kernel<0><<<nblk(P.edgeCap, 256), 256, 0, st>>>(
       (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), h->interest.as<unsigned char>(),
-      world, P.edge, nullptr, nullptr, nullptr, cursor, rw, nullptr);
-  unsigned long long cnt[64], off[64], total = 0;
-  CK(cudaMemcpyAsync(cnt, cursor, 8 * world, cudaMemcpyDeviceToHost, st));
+      world, P.edge, nullptr, nullptr, nullptr, cursor, rw, nullptr, self_rank);
+  unsigned long long cnt[65], off[64], total = 0;
+  CK(cudaMemcpyAsync(cnt, cursor, 8 * 65, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  h->tableOccupied = (long long)cnt[64];
   for (int d = 0; d < world; ++d) { off[d] = total; total += cnt[d]; counts[d] = (int64_t)cnt[d]; }
   CK(h->exportBuf.ensure(4 * (size_t)rw * (size_t)std::max<unsigned long long>(total, 1)));
   CK(cudaMemcpyAsync(cursor, off, 8 * world, cudaMemcpyHostToDevice, st));
   export_edges_kernel<1><<<nblk(P.edgeCap, 256), 256, 0, st>>>(
       (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), h->interest.as<unsigned char>(),
       world, P.edge, h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), cursor, rw,
-      h->exportBuf.as<uint32_t>());
+      h->exportBuf.as<uint32_t>(), self_rank);
   h->launches += 3;
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));
   if (buf) *buf = h->exportBuf.p;
   if (rec_bytes) *rec_bytes = 4 * rw;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_table_load(const glia_handle* h, int64_t* occupied, int64_t* capacity) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  if (occupied) *occupied = h->tableOccupied;
+  if (capacity) *capacity = (int64_t)h->vp.edgeCap;
   return GLIA_OK;
 }
 

@@ -7,6 +7,7 @@ file only moves the partial tables between ranks.
   build_sharded(comm, b, labels_slab, pb_slab)      # b now holds the candidates this rank owns
   sal = b.score_candidates(forest)
 """
+import os
 import threading
 
 import numpy as np
@@ -207,18 +208,31 @@ def build_sharded(comm, b, labels, pb, mask=None, timings=None):
     pi, ni = b.edge_interest(comm.world)
     comm.all_reduce(dev_tensor(pi, ni, torch.uint8, dev), "max")
     torch.cuda.synchronize(dev)
-    counts, pe, rec = b.export_edges(comm.world)
-    send = dev_tensor(pe, sum(counts) * rec, torch.uint8, dev).view(-1, rec)
-    recv = comm.all_to_all_v(send, counts)                            # reduce keyed by label pair, part 1
-    torch.cuda.synchronize(dev)
+    # reduce keyed by label pair: every rank keeps its own records and merges what the others send; if the
+    # merged set would not fit some rank's table (labels far from spatial order) all ranks repeat the exchange
+    # with their own records included and rebuild (and grow) the tables from the received runs
+    rebuild = bool(os.environ.get("GLIA_B200_FORCE_REBUILD"))  # test hook: take the fallback path
+    for attempt in range(2):
+        counts, pe, rec = b.export_edges(comm.world, -1 if rebuild else comm.rank)
+        send = dev_tensor(pe, sum(counts) * rec, torch.uint8, dev).view(-1, rec)
+        recv = comm.all_to_all_v(send, counts)
+        torch.cuda.synchronize(dev)
+        if rebuild:
+            break
+        occ, cap = b.table_load()
+        flag = torch.tensor([1 if (occ + recv.shape[0]) * 10 > cap * 8 else 0], dtype=torch.int32, device=dev)
+        comm.all_reduce(flag, "max")
+        if int(flag.item()) == 0:
+            break
+        rebuild = True
     mark()
-    b.import_edges(recv.data_ptr() if recv.numel() else 0, recv.shape[0], True)  # part 2: merge equal pairs
+    b.import_edges(recv.data_ptr() if recv.numel() else 0, recv.shape[0], rebuild)
     lo, hi = owner_range(R, comm.world, comm.rank)
     b.finalize_edges(lo, hi)
     mark()
     if timings is not None:
         torch.cuda.synchronize(dev)
         timings.update(voxel_ms=ev[0].elapsed_time(ev[1]), exchange_ms=ev[1].elapsed_time(ev[2]),
-                       graph_ms=ev[2].elapsed_time(ev[3]), sent_records=int(sum(counts) - counts[comm.rank]),
+                       graph_ms=ev[2].elapsed_time(ev[3]), sent_records=int(sum(counts)),
                        record_bytes=rec)
     return b

@@ -133,7 +133,7 @@ GLIA_API int glia_b200_bc_feat(glia_handle* h, const uint32_t* order /*[n][3]*/,
  * order (glia_b200/parallel.py drives it with NCCL collectives):
  *   build_partial -> all-reduce raw_region_tables (add: sum, max: unsigned max, f64: sum)
  *   -> finalize_regions -> edge_interest (all-reduce max over the byte mask)
- *   -> export_edges -> all-to-all of the per-destination record runs -> import_edges(clear_first=1)
+ *   -> export_edges -> all-to-all of the per-destination record runs -> import_edges
  *   -> finalize_edges(own_lo, own_hi) -> init_candidates / score_candidates on the owned candidates.
  * Region index r (ascending label order, identical on all ranks) is owned by rank
  * min(world-1, r / ceil(R/world)); a candidate (a,b), a<b, belongs to the owner of a.
@@ -143,8 +143,16 @@ GLIA_API int glia_b200_raw_region_tables(glia_handle* h, void** add, void** mx, 
                                          int64_t* n_max, int64_t* n_f64);
 GLIA_API int glia_b200_finalize_regions(glia_handle* h, int64_t* R);
 GLIA_API int glia_b200_edge_interest(glia_handle* h, int world, void** mask, int64_t* bytes);
-/* counts [world]: records for each destination rank, stored back to back in *buf in rank order. */
-GLIA_API int glia_b200_export_edges(glia_handle* h, int world, int64_t* counts, void** buf, int* rec_bytes);
+/* counts [world]: records for each destination rank, stored back to back in *buf in rank order.
+ * self_rank >= 0: nothing is exported to that rank - its records stay in the handle's table and the
+ * received ones are merged with import_edges(clear_first = 0); self_rank < 0: every destination gets a run
+ * and the table is rebuilt with import_edges(clear_first = 1). */
+GLIA_API int glia_b200_export_edges(glia_handle* h, int world, int self_rank, int64_t* counts, void** buf,
+                                    int* rec_bytes);
+/* occupied slots (counted by the last export_edges) and capacity of the boundary table: a caller that
+ * keeps its own records (self_rank >= 0) checks that occupied + received fits before import_edges(…, 0),
+ * and otherwise repeats the exchange with self_rank = -1 / clear_first = 1, which grows the table. */
+GLIA_API int glia_b200_table_load(const glia_handle* h, int64_t* occupied, int64_t* capacity);
 GLIA_API int glia_b200_import_edges(glia_handle* h, const void* buf, int64_t n, int clear_first);
 GLIA_API int glia_b200_finalize_edges(glia_handle* h, int64_t own_lo, int64_t own_hi);
 

@@ -90,3 +90,17 @@ def test_sharded_against_oracle():
     keys = np.concatenate([r[0] for r in res]); rows = np.concatenate([r[1] for r in res])
     assert np.array_equal(keys, ko)
     np.testing.assert_allclose(rows, rowo, rtol=1e-5, atol=1e-12)
+
+
+def test_sharded_rebuild_path(monkeypatch):
+    """The fallback of build_sharded (own records exported too, tables rebuilt and grown from the received
+    runs) gives the same candidates as the default path (own records kept in place)."""
+    shape = (20, 30, 44)
+    lab, pb = synth.voronoi_volume(shape, 6, seed=9)
+    perm = np.random.RandomState(4).permutation(int(lab.max()) + 1).astype(np.uint32) + 1
+    lab = perm[lab]
+    a = _run_sharded(3, shape, lab, pb, _cfg)
+    monkeypatch.setenv("GLIA_B200_FORCE_REBUILD", "1")
+    b = _run_sharded(3, shape, lab, pb, _cfg)
+    for ra, rb in zip(a, b):
+        assert np.array_equal(ra[0], rb[0]) and np.array_equal(ra[1], rb[1])
