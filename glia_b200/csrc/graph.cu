@@ -78,6 +78,33 @@ __global__ void gather_edges_kernel(const unsigned long long* __restrict__ keySo
   for (int i = lane; i < L.nF64; i += 32) sF64[(size_t)w * L.nF64 + i] = gF64[s * L.nF64 + i];
 }
 
+// Vectorised variant for record layouts made of whole 16-byte units (default hmt layout: 20 add words,
+// 2 max words, 2 doubles): 8 lanes move one record with uint4 / uint2 / double2 accesses, 4 records per
+// warp, so four times as many bytes are in flight per warp as in the word-per-lane kernel above (which
+// ran at 0.7 TB/s on the 1.6 GB of scattered records of C4).
+__global__ void gather_edges_vec_kernel(const unsigned long long* __restrict__ keySorted,
+                                        const uint32_t* __restrict__ slotSorted, long long E, RecLayout L,
+                                        const uint32_t* __restrict__ gAdd, const uint32_t* __restrict__ gMax,
+                                        const double* __restrict__ gF64, int* __restrict__ ea,
+                                        int* __restrict__ eb, uint32_t* __restrict__ sAdd,
+                                        uint32_t* __restrict__ sMax, double* __restrict__ sF64) {
+  const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 3;
+  const int sub = threadIdx.x & 7;
+  if (w >= E) return;
+  const size_t s = slotSorted[w];
+  const int nA4 = L.nAdd >> 2, nM2 = L.nMax >> 1, nF2 = L.nF64 >> 1;
+  const uint4* a4 = (const uint4*)(gAdd + s * L.nAdd);
+  uint4* o4 = (uint4*)(sAdd + (size_t)w * L.nAdd);
+  for (int i = sub; i < nA4; i += 8) o4[i] = a4[i];
+  const uint2* m2 = (const uint2*)(gMax + s * L.nMax);
+  uint2* om = (uint2*)(sMax + (size_t)w * L.nMax);
+  for (int i = sub; i < nM2; i += 8) om[i] = m2[i];
+  const double2* f2 = (const double2*)(gF64 + s * L.nF64);
+  double2* of = (double2*)(sF64 + (size_t)w * L.nF64);
+  for (int i = 7 - sub; i < nF2; i += 8) of[i] = f2[i];
+  if (sub == 6) { unsigned long long k = keySorted[w]; ea[w] = (int)(k >> 32); eb[w] = (int)(uint32_t)k; }
+}
+
 // row[r] = first edge with a >= r (r in 0..R)
 __global__ void csr_rows_kernel(const int* __restrict__ ea, long long E, long long R,
                                 int* __restrict__ row) {
@@ -268,7 +295,16 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   CK(h->sAdd.ensure(4 * (size_t)(E + 1) * P.edge.nAdd));
   CK(h->sMax.ensure(4 * (size_t)(E + 1) * (P.edge.nMax + 1)));
   CK(h->sF64.ensure(8 * (size_t)(E + 1) * (P.edge.nF64 + 1)));
-  if (E > 0) {
+  const bool vecLayout = (P.edge.nAdd % 4 == 0) && (P.edge.nMax % 2 == 0) && (P.edge.nF64 % 2 == 0) && P.edge.nMax > 0 &&
+                         P.edge.nF64 > 0;
+  if (E > 0 && vecLayout) {
+    gather_edges_vec_kernel<<<nblk(E * 8, 256), 256, 0, st>>>(
+        h->eKeySorted.as<unsigned long long>(), h->eSlotSorted.as<uint32_t>(), E, P.edge,
+        h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(),
+        h->ea.as<int>(), h->eb.as<int>(), h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
+        h->sF64.as<double>());
+    h->launches++;
+  } else if (E > 0) {
     gather_edges_kernel<<<nblk(E * 32, 256), 256, 0, st>>>(
         h->eKeySorted.as<unsigned long long>(), h->eSlotSorted.as<uint32_t>(), E, P.edge,
         h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(),
