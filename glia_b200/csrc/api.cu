@@ -140,7 +140,7 @@ extern "C" void glia_b200_destroy(glia_handle* h) {
                           &h->eSlotSorted, &h->eKeySorted, &h->sAdd, &h->sMax, &h->sF64, &h->ea,
                           &h->eb, &h->row, &h->rev, &h->cand, &h->bAggAdd, &h->bAggMax, &h->bAggF64,
                           &h->cubTmp, &h->scalars, &h->rows, &h->sal, &h->keysOut, &h->interest,
-                          &h->exportBuf, &h->exportCursor, &h->regBlocks};
+                          &h->exportBuf, &h->exportCursor, &h->regBlocks, &h->bAggMax2, &h->bAggOwn};
   for (auto b : bufs) b->release();
   for (auto& b : h->inImg) b.release();
   for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);

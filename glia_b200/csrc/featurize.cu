@@ -16,6 +16,7 @@ struct GraphView {
   const uint32_t* cAdd; const uint32_t* cMax; const double* cF64;        // regions
   const uint32_t* sAdd; const uint32_t* sMax; const double* sF64;        // directed boundaries
   const uint32_t* aAdd; const uint32_t* aMax; const double* aF64;        // per-region boundary aggregate
+  const uint32_t* aMax2; const int* aOwn;                                // second best / holder of the best
 };
 
 __global__ void __launch_bounds__(128)
@@ -93,14 +94,30 @@ init_candidates_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_co
   RecSum2 pb{pe, pr};  // pair boundary b(X,Y) = (a->b) u (b->a)   (util/struct.hxx:10-16)
   RecBoundaryZ bz;
   bz.pa = G.aAdd + (size_t)a * LE.nAdd; bz.qa = G.aAdd + (size_t)b * LE.nAdd; bz.ea = pe.a; bz.ra = pr.a;
-  for (int i = 0; i < LE.nMax; ++i) bz.mxw[i] = 0;
-  for (int i = 0; i < LE.nF64; ++i) bz.f[i] = 0.0;
-  for (int side = 0; side < 2; ++side) {  // entries(Z), region.hxx:66-75
-    int r = side ? b : a;
-    for (int k = G.row[r]; k < G.row[r + 1]; ++k) {
-      if (k == e || k == rv) continue;
-      for (int i = 0; i < LE.nMax; ++i) bz.mxw[i] = max(bz.mxw[i], G.sMax[(size_t)k * LE.nMax + i]);
-      for (int i = 0; i < LE.nF64; ++i) bz.f[i] += G.sF64[(size_t)k * LE.nF64 + i];
+  // entries(Z) = all boundaries of a and of b except the mutual pair (region.hxx:66-75).  Instead of
+  // walking the ~2 deg boundary records per candidate: max words from the per-region best / second best
+  // (the excluded boundary may hold the best), sums as aggregate - pair (exact for dyadic values, ~1e-13
+  // relative otherwise; non-finite totals take the walk so that inf - inf cannot appear).
+  bool walk = false;
+  for (int i = 0; i < LE.nF64; ++i) {
+    const double ta = G.aF64[(size_t)a * LE.nF64 + i], tb = G.aF64[(size_t)b * LE.nF64 + i];
+    walk = walk || !isfinite(ta) || !isfinite(tb);
+    bz.f[i] = (ta - pe.f[i]) + (tb - pr.f[i]);
+  }
+  for (int i = 0; i < LE.nMax; ++i) {
+    const size_t ia = (size_t)a * LE.nMax + i, ib = (size_t)b * LE.nMax + i;
+    const uint32_t ma = G.aOwn[ia] == e ? G.aMax2[ia] : G.aMax[ia];
+    const uint32_t mb = G.aOwn[ib] == rv ? G.aMax2[ib] : G.aMax[ib];
+    bz.mxw[i] = max(ma, mb);
+  }
+  if (walk) {
+    for (int i = 0; i < LE.nF64; ++i) bz.f[i] = 0.0;
+    for (int side = 0; side < 2; ++side) {
+      int r = side ? b : a;
+      for (int k = G.row[r]; k < G.row[r + 1]; ++k) {
+        if (k == e || k == rv) continue;
+        for (int i = 0; i < LE.nF64; ++i) bz.f[i] += G.sF64[(size_t)k * LE.nF64 + i];
+      }
     }
   }
   const int ld = xi + 2;
@@ -173,6 +190,7 @@ GraphView glia_graph_view(const glia_handle* h) {
   G.cAdd = h->cAdd.as<uint32_t>(); G.cMax = h->cMax.as<uint32_t>(); G.cF64 = h->cF64.as<double>();
   G.sAdd = h->sAdd.as<uint32_t>(); G.sMax = h->sMax.as<uint32_t>(); G.sF64 = h->sF64.as<double>();
   G.aAdd = h->bAggAdd.as<uint32_t>(); G.aMax = h->bAggMax.as<uint32_t>(); G.aF64 = h->bAggF64.as<double>();
+  G.aMax2 = h->bAggMax2.as<uint32_t>(); G.aOwn = h->bAggOwn.as<int>();
   return G;
 }
 

@@ -139,7 +139,8 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
                                           const uint32_t* __restrict__ sMax,
                                           const double* __restrict__ sF64,
                                           uint32_t* __restrict__ aAdd, uint32_t* __restrict__ aMax,
-                                          double* __restrict__ aF64, long long lo, long long hi) {
+                                          double* __restrict__ aF64, uint32_t* __restrict__ aMax2,
+                                          int* __restrict__ aOwn, long long lo, long long hi) {
   long long r = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (r >= R) return;
@@ -150,10 +151,15 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
     for (int e = e0; e < e1; ++e) s += sAdd[(size_t)e * L.nAdd + i];
     aAdd[(size_t)r * L.nAdd + i] = s;
   }
-  for (int i = lane; i < L.nMax; i += 32) {
-    uint32_t s = 0;
-    for (int e = e0; e < e1; ++e) s = max(s, sMax[(size_t)e * L.nMax + i]);
-    aMax[(size_t)r * L.nMax + i] = s;
+  for (int i = lane; i < L.nMax; i += 32) {  // best, its boundary, and the best of the others
+    uint32_t b1 = 0, b2 = 0; int own = -1;
+    for (int e = e0; e < e1; ++e) {
+      uint32_t v = sMax[(size_t)e * L.nMax + i];
+      if (v > b1) { b2 = b1; b1 = v; own = e; } else if (v > b2) b2 = v;
+    }
+    aMax[(size_t)r * L.nMax + i] = b1;
+    aMax2[(size_t)r * L.nMax + i] = b2;
+    aOwn[(size_t)r * L.nMax + i] = own;
   }
   for (int i = lane; i < L.nF64; i += 32) {
     double s = 0.0;
@@ -338,11 +344,13 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   CK(h->bAggAdd.ensure(4 * (size_t)(R + 1) * P.edge.nAdd));
   CK(h->bAggMax.ensure(4 * (size_t)(R + 1) * (P.edge.nMax + 1)));
   CK(h->bAggF64.ensure(8 * (size_t)(R + 1) * (P.edge.nF64 + 1)));
+  CK(h->bAggMax2.ensure(4 * (size_t)(R + 1) * (P.edge.nMax + 1)));
+  CK(h->bAggOwn.ensure(4 * (size_t)(R + 1) * (P.edge.nMax + 1)));
   if (R > 0) {
     boundary_aggregate_kernel<<<nblk(R * 32, 256), 256, 0, st>>>(
         h->row.as<int>(), R, P.edge, h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
         h->sF64.as<double>(), h->bAggAdd.as<uint32_t>(), h->bAggMax.as<uint32_t>(),
-        h->bAggF64.as<double>(), ownLo, ownHi);
+        h->bAggF64.as<double>(), h->bAggMax2.as<uint32_t>(), h->bAggOwn.as<int>(), ownLo, ownHi);
     h->launches++;
   }
   CK(cudaGetLastError());

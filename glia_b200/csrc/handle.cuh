@@ -106,6 +106,7 @@ struct glia_handle {
   glia::DevBuf eSlot, eKey, eSlotSorted, eKeySorted;      // compaction + sort
   glia::DevBuf sAdd, sMax, sF64, ea, eb, row, rev, cand;  // directed boundaries, CSR by a
   glia::DevBuf bAggAdd, bAggMax, bAggF64;                 // per-region sum over its boundaries
+  glia::DevBuf bAggMax2, bAggOwn;                         // second-best max words and the boundary holding the best
   glia::DevBuf cubTmp, scalars, rows, sal, keysOut;
   glia::DevBuf regBlocks;                                 // per-region x1/x2 row blocks (featurize.cu)
   glia::DevBuf interest, exportBuf, exportCursor;         // multi-GPU exchange (shard.cu)
