@@ -66,6 +66,7 @@ struct glia_rf {
   int totalNodes = 0;
   int* d_treeOff = nullptr;      // [ntree+1]
   void* d_nodes = nullptr;       // packed nodes
+  void* d_nodesW = nullptr;      // walk encoding for rf_score_smem_kernel: leaves are self-loops (rf.cu)
   void* d_nodes8 = nullptr;      // 8-byte nodes {float threshold, left << 8 | feature} (rf.cu v4)
   double* d_thr = nullptr;       // exact thresholds, same indexing as d_nodes8
   int maxDepth = 0;

@@ -61,6 +61,23 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
 }
 
 
+// node as one 16-byte load: {thr.lo, thr.hi, left, feat}
+__device__ __forceinline__ int4 rf_node(const int4* np, int k) { return __ldg(np + k); }
+__device__ __forceinline__ double rf_lds(uint32_t a) {
+  double v;
+  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+// alg/rf.hxx:35-36 -> classForest: x <= threshold goes left, anything else (NaN too) goes right.
+// Nodes are in the walk encoding (rf_build_device): leaf = sign bit of the feature word, class in the low word.
+// A walk that has reached its leaf issues no loads.  Measured on B200 (profiles/r1_rf_v4_notes.txt): stepping
+// finished walks unconditionally over their self-loop is 7.5 instructions per level instead of 9 but 28 % slower
+// on C5 - the kernel is bound by L1 wavefronts of the divergent 16-byte node loads, not by issue slots.
+#define RF_STEP_P(n)                                                                             \
+  if (n.w >= 0) {                                                                                \
+    const double xv_ = rf_lds(xs + 8u * (uint32_t)n.w);                                          \
+    n = rf_node(np, n.z + (xv_ <= __hiloint2double(n.y, n.x) ? 0 : 1)); }
+
 // v2: a CTA scores RF_CPB candidates whose rows are staged ONCE in shared memory (one coalesced
 // copy; the v1 kernel re-streamed them from DRAM ~85 times, profiles/r1_v1_ncu_rf.txt); four
 // threads share a candidate and split the trees, two trees in flight per thread; sibling pairs
@@ -86,7 +103,10 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
   // (v2 mapped 4 lanes to one candidate; L1 wavefronts were the limiter, profiles/r1_v3_ncu_c4s.txt).
   __shared__ int svote[RF_CPB];
   __shared__ int sntree[RF_CPB];
+  __shared__ volatile uint32_t spin[1];
+  __shared__ volatile unsigned long long spin64[1];
   if (threadIdx.x < RF_CPB) svote[threadIdx.x] = 0;
+  if (threadIdx.x == 0) { spin[0] = (uint32_t)__cvta_generic_to_shared(srow); spin64[0] = (unsigned long long)nodes; }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cand = (warp & 1) * 32 + lane, slice = warp >> 1;
@@ -96,23 +116,24 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
     const int mdl = ENS ? dist.pick(x) : 0;
     const int tbeg = ENS ? dist.begin(mdl) : 0, ntree = ENS ? dist.end(mdl) : dist.te[0];  // uniform when !ENS
     if (slice == 0) sntree[cand] = ntree - tbeg;
+    // The row base (a 32-bit shared-window address) and the node base are read back from shared memory
+    // once: a value ptxas can recompute from a kernel parameter is rematerialised inside every step
+    // (S2R + LDC + 5 integer ops; 20 instructions per tree level where 8 do the work).
+    const uint32_t xs = spin[0] + 8u * (uint32_t)(cand * ldRow);
+    const int4* np = reinterpret_cast<const int4*>(spin64[0]);
     int t = tbeg + slice;
     for (; t + 12 < ntree; t += 16) {  // four trees in flight
-      int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4), kc = __ldg(treeOff + t + 8), kd = __ldg(treeOff + t + 12);
-      RfNode na = nodes[ka], nb = nodes[kb], nc = nodes[kc], nd = nodes[kd];
-      while (na.feat >= 0 || nb.feat >= 0 || nc.feat >= 0 || nd.feat >= 0) {
-        if (na.feat >= 0) { ka = na.left + (x[na.feat] <= na.thr ? 0 : 1); na = nodes[ka]; }
-        if (nb.feat >= 0) { kb = nb.left + (x[nb.feat] <= nb.thr ? 0 : 1); nb = nodes[kb]; }
-        if (nc.feat >= 0) { kc = nc.left + (x[nc.feat] <= nc.thr ? 0 : 1); nc = nodes[kc]; }
-        if (nd.feat >= 0) { kd = nd.left + (x[nd.feat] <= nd.thr ? 0 : 1); nd = nodes[kd]; }
+      int4 na = rf_node(np, __ldg(treeOff + t)), nb = rf_node(np, __ldg(treeOff + t + 4));
+      int4 nc = rf_node(np, __ldg(treeOff + t + 8)), nd = rf_node(np, __ldg(treeOff + t + 12));
+      while ((na.w & nb.w & nc.w & nd.w) >= 0) {  // some walk still on an internal node (leaf: sign bit)
+        RF_STEP_P(na) RF_STEP_P(nb) RF_STEP_P(nc) RF_STEP_P(nd)
       }
-      hits += (na.left == labelIdx) + (nb.left == labelIdx) + (nc.left == labelIdx) + (nd.left == labelIdx);
+      hits += (na.x == labelIdx) + (nb.x == labelIdx) + (nc.x == labelIdx) + (nd.x == labelIdx);
     }
     for (; t < ntree; t += 4) {
-      int k = __ldg(treeOff + t);
-      RfNode nd = nodes[k];
-      while (nd.feat >= 0) { k = nd.left + (x[nd.feat] <= nd.thr ? 0 : 1); nd = nodes[k]; }
-      hits += (nd.left == labelIdx);
+      int4 nd = rf_node(np, __ldg(treeOff + t));
+      while (nd.w >= 0) RF_STEP_P(nd)
+      hits += (nd.x == labelIdx);
     }
     atomicAdd(&svote[cand], hits);
   }
@@ -224,6 +245,19 @@ static int rf_build_device(glia_rf* m) {
   if (cudaMalloc((void**)&m->d_treeOff, 4 * treeOff.size()) != cudaSuccess) return GLIA_E_CUDA;
   if (cudaMemcpy(m->d_nodes, nodes.data(), sizeof(RfNode) * nodes.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
   if (cudaMemcpy(m->d_treeOff, treeOff.data(), 4 * treeOff.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+  {  // walk encoding: a leaf is {NaN with the class in the low word, self - 1, feature 0 | sign bit}.  "x <= NaN" is
+     // false for every x, so the step "left + !(x <= thr)" of a leaf lands on itself: walks need no leaf test.
+    std::vector<RfNode> w(nodes);
+    for (size_t i = 0; i < w.size(); ++i)
+      if (w[i].feat < 0) {
+        const uint64_t bits = 0x7FF8000000000000ull | (uint32_t)w[i].left;
+        memcpy(&w[i].thr, &bits, 8);
+        w[i].left = (int)i - 1;
+        w[i].feat = (int)0x80000000u;
+      }
+    if (cudaMalloc(&m->d_nodesW, sizeof(RfNode) * w.size()) != cudaSuccess) return GLIA_E_CUDA;
+    if (cudaMemcpy(m->d_nodesW, w.data(), sizeof(RfNode) * w.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+  }
   // 8-byte nodes + exact thresholds for rf_score_f32_kernel (features < 255, node ids < 2^24)
   if (m->mdim <= 254 && nodes.size() < (1u << 24)) {
     std::vector<RfNode8> n8(nodes.size());
@@ -401,6 +435,7 @@ extern "C" void glia_b200_rf_destroy(glia_rf* m) {
   if (!m) return;
   if (m->d_nodes) cudaFree(m->d_nodes);
   if (m->d_treeOff) cudaFree(m->d_treeOff);
+  if (m->d_nodesW) cudaFree(m->d_nodesW);
   if (m->d_nodes8) cudaFree(m->d_nodes8);
   if (m->d_thr) cudaFree(m->d_thr);
   delete m;
@@ -448,9 +483,9 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
       }
       const unsigned nb = (unsigned)((N + RF_CPB - 1) / RF_CPB);
       if (m->dist.n > 1)
-        rf_score_smem_kernel<true><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+        rf_score_smem_kernel<true><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
       else
-        rf_score_smem_kernel<false><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+        rf_score_smem_kernel<false><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
     } else {
       rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist,
                                                      m->nclass, labelIdx, dX, N, D, nullptr, dProb);

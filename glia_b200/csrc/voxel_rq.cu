@@ -22,7 +22,7 @@
 namespace glia {
 namespace {
 
-#define RQ_CAP 96      // runs per warp queue (drained at >= 32; one step appends at most 64)
+#define RQ_CAP 128     // per warp: 64 region runs + 64 boundary runs (drained 32 at a time; a step appends <= 32 each)
 #define RQ_EDGE 0x80000000u
 
 // one finished run.  Region: a = label, b = RQ_REGION; boundary: (a -> b)
@@ -67,39 +67,6 @@ __device__ __forceinline__ long long rq_edge_slot_global(const FastParams& P, un
   return -1;
 }
 
-// a run whose key found no shared slot goes straight to the global records
-__device__ __noinline__ void rq_region_run_global(const FastParams& P, const RqEntry& e, int x0warp, int gy, int z0) {
-  if (e.a >= P.labelBound) { atomicExch(P.overflow, 2); return; }
-  uint32_t* ga = P.regAdd + (size_t)e.a * P.reg.nAdd;
-  uint32_t* gm = P.regMax + (size_t)e.a * P.reg.nMax;
-  double* gf = P.regF64 + (size_t)e.a * P.reg.nF64;
-  atomicAdd(ga, e.cnt & 0xFFFFu);
-  if (e.cnt >> 16) atomicAdd(ga + 1, e.cnt >> 16);
-  for (int k = 0; k < 16; ++k) { uint32_t v = ((k < 8 ? e.hlo : e.hhi) >> (4 * (k & 7))) & 15u; if (v) atomicAdd(ga + 2 + k, v); }
-  atomicAdd(gf, e.s); atomicAdd(gf + 1, e.s2);
-  if (e.aux & 0x10000u) {
-    const uint32_t gx = (uint32_t)(x0warp + (int)(e.aux >> 24));
-    const uint32_t zmn = (uint32_t)(z0 + (int)(e.aux & 0xFFu)), zmx = (uint32_t)(z0 + (int)((e.aux >> 8) & 0xFFu));
-    atomicMax(gm + 0, ~gx); atomicMax(gm + 1, ~(uint32_t)gy); atomicMax(gm + 2, ~zmn);
-    atomicMax(gm + 3, gx + 1); atomicMax(gm + 4, (uint32_t)gy + 1); atomicMax(gm + 5, zmx + 1);
-  }
-  if (e.kmin) atomicMax(gm + 6, e.kmin);
-  if (e.kmax) atomicMax(gm + 7, e.kmax);
-}
-__device__ __noinline__ void rq_edge_run_global(const FastParams& P, const RqEntry& e) {
-  long long g = rq_edge_slot_global(P, ((unsigned long long)e.a << 32) | e.b);
-  if (g < 0) return;
-  uint32_t* ga = P.edgeAdd + (size_t)g * P.edge.nAdd;
-  uint32_t* gm = P.edgeMax + (size_t)g * P.edge.nMax;
-  double* gf = P.edgeF64 + (size_t)g * P.edge.nF64;
-  atomicAdd(ga, e.cnt & 0xFFu);
-  for (int t = 0; t < P.nThr; ++t) { uint32_t v = (e.cnt >> (8 * (t + 1))) & 0xFFu; if (v) atomicAdd(ga + 1 + t, v); }
-  for (int k = 0; k < 16; ++k) { uint32_t v = ((k < 8 ? e.hlo : e.hhi) >> (4 * (k & 7))) & 15u; if (v) atomicAdd(ga + 1 + P.nThr + k, v); }
-  atomicAdd(gf, e.s); atomicAdd(gf + 1, e.s2);
-  if (e.kmin) atomicMax(gm + 0, e.kmin);
-  if (e.kmax) atomicMax(gm + 1, e.kmax);
-}
-
 // shared-memory tables of a CTA (same layout as v3):
 //   region slot: key u32 | cnt = count | border << 16 | hist[8] (2 x 16-bit bins per word) |
 //                sum, sum2 (double) | mx[8] = ~bbminx, ~bbminy, ~bbminz, bbmax+1 x3, ~min, max
@@ -141,67 +108,168 @@ size_t voxel_rq_smem_bytes(const FastParams& P) {
 
 namespace {
 
-// the whole warp applies the queued runs, one per lane: slot lookup + a handful of shared atomics
-__device__ __forceinline__ void rq_drain(const FastParams& P, const RqSmem& S, const RqEntry* q, int n, int lane,
-                                         int x0warp, int gy, int z0) {
+// ---- drain: 32 queued runs of one kind, one per lane.  Runs finished in the same step by neighbouring
+// lanes sit next to each other in the queue and mostly carry the same key, so adjacent equal keys are
+// combined first (5-step segmented shuffle reduction, profiles/r1_v4_notes.txt) and only segment heads
+// look up a slot and touch the tables: no region/boundary branch, no second round for leftovers, no
+// contended CAS loops on the doubles.
+__device__ __forceinline__ uint32_t rq_segment(bool head, int lane, int& end) {
+  const uint32_t heads = __ballot_sync(0xffffffffu, head);
+  const uint32_t above = lane == 31 ? 0u : (heads & (0xffffffffu << (lane + 1)));
+  end = above ? (__ffs(above) - 2) : 31;
+  return heads;
+}
+#define RQ_SEG_BEGIN for (int d_ = 1; d_ < 32; d_ <<= 1) { const bool ok_ = lane + d_ <= end;
+#define RQ_SEG_ADD(v) { auto t_ = __shfl_down_sync(0xffffffffu, v, d_); if (ok_) v += t_; }
+#define RQ_SEG_MAX(v) { uint32_t t_ = __shfl_down_sync(0xffffffffu, v, d_); if (ok_) v = max(v, t_); }
+#define RQ_SEG_END }
+
+__device__ __forceinline__ void rq_widen(uint32_t hlo, uint32_t hhi, uint32_t (&w)[8]) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {  // 2 x 16-bit bins per word: the layout of the shared tables
+    w[j] = ((hlo >> (8 * j)) & 0xFu) | (((hlo >> (8 * j + 4)) & 0xFu) << 16);
+    w[4 + j] = ((hhi >> (8 * j)) & 0xFu) | (((hhi >> (8 * j + 4)) & 0xFu) << 16);
+  }
+}
+
+__device__ __forceinline__ void rq_drain_regions(const FastParams& P, const RqSmem& S, const RqEntry* q, int n,
+                                                 int lane, int x0warp, int gy, int z0) {
   __syncwarp();
-  const uint32_t rmask = (uint32_t)(P.regSlots - 1), emask = (uint32_t)(P.edgeSlots - 1);
-  for (int i = lane; i < n; i += 32) {
-    const RqEntry e = q[i];
-    unsigned long long h = (unsigned long long)e.hlo | ((unsigned long long)e.hhi << 32);
-    if (e.b == RQ_REGION) {
-      int slot = -1;
-      uint32_t hsh = ((e.a * 2654435761u) >> 9) & rmask;
-      for (int probe = 0; probe < 8; ++probe) {
-        uint32_t cur = S.rkeys[hsh];
-        if (cur == 0xFFFFFFFFu) cur = atomicCAS(S.rkeys + hsh, 0xFFFFFFFFu, e.a);
-        if (cur == e.a || cur == 0xFFFFFFFFu) { slot = (int)hsh; break; }
-        hsh = (hsh + 1) & rmask;
-      }
-      if (slot < 0) { rq_region_run_global(P, e, x0warp, gy, z0); continue; }
-      atomicAdd(S.rcnt + slot, e.cnt);
-      while (h) {
-        const int b = (__ffsll((long long)h) - 1) >> 2;
-        const uint32_t v = (uint32_t)(h >> (4 * b)) & 15u;
-        atomicAdd(S.rhist + 8 * slot + (b >> 1), v << (16 * (b & 1)));
-        h &= ~(15ull << (4 * b));
-      }
-      atomicAdd(S.rsum + 2 * slot, e.s); atomicAdd(S.rsum + 2 * slot + 1, e.s2);
+  const bool valid = lane < n;
+  RqEntry e;
+  if (valid) e = q[lane]; else { e.a = 0; e.b = RQ_REGION; e.cnt = 0; e.hlo = e.hhi = 0; e.kmin = e.kmax = 0; e.aux = 0; e.s = 0.0; e.s2 = 0.0; }
+  const uint32_t pl = __shfl_up_sync(0xffffffffu, e.a, 1);
+  int end;
+  rq_segment(lane == 0 || !valid || lane == n || pl != e.a, lane, end);
+  const bool head = valid && (lane == 0 || pl != e.a);
+  uint32_t w[8];
+  rq_widen(e.hlo, e.hhi, w);
+  const bool fl = (e.aux & 0x10000u) != 0;
+  const uint32_t gx = (uint32_t)(x0warp + (int)(e.aux >> 24));
+  uint32_t cx0 = fl ? ~gx : 0u, cx1 = fl ? gx + 1u : 0u;
+  uint32_t cz0 = fl ? ~(uint32_t)(z0 + (int)(e.aux & 0xFFu)) : 0u, cz1 = fl ? (uint32_t)(z0 + (int)((e.aux >> 8) & 0xFFu)) + 1u : 0u;
+  uint32_t c = e.cnt, kmin = e.kmin, kmax = e.kmax;
+  double s = e.s, s2 = e.s2;
+  RQ_SEG_BEGIN
+    RQ_SEG_ADD(c) RQ_SEG_ADD(s) RQ_SEG_ADD(s2)
+    RQ_SEG_ADD(w[0]) RQ_SEG_ADD(w[1]) RQ_SEG_ADD(w[2]) RQ_SEG_ADD(w[3]) RQ_SEG_ADD(w[4]) RQ_SEG_ADD(w[5]) RQ_SEG_ADD(w[6]) RQ_SEG_ADD(w[7])
+    RQ_SEG_MAX(kmin) RQ_SEG_MAX(kmax) RQ_SEG_MAX(cx0) RQ_SEG_MAX(cx1) RQ_SEG_MAX(cz0) RQ_SEG_MAX(cz1)
+  RQ_SEG_END
+  if (head) {
+    const uint32_t rmask = (uint32_t)(P.regSlots - 1);
+    int slot = -1;
+    uint32_t hsh = ((e.a * 2654435761u) >> 9) & rmask;
+    for (int probe = 0; probe < 8; ++probe) {
+      uint32_t cur = S.rkeys[hsh];
+      if (cur == 0xFFFFFFFFu) cur = atomicCAS(S.rkeys + hsh, 0xFFFFFFFFu, e.a);
+      if (cur == e.a || cur == 0xFFFFFFFFu) { slot = (int)hsh; break; }
+      hsh = (hsh + 1) & rmask;
+    }
+    if (slot >= 0) {
+      atomicAdd(S.rcnt + slot, c);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (w[j]) atomicAdd(S.rhist + 8 * slot + j, w[j]);
+      atomicAdd(S.rsum + 2 * slot, s); atomicAdd(S.rsum + 2 * slot + 1, s2);
       uint32_t* m = S.rmx + 8 * slot;
-      if (e.aux & 0x10000u) {
-        const uint32_t gx = (uint32_t)(x0warp + (int)(e.aux >> 24));
-        const uint32_t zmn = (uint32_t)(z0 + (int)(e.aux & 0xFFu)), zmx = (uint32_t)(z0 + (int)((e.aux >> 8) & 0xFFu));
-        rq_smax(m + 0, ~gx); rq_smax(m + 1, ~(uint32_t)gy); rq_smax(m + 2, ~zmn);
-        rq_smax(m + 3, gx + 1); rq_smax(m + 4, (uint32_t)gy + 1); rq_smax(m + 5, zmx + 1);
+      if (cx1) {
+        rq_smax(m + 0, cx0); rq_smax(m + 1, ~(uint32_t)gy); rq_smax(m + 2, cz0);
+        rq_smax(m + 3, cx1); rq_smax(m + 4, (uint32_t)gy + 1); rq_smax(m + 5, cz1);
       }
-      if (e.kmin) rq_smax(m + 6, e.kmin);
-      if (e.kmax) rq_smax(m + 7, e.kmax);
-    } else {
-      const unsigned long long key = ((unsigned long long)e.a << 32) | e.b;
-      int slot = -1;
-      uint32_t hsh = ((e.a * 0x9E3779B1u) ^ (e.b * 0x85EBCA77u)) >> 11 & emask;
-      for (int probe = 0; probe < 8; ++probe) {
-        unsigned long long cur = S.ekeys[hsh];
-        if (cur == EDGE_EMPTY) cur = atomicCAS(S.ekeys + hsh, EDGE_EMPTY, key);
-        if (cur == key || cur == EDGE_EMPTY) { slot = (int)hsh; break; }
-        hsh = (hsh + 1) & emask;
+      if (kmin) rq_smax(m + 6, kmin);
+      if (kmax) rq_smax(m + 7, kmax);
+    } else if (e.a >= P.labelBound) {
+      atomicExch(P.overflow, 2);
+    } else {  // table full: the combined run goes straight to the global record
+      uint32_t* ga = P.regAdd + (size_t)e.a * P.reg.nAdd;
+      uint32_t* gm = P.regMax + (size_t)e.a * P.reg.nMax;
+      double* gf = P.regF64 + (size_t)e.a * P.reg.nF64;
+      atomicAdd(ga, c & 0xFFFFu);
+      if (c >> 16) atomicAdd(ga + 1, c >> 16);
+      for (int j = 0; j < 8; ++j) {
+        if (w[j] & 0xFFFFu) atomicAdd(ga + 2 + 2 * j, w[j] & 0xFFFFu);
+        if (w[j] >> 16) atomicAdd(ga + 3 + 2 * j, w[j] >> 16);
       }
-      if (slot < 0) { rq_edge_run_global(P, e); continue; }
-      // shared layout: {count | thr0 << 16, thr1 | thr2 << 16}
-      atomicAdd(S.ecnt + 2 * slot, (e.cnt & 0xFFu) | ((e.cnt & 0xFF00u) << 8));
-      const uint32_t t12 = ((e.cnt >> 16) & 0xFFu) | ((e.cnt >> 24) << 16);
-      if (t12) atomicAdd(S.ecnt + 2 * slot + 1, t12);
-      while (h) {
-        const int b = (__ffsll((long long)h) - 1) >> 2;
-        const uint32_t v = (uint32_t)(h >> (4 * b)) & 15u;
-        atomicAdd(S.ehist + 8 * slot + (b >> 1), v << (16 * (b & 1)));
-        h &= ~(15ull << (4 * b));
+      atomicAdd(gf, s); atomicAdd(gf + 1, s2);
+      if (cx1) {
+        atomicMax(gm + 0, cx0); atomicMax(gm + 1, ~(uint32_t)gy); atomicMax(gm + 2, cz0);
+        atomicMax(gm + 3, cx1); atomicMax(gm + 4, (uint32_t)gy + 1); atomicMax(gm + 5, cz1);
       }
-      atomicAdd(S.esum + 2 * slot, e.s); atomicAdd(S.esum + 2 * slot + 1, e.s2);
-      if (e.kmin) rq_smax(S.emx + 2 * slot, e.kmin);
-      if (e.kmax) rq_smax(S.emx + 2 * slot + 1, e.kmax);
+      if (kmin) atomicMax(gm + 6, kmin);
+      if (kmax) atomicMax(gm + 7, kmax);
     }
   }
+  __syncwarp();
+}
+
+__device__ __forceinline__ void rq_drain_edges(const FastParams& P, const RqSmem& S, const RqEntry* q, int n, int lane) {
+  __syncwarp();
+  const bool valid = lane < n;
+  RqEntry e;
+  if (valid) e = q[lane]; else { e.a = 0; e.b = 0; e.cnt = 0; e.hlo = e.hhi = 0; e.kmin = e.kmax = 0; e.aux = 0; e.s = 0.0; e.s2 = 0.0; }
+  const uint32_t pa = __shfl_up_sync(0xffffffffu, e.a, 1), pb = __shfl_up_sync(0xffffffffu, e.b, 1);
+  int end;
+  rq_segment(lane == 0 || !valid || lane == n || pa != e.a || pb != e.b, lane, end);
+  const bool head = valid && (lane == 0 || pa != e.a || pb != e.b);
+  uint32_t w[8];
+  rq_widen(e.hlo, e.hhi, w);
+  uint32_t c01 = (e.cnt & 0xFFu) | ((e.cnt & 0xFF00u) << 8);         // voxels | thr0 << 16 (table layout)
+  uint32_t c23 = ((e.cnt >> 16) & 0xFFu) | ((e.cnt >> 24) << 16);     // thr1 | thr2 << 16
+  uint32_t kmin = e.kmin, kmax = e.kmax;
+  double s = e.s, s2 = e.s2;
+  RQ_SEG_BEGIN
+    RQ_SEG_ADD(c01) RQ_SEG_ADD(c23) RQ_SEG_ADD(s) RQ_SEG_ADD(s2)
+    RQ_SEG_ADD(w[0]) RQ_SEG_ADD(w[1]) RQ_SEG_ADD(w[2]) RQ_SEG_ADD(w[3]) RQ_SEG_ADD(w[4]) RQ_SEG_ADD(w[5]) RQ_SEG_ADD(w[6]) RQ_SEG_ADD(w[7])
+    RQ_SEG_MAX(kmin) RQ_SEG_MAX(kmax)
+  RQ_SEG_END
+  if (head) {
+    const uint32_t emask = (uint32_t)(P.edgeSlots - 1);
+    const unsigned long long key = ((unsigned long long)e.a << 32) | e.b;
+    int slot = -1;
+    uint32_t hsh = ((e.a * 0x9E3779B1u) ^ (e.b * 0x85EBCA77u)) >> 11 & emask;
+    for (int probe = 0; probe < 8; ++probe) {
+      unsigned long long cur = S.ekeys[hsh];
+      if (cur == EDGE_EMPTY) cur = atomicCAS(S.ekeys + hsh, EDGE_EMPTY, key);
+      if (cur == key || cur == EDGE_EMPTY) { slot = (int)hsh; break; }
+      hsh = (hsh + 1) & emask;
+    }
+    if (slot >= 0) {
+      atomicAdd(S.ecnt + 2 * slot, c01);
+      if (c23) atomicAdd(S.ecnt + 2 * slot + 1, c23);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (w[j]) atomicAdd(S.ehist + 8 * slot + j, w[j]);
+      atomicAdd(S.esum + 2 * slot, s); atomicAdd(S.esum + 2 * slot + 1, s2);
+      if (kmin) rq_smax(S.emx + 2 * slot, kmin);
+      if (kmax) rq_smax(S.emx + 2 * slot + 1, kmax);
+    } else {
+      const long long g = rq_edge_slot_global(P, key);
+      if (g >= 0) {
+        uint32_t* ga = P.edgeAdd + (size_t)g * P.edge.nAdd;
+        uint32_t* gm = P.edgeMax + (size_t)g * P.edge.nMax;
+        double* gf = P.edgeF64 + (size_t)g * P.edge.nF64;
+        atomicAdd(ga, c01 & 0xFFFFu);
+        if (P.nThr > 0 && (c01 >> 16)) atomicAdd(ga + 1, c01 >> 16);
+        if (P.nThr > 1 && (c23 & 0xFFFFu)) atomicAdd(ga + 2, c23 & 0xFFFFu);
+        if (P.nThr > 2 && (c23 >> 16)) atomicAdd(ga + 3, c23 >> 16);
+        uint32_t* gh = ga + 1 + P.nThr;
+        for (int j = 0; j < 8; ++j) {
+          if (w[j] & 0xFFFFu) atomicAdd(gh + 2 * j, w[j] & 0xFFFFu);
+          if (w[j] >> 16) atomicAdd(gh + 2 * j + 1, w[j] >> 16);
+        }
+        atomicAdd(gf, s); atomicAdd(gf + 1, s2);
+        if (kmin) atomicMax(gm + 0, kmin);
+        if (kmax) atomicMax(gm + 1, kmax);
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// after draining the first 32 entries: move the remaining rem (< 32) to the front
+__device__ __forceinline__ void rq_shift(RqEntry* q, int rem, int lane) {
+  RqEntry t;
+  if (lane < rem) t = q[32 + lane];
+  __syncwarp();
+  if (lane < rem) q[lane] = t;
   __syncwarp();
 }
 
@@ -239,8 +307,9 @@ voxel_pass_rq(const __grid_constant__ FastParams P) {
   const bool edgeLane = active && ((lane == 0 && vxm) || (lane == 31 && vxp));
   const int edgeOff = (lane == 0) ? -1 : 1;
   const uint32_t ltmask = (1u << lane) - 1u;
-  RqEntry* myq = S.queue + (size_t)warp * RQ_CAP;
-  int qn = 0;  // warp-uniform queue length
+  RqEntry* myq = S.queue + (size_t)warp * RQ_CAP;  // region runs
+  RqEntry* myqe = myq + 64;                         // boundary runs
+  int qn = 0, qe = 0;  // warp-uniform queue lengths
 
   uint32_t rLabel = 0, rCnt = 0, rHlo = 0, rHhi = 0, rKmin = 0, rKmax = 0; int rZmin = 0, rZmax = -1; double rS = 0.0, rS2 = 0.0;
   uint32_t eA = 0, eB = 0, eCnt = 0, eHlo = 0, eHhi = 0, eKmin = 0, eKmax = 0; double eS = 0.0, eS2 = 0.0;
@@ -252,7 +321,7 @@ voxel_pass_rq(const __grid_constant__ FastParams P) {
         (rZmax >= 0 ? (uint32_t)(rZmin - z0) | ((uint32_t)(rZmax - z0) << 8) | 0x10000u : 0u) | ((uint32_t)lane << 24)); \
     *((double2*)d_ + 2) = make_double2(rS, rS2); }
 #define RQ_PUSH_EDGE(pos)                                                                                    \
-  { RqEntry* d_ = myq + (pos);                                                                                \
+  { RqEntry* d_ = myqe + (pos);                                                                               \
     *(uint4*)d_ = make_uint4(eA, eB, eCnt, eHlo);                                                             \
     *((uint4*)d_ + 1) = make_uint4(eHhi, eKmin, eKmax, 0u);                                                   \
     *((double2*)d_ + 2) = make_double2(eS, eS2); }
@@ -317,8 +386,8 @@ voxel_pass_rq(const __grid_constant__ FastParams P) {
       // ---- directed boundary run (me -> nb); voxels that are not boundary voxels do not end it
       const bool endE = found && eCnt != 0 && (eA != me || eB != nb || (eCnt & 0xFFu) >= 15u);
       const uint32_t mE = __ballot_sync(0xffffffffu, endE);
-      if (endE) { RQ_PUSH_EDGE(qn + __popc(mE & ltmask)); eCnt = 0; }
-      qn += __popc(mE);
+      if (endE) { RQ_PUSH_EDGE(qe + __popc(mE & ltmask)); eCnt = 0; }
+      qe += __popc(mE);
       if (found) {
         if (eCnt == 0) { eA = me; eB = nb; eHlo = eHhi = 0; eKmin = eKmax = 0; eS = 0.0; eS2 = 0.0; }
         eCnt += 1u | ((P.nThr > 0 && pv >= P.thr_up[0]) ? 0x100u : 0u) | ((P.nThr > 1 && pv >= P.thr_up[1]) ? 0x10000u : 0u) |
@@ -327,7 +396,8 @@ voxel_pass_rq(const __grid_constant__ FastParams P) {
         eS += dv; eS2 += dv2;
         if (notNan) { eKmin = max(eKmin, ~kord); eKmax = max(eKmax, kord); }
       }
-      if (qn >= 32) { rq_drain(P, S, myq, qn, lane, x0warp, gy, z0); qn = 0; }
+      if (qn >= 32) { rq_drain_regions(P, S, myq, 32, lane, x0warp, gy, z0); qn -= 32; rq_shift(myq, qn, lane); }
+      if (qe >= 32) { rq_drain_edges(P, S, myqe, 32, lane); qe -= 32; rq_shift(myqe, qe, lane); }
       lm = l0; l0 = lp; lp = nlp; ym = nym; yp = nyp; xe = nxe; pv = npv;
     }
     // close the open runs and drain
@@ -335,9 +405,10 @@ voxel_pass_rq(const __grid_constant__ FastParams P) {
     if (rCnt != 0) RQ_PUSH_REGION(qn + __popc(mR & ltmask));
     qn += __popc(mR);
     const uint32_t mE = __ballot_sync(0xffffffffu, eCnt != 0);
-    if (eCnt != 0) RQ_PUSH_EDGE(qn + __popc(mE & ltmask));
-    qn += __popc(mE);
-    rq_drain(P, S, myq, qn, lane, x0warp, gy, z0);
+    if (eCnt != 0) RQ_PUSH_EDGE(qe + __popc(mE & ltmask));
+    qe += __popc(mE);
+    for (int o = 0; o < qn; o += 32) rq_drain_regions(P, S, myq + o, min(32, qn - o), lane, x0warp, gy, z0);
+    for (int o = 0; o < qe; o += 32) rq_drain_edges(P, S, myqe + o, min(32, qe - o), lane);
   }
   __syncthreads();
   // ---- flush the CTA's tables into the global records
