@@ -147,11 +147,24 @@ __device__ double* push_region(const FeatCfg& F, const ShapeFeat& s, const RR& r
 template <class RX, class RY, class RZ, class BX, class BY, class BZ, class PB>
 __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, const RZ& rz,
                               const BX& bx, const BY& by, const BZ& bz, const PB& pb,
-                              const double* sal, double* out) {
+                              const double* sal, double* out, int part = -1) {
+  // part: -1 = whole row; 0 = x0 (pair terms), 1 / 2 = first / second region block, 3 = merged block.
+  // The four parts write disjoint ranges, so four threads can build one row (merge_order.cu).
   ShapeFeat sx, sy, sz;
   shape_feat(F, rx, bx, sx);
   shape_feat(F, ry, by, sy);
-  shape_feat(F, rz, bz, sz);
+  if (part < 0 || part == 3) shape_feat(F, rz, bz, sz);
+  if (part > 0) {
+    if (F.simple) return;
+    const bool sw = sx.area > sy.area;
+    const int xi = F.D + 4 + 2 * F.nThr + 5 * F.nR + F.nRL + 5 * F.nB + (sal ? 1 : 0);
+    const int x0len = F.dim + (sal ? 5 : 0) - 3 * xi;
+    double* q = out + x0len + (size_t)(part - 1) * xi;
+    if (part == 1) { if (sw) push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, q); else push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, q); }
+    else if (part == 2) { if (sw) push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, q); else push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, q); }
+    else push_region(F, sz, rz, bz, sal ? sal + 2 : nullptr, q);
+    return;
+  }
   const bool swp = sx.area > sy.area;
   const ShapeFeat& s1 = swp ? sy : sx;
   const ShapeFeat& s2 = swp ? sx : sy;
@@ -228,6 +241,7 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
     *p++ = d02 < d12 ? d02 : d12;
     *p++ = d02 < d12 ? d12 : d02;
   }
+  if (part == 0) return;
   if (swp) {
     p = push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, p);
     p = push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, p);

@@ -18,6 +18,7 @@
 #include <set>
 #include <unordered_map>
 #include <vector>
+#include <chrono>
 #include "featurize.cuh"
 
 int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
@@ -29,21 +30,27 @@ namespace glia {
 
 struct __align__(16) RfNode16 { double thr; int left; int feat; };  // == RfNode (rf.cu)
 
-// One warp per candidate.  Lane 0 builds the feature row from the six staged records (region
-// X, Y; boundary-of X, Y, Z; pair boundary), then the 32 lanes split the trees of the forest.
-__global__ void __launch_bounds__(128)
+// One CTA per candidate.  Four threads (one per warp) build the four parts of the feature row from the
+// six staged records (region X, Y; boundary-of X, Y, Z; pair boundary); the row is then staged in shared memory and every thread walks
+// its own trees of the forest: the chain of a merge is latency-bound (m is tens of candidates, a walk is
+// ~20 dependent L2 loads), so the trees of one candidate are spread over 256 threads, not 32.
+#define MERGE_TPB 256
+__global__ void __launch_bounds__(MERGE_TPB)
 merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __restrict__ stage,
                    int stageWords, const RfNode16* __restrict__ nodes,
                    const int* __restrict__ treeOff, const RfDist dist, int labelIdx,
                    double* __restrict__ rows, double* __restrict__ sal) {
-  int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  extern __shared__ __align__(16) double srow[];
+  __shared__ int shits;
+  const int w = blockIdx.x;
   if (w >= m) return;
   const RecLayout LR = F.reg, LE = F.edge;
   const int regW = LR.nAdd + LR.nMax + ((LR.nAdd + LR.nMax) & 1) + 2 * LR.nF64;
   const int edgeW = LE.nAdd + LE.nMax + ((LE.nAdd + LE.nMax) & 1) + 2 * LE.nF64;
   const uint32_t* base = stage + (size_t)w * stageWords;
   double* row = rows + (size_t)w * F.dim;
-  if (lane == 0) {
+  if (threadIdx.x == 0) shits = 0;
+  if ((threadIdx.x & 31) == 0 && threadIdx.x < 128) {  // four warps, one part of the row each
     auto regRec = [&](int k) {
       const uint32_t* p = base + (size_t)k * regW;
       return RecSingle{p, p + LR.nAdd, (const double*)(p + LR.nAdd + LR.nMax + ((LR.nAdd + LR.nMax) & 1))};
@@ -54,22 +61,27 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
     };
     RecSingle rx = regRec(0), ry = regRec(1);
     RecSum2 rz{rx, ry};
-    featurize_row(F, rx, ry, rz, edgeRec(0), edgeRec(1), edgeRec(2), edgeRec(3), nullptr, row);
+    featurize_row(F, rx, ry, rz, edgeRec(0), edgeRec(1), edgeRec(2), edgeRec(3), nullptr, row,
+                  F.simple ? (threadIdx.x == 0 ? -1 : 4) : (int)(threadIdx.x >> 5));
   }
-  __syncwarp();
+  __syncthreads();
+  for (int i = threadIdx.x; i < F.dim; i += MERGE_TPB) srow[i] = row[i];
+  __syncthreads();
   int hits = 0;
-  const int mdl = dist.pick(row), tb = dist.begin(mdl), ntree = dist.end(mdl) - tb;  // alg/rf.hxx:97-98
-  for (int t = tb + lane; t < tb + ntree; t += 32) {
+  const int mdl = dist.pick(srow), tb = dist.begin(mdl), ntree = dist.end(mdl) - tb;  // alg/rf.hxx:97-98
+  for (int t = tb + (int)threadIdx.x; t < tb + ntree; t += MERGE_TPB) {
     int k = treeOff[t];
     RfNode16 nd = nodes[k];
     while (nd.feat >= 0) {
-      k = nd.left + (row[nd.feat] <= nd.thr ? 0 : 1);
+      k = nd.left + (srow[nd.feat] <= nd.thr ? 0 : 1);
       nd = nodes[k];
     }
     hits += (nd.left == labelIdx);
   }
   for (int o = 16; o; o >>= 1) hits += __shfl_xor_sync(0xffffffffu, hits, o);
-  if (lane == 0) sal[w] = (double)hits / (double)ntree;
+  if ((threadIdx.x & 31) == 0 && hits) atomicAdd(&shits, hits);
+  __syncthreads();
+  if (threadIdx.x == 0) sal[w] = (double)shits / (double)ntree;
 }
 
 }  // namespace glia
@@ -251,6 +263,9 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
 
   int M = 0;
   int nextId = R;
+  const bool trace = getenv("GLIA_B200_TRACE") != nullptr;
+  double tBook = 0.0, tStage = 0.0, tDev = 0.0, tIns = 0.0;
+  auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   std::vector<uint32_t> best1, best2; std::vector<int> owner1;
   auto top2 = [&](int X) {  // per max word: best, its owning neighbour (-1: non-mutual), second best
     best1.assign(LE.nMax, 0); best2.assign(LE.nMax, 0); owner1.assign(LE.nMax, -2);
@@ -265,6 +280,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     for (int e : G.nmOut[X]) feed(G.sMax.data() + (size_t)e * LE.nMax, -1);
   };
   while (!table.empty()) {
+    const double tA = trace ? now() : 0.0;
     // top: largest saliency, among equals the most recently inserted (boundary_table.hxx:47-52)
     QKey q = *queue.rbegin();
     Key k01 = std::get<2>(q);
@@ -327,6 +343,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       cudaError_t e = ensure_batch(m);
       if (e != cudaSuccess) { h->err = std::string("merge_order_bc batch buffers: ") + cudaGetErrorString(e); return GLIA_E_CUDA; }
     }
+    const double tB = trace ? now() : 0.0;
     // ---- stage the six records of every new candidate (X = W, Y = r2)
     std::unordered_map<int, std::vector<int>> nmByTarget;
     for (int e : G.nmOut[r2]) { int t = G.cur(G.eb[e]); if (t != r2) nmByTarget[t].push_back(e); }
@@ -351,13 +368,15 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       if (nt != nmByTarget.end()) for (int e : nt->second) if (G.active(G.eb[e], W)) pb.merge(G.edgeRec(e));
       put_rec(p, bx); put_rec(p, by); put_rec(p, bzz); put_rec(p, pb);
     }
+    const double tC = trace ? now() : 0.0;
     CK(cudaMemcpyAsync(dStage, hStage, 4 * m * stageWords, cudaMemcpyHostToDevice, st));
-    merge_batch_kernel<<<(unsigned)((m * 32 + 127) / 128), 128, 0, st>>>(
+    merge_batch_kernel<<<(unsigned)m, MERGE_TPB, 8 * (size_t)dim, st>>>(
         h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, dSal);
     h->launches++;
     CK(cudaMemcpyAsync(hSal, dSal, 8 * m, cudaMemcpyDeviceToHost, st));
     if (rows) CK(cudaMemcpyAsync(hRows, dRows, 8 * m * dim, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    const double tD = trace ? now() : 0.0;
     nfeat += (long long)m;
     for (size_t j = 0; j < m; ++j) {
       Item it; it.sal = hSal[j]; it.seq = seq++;
@@ -366,7 +385,11 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       queue.insert(QKey(it.sal, it.seq, k));
       table.emplace(k, std::move(it));
     }
+    if (trace) { const double tE = now(); tBook += tB - tA; tStage += tC - tB; tDev += tD - tC; tIns += tE - tD; }
   }
+  if (trace)
+    fprintf(stderr, "[glia_b200] merge_order_bc: %d merges, %lld candidates | bookkeeping %.3f s, staging %.3f s, device round trips %.3f s, queue inserts %.3f s\n",
+            M, nfeat, tBook, tStage, tDev, tIns);
   if (n_merges) *n_merges = M;
   if (n_featurized) *n_featurized = nfeat;
   return GLIA_OK;
