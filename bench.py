@@ -63,6 +63,8 @@ RF_SWEEP = dict(n=10_000_000, d=50, ntree=255, desc="RF scoring sweep: 255-tree 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE voxel_pass_fast launch, from the committed
 # `ncu --set full` captures (profiles/r1_final_ncu_c2.txt, profiles/r1_v3_ncu_c4s.txt); None = not captured
 VOXEL_PASS_TRAFFIC = {"c2": 298.95e6 + 81.93e6, "c4s": 1.884e9 + 0.378e9}
+# the same for ONE rf_score_smem_kernel launch (profiles/r1_final_ncu_c2.txt)
+RF_SCORE_TRAFFIC = {"c2": 233.58e6 + 5.10e6}
 
 
 def load_peaks():
@@ -418,8 +420,18 @@ def main():
             dist.destroy_process_group()
         return 0
     peak, peak_src = load_peaks()
-    alg_bytes = 8.0 * nvox  # label u32 + pb f32 read once
-    achieved = alg_bytes / (kern_ms[0] * 1e-3) / 1e9
+    # SURVEY §8d.  Voxel pass: label u32 + pb f32 read once.  RF scoring: 8*D + 8 bytes per candidate (row in,
+    # probability out) + the forest once (16-byte nodes).  "roofline" is the kernel with the longer launch in
+    # this run (RF scoring at C2, the voxel pass in 3D); "roofline_kernels" carries both.
+    def roof(kernel, alg, ms, traffic):
+        a = alg / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        return {"bound": "hbm", "kernel": kernel, "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
+                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
+                "launch_ms": ms}
+    roofs = [roof("voxel_pass_fast", 8.0 * nvox, kern_ms[0], VOXEL_PASS_TRAFFIC.get(args.workload)),
+             roof("rf_score_smem_kernel", float(Cn) * (8 * dim + 8) + 16.0 * float(forest_arrays["ndbigtree"].sum()),
+                  kern_ms[3], RF_SCORE_TRAFFIC.get(args.workload))]
+    dominant = max(roofs, key=lambda r: r["launch_ms"])
     line = {"metric": "Mvoxels/s, labels+pb -> scored initial merge candidates", "value": value, "unit": "Mvoxels/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -432,9 +444,7 @@ def main():
             "candidates_per_s": cands_all / (elapsed_ms * 1e-3),
             "stage_ms": {"table_init": kern_ms[4], "voxel_pass": kern_ms[0], "graph": kern_ms[1], "featurize": kern_ms[2],
                          "rf_score": kern_ms[3]},
-            "roofline": {"bound": "hbm", "kernel": "voxel_pass_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": VOXEL_PASS_TRAFFIC.get(args.workload), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes},
+            "roofline": dominant, "roofline_kernels": roofs,
             "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
     if not args.no_cpu_baseline and world == 1:
         r = cpu_reference(args.workload, forest_arrays, 1, 0)

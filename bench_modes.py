@@ -82,6 +82,7 @@ def run_slab(args, rank, world, local_rank, dist):
         step()
     launches0 = b.launch_count()
     acc = dict(voxel_ms=0.0, exchange_ms=0.0, graph_ms=0.0)
+    detail = {}
     feat_ms = rf_ms = 0.0
     sent = 0
     barrier()
@@ -93,6 +94,8 @@ def run_slab(args, rank, world, local_rank, dist):
         step(tm)
         for k in acc:
             acc[k] += tm[k]
+        for k, v in tm["exchange_detail_ms"].items():
+            detail[k] = detail.get(k, 0.0) + v
         sent += tm["sent_records"] * tm["record_bytes"]
         ms = b.last_ms()
         feat_ms += ms[2]; rf_ms += ms[3]
@@ -149,6 +152,7 @@ def run_slab(args, rank, world, local_rank, dist):
                 "stage_ms_rank0": {"voxel_pass+table_init": acc["voxel_ms"] / args.steps,
                                    "exchange": acc["exchange_ms"] / args.steps, "graph": acc["graph_ms"] / args.steps,
                                    "featurize": feat_ms / args.steps, "rf_score": rf_ms / args.steps},
+                "exchange_detail_ms_rank0": {k: v / args.steps for k, v in detail.items()},
                 "exchange_bytes_per_step": sent_all,
                 "roofline": {"bound": "hbm", "kernel": "voxel_pass_fast", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,

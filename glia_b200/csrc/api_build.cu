@@ -154,7 +154,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       const bool useRuns = vsel && vsel[0] == 'r';
       const bool useRq = vsel && vsel[0] == 'q';  // GLIA_B200_VOXEL=queue: v5 run queue (voxel_rq.cu), experimental
       const char* tzs = getenv("GLIA_B200_TZ");
-      F.TZ = tzs ? atoi(tzs) : (useRuns ? (P.ndim == 3 ? 64 : 32) : 32);
+      F.TZ = tzs ? atoi(tzs) : (useRuns ? (P.ndim == 3 ? 64 : 32) : (useRq ? 32 : 16));
       if (F.TZ < 1) F.TZ = 32;
       F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);
       F.tilesY = (P.Y + F.warpsY - 1) / F.warpsY;
@@ -173,7 +173,10 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.regAdd = P.regAdd; F.regMax = P.regMax; F.regF64 = P.regF64;
       F.edgeCap = P.edgeCap; F.edgeKeys = P.edgeKeys; F.edgeAdd = P.edgeAdd; F.edgeMax = P.edgeMax; F.edgeF64 = P.edgeF64;
       F.overflow = P.overflow;
-      F.regSlots = 128; F.edgeSlots = 512;
+      // v3: 256 boundary slots + 16-plane tiles keep a CTA at 54 KB / 62 registers -> 4 CTAs per SM
+      // (profiles/r1_v4_notes.txt, "occupancy"); the experimental kernels keep the sizes they were measured with
+      F.regSlots = 128;
+      F.edgeSlots = getenv("GLIA_B200_ESLOTS") ? atoi(getenv("GLIA_B200_ESLOTS")) : ((useRuns || useRq) ? 512 : 256);
       for (int k = 0; k < nChunks; ++k) {
         if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));
         F.zBegin = zCut[k]; F.zEnd = zCut[k + 1];

@@ -83,8 +83,8 @@ __device__ __forceinline__ double rf_lds(uint32_t a) {
 // threads share a candidate and split the trees, two trees in flight per thread; sibling pairs
 // are 32-byte aligned so that one L2 sector serves either outcome of a split.
 #define RF_CPB 64
-template <bool ENS>  // ENS: model ensemble, the tree range depends on the row (alg/rf.hxx:97-98)
-__global__ void __launch_bounds__(256)
+template <bool ENS, int NS>  // NS: tree slices per candidate (CTA = 64 * NS threads); ENS: model ensemble, the tree range depends on the row (alg/rf.hxx:97-98)
+__global__ void __launch_bounds__(64 * NS, NS == 8 ? 3 : 6)
 rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, const RfDist dist,
                      int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
                      double* __restrict__ prob) {
@@ -122,15 +122,15 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
     const uint32_t xs = spin[0] + 8u * (uint32_t)(cand * ldRow);
     const int4* np = reinterpret_cast<const int4*>(spin64[0]);
     int t = tbeg + slice;
-    for (; t + 12 < ntree; t += 16) {  // four trees in flight
-      int4 na = rf_node(np, __ldg(treeOff + t)), nb = rf_node(np, __ldg(treeOff + t + 4));
-      int4 nc = rf_node(np, __ldg(treeOff + t + 8)), nd = rf_node(np, __ldg(treeOff + t + 12));
+    for (; t + 3 * NS < ntree; t += 4 * NS) {  // four trees in flight
+      int4 na = rf_node(np, __ldg(treeOff + t)), nb = rf_node(np, __ldg(treeOff + t + NS));
+      int4 nc = rf_node(np, __ldg(treeOff + t + 2 * NS)), nd = rf_node(np, __ldg(treeOff + t + 3 * NS));
       while ((na.w & nb.w & nc.w & nd.w) >= 0) {  // some walk still on an internal node (leaf: sign bit)
         RF_STEP_P(na) RF_STEP_P(nb) RF_STEP_P(nc) RF_STEP_P(nd)
       }
       hits += (na.x == labelIdx) + (nb.x == labelIdx) + (nc.x == labelIdx) + (nd.x == labelIdx);
     }
-    for (; t < ntree; t += 4) {
+    for (; t < ntree; t += NS) {
       int4 nd = rf_node(np, __ldg(treeOff + t));
       while (nd.w >= 0) RF_STEP_P(nd)
       hits += (nd.x == labelIdx);
@@ -477,15 +477,22 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
     if (smem <= 200 * 1024) {
       static bool attr = false;
       if (!attr) {
-        cudaFuncSetAttribute(rf_score_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        cudaFuncSetAttribute(rf_score_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(rf_score_smem_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(rf_score_smem_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(rf_score_smem_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr = true;
       }
       const unsigned nb = (unsigned)((N + RF_CPB - 1) / RF_CPB);
+      // wide rows leave room for only 3-4 CTAs of staged rows per SM: spread a candidate's trees over 8 warps
+      // instead of 4 so that the SM still holds 64 warps (C2: 0.91 -> 0.69 ms, profiles/r1_rf_v4_notes.txt)
+      static const int nsEnv = getenv("GLIA_B200_RF_NS") ? atoi(getenv("GLIA_B200_RF_NS")) : 0;
+      const int ns = nsEnv ? nsEnv : (smem > 28 * 1024 ? 8 : 4);
       if (m->dist.n > 1)
-        rf_score_smem_kernel<true><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+        rf_score_smem_kernel<true, 4><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+      else if (ns == 8)
+        rf_score_smem_kernel<false, 8><<<nb, 512, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
       else
-        rf_score_smem_kernel<false><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+        rf_score_smem_kernel<false, 4><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
     } else {
       rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist,
                                                      m->nclass, labelIdx, dX, N, D, nullptr, dProb);

@@ -20,6 +20,7 @@
 //    (8.7 of 32 lanes active on average, 1195 warp-instructions per 32 voxels:
 //    profiles/r1_v2_ncu_voxel_fast.txt); the queue turns that into convergent work.
 //  * The CTA's tables are flushed once per tile into the global records with RED atomics.
+#include <cstdlib>
 #include "voxel_fast.cuh"
 
 namespace glia {
@@ -168,7 +169,8 @@ __device__ __forceinline__ void drain_queue(const SmemView& S, int warp, int lan
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(256)
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB)
 voxel_pass_fast(const __grid_constant__ FastParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x;
@@ -376,11 +378,14 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
 
 cudaError_t launch_voxel_pass_fast(const FastParams& P, cudaStream_t st) {
   size_t smem = voxel_fast_smem_bytes(P);
-  cudaError_t e = cudaFuncSetAttribute(voxel_pass_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static const int minb = getenv("GLIA_B200_MINB") ? atoi(getenv("GLIA_B200_MINB")) : 4;
+  cudaError_t e = minb >= 4 ? cudaFuncSetAttribute(voxel_pass_fast<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                            : cudaFuncSetAttribute(voxel_pass_fast<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   long long tiles = (long long)P.tilesX * P.tilesY * P.tilesZ;
   if (tiles <= 0) return cudaSuccess;
-  voxel_pass_fast<<<(unsigned)tiles, 32 * P.warpsX * P.warpsY, smem, st>>>(P);
+  if (minb >= 4) voxel_pass_fast<4><<<(unsigned)tiles, 32 * P.warpsX * P.warpsY, smem, st>>>(P);
+  else voxel_pass_fast<3><<<(unsigned)tiles, 32 * P.warpsX * P.warpsY, smem, st>>>(P);
   return cudaGetLastError();
 }
 

@@ -71,13 +71,21 @@ class TorchComm:
         else:
             d.all_reduce(t, op=d.ReduceOp.SUM if op == "sum" else d.ReduceOp.MAX, group=self.group)
 
-    def all_to_all_v(self, send, counts):
-        """send: [sum(counts), rec] uint8 rows grouped by destination; returns the rows received."""
+    def all_gather_fixed(self, t):
+        """Concatenation over ranks of equally sized 1-D tensors."""
+        out = torch.empty((self.world * t.numel(),), dtype=t.dtype, device=t.device)
+        self.dist.all_gather_into_tensor(out, t, group=self.group)
+        return out
+
+    def all_to_all_v(self, send, counts, cout=None):
+        """send: [sum(counts), rec] uint8 rows grouped by destination; returns the rows received.
+        cout: rows to expect from each rank when the caller already knows them."""
         d = self.dist
-        cin = torch.tensor(counts, dtype=torch.int64, device=send.device)
-        cout = torch.empty_like(cin)
-        d.all_to_all_single(cout, cin, group=self.group)
-        cout = [int(x) for x in cout.tolist()]
+        if cout is None:
+            cin = torch.tensor(counts, dtype=torch.int64, device=send.device)
+            cout = torch.empty_like(cin)
+            d.all_to_all_single(cout, cin, group=self.group)
+            cout = [int(x) for x in cout.tolist()]
         recv = torch.empty((sum(cout), send.shape[1]), dtype=send.dtype, device=send.device)
         d.all_to_all_single(recv, send, output_split_sizes=cout, input_split_sizes=list(counts), group=self.group)
         return recv
@@ -142,7 +150,10 @@ class ThreadComm:
         self._sync(t)
         s.bar.wait()
 
-    def all_to_all_v(self, send, counts):
+    def all_gather_fixed(self, t):
+        return self.all_gather_v(t)
+
+    def all_to_all_v(self, send, counts, cout=None):
         s = self.s
         self._sync(send)
         s.slots[self.rank] = (send, list(counts))
@@ -196,35 +207,49 @@ def build_sharded(comm, b, labels, pb, mask=None, timings=None):
             e.record()
             ev.append(e)
 
+    # the library's launches and the collectives are ordered by the stream when the handle runs on torch's
+    # current stream (bench.py does); otherwise fence each hand-over
+    own_stream = not b.params.stream or b.params.stream != torch.cuda.current_stream(dev).cuda_stream
+
+    def fence():
+        if own_stream:
+            torch.cuda.synchronize(dev)
+
     mark()
     b.build_partial(labels, pb, mask)
     mark()
+    fence()
     (pa, na), (pm, nm), (pf, nf) = b.raw_region_tables()
     comm.all_reduce(dev_tensor(pa, na, torch.int32, dev), "sum")      # counts, histogram bins
     comm.all_reduce(dev_tensor(pm, nm, torch.int32, dev), "max_u32")  # bbox, min/max codes
     comm.all_reduce(dev_tensor(pf, nf, torch.float64, dev), "sum")    # sum v, sum v^2
-    torch.cuda.synchronize(dev)
+    fence()
+    mark()
     R = b.finalize_regions()
     pi, ni = b.edge_interest(comm.world)
+    fence()
     comm.all_reduce(dev_tensor(pi, ni, torch.uint8, dev), "max")
-    torch.cuda.synchronize(dev)
+    fence()
+    mark()
     # reduce keyed by label pair: every rank keeps its own records and merges what the others send; if the
     # merged set would not fit some rank's table (labels far from spatial order) all ranks repeat the exchange
-    # with their own records included and rebuild (and grow) the tables from the received runs
+    # with their own records included and rebuild (and grow) the tables from the received runs.  One small
+    # all-gather carries every rank's send counts and table load, so all ranks size their receive buffers
+    # and take the same decision without a second collective.
     rebuild = bool(os.environ.get("GLIA_B200_FORCE_REBUILD"))  # test hook: take the fallback path
     for attempt in range(2):
         counts, pe, rec = b.export_edges(comm.world, -1 if rebuild else comm.rank)
-        send = dev_tensor(pe, sum(counts) * rec, torch.uint8, dev).view(-1, rec)
-        recv = comm.all_to_all_v(send, counts)
-        torch.cuda.synchronize(dev)
-        if rebuild:
-            break
         occ, cap = b.table_load()
-        flag = torch.tensor([1 if (occ + recv.shape[0]) * 10 > cap * 8 else 0], dtype=torch.int32, device=dev)
-        comm.all_reduce(flag, "max")
-        if int(flag.item()) == 0:
+        info = comm.all_gather_fixed(torch.tensor(list(counts) + [occ, cap], dtype=torch.int64, device=dev))
+        info = info.view(comm.world, comm.world + 2).tolist()
+        cout = [int(info[r][comm.rank]) for r in range(comm.world)]
+        send = dev_tensor(pe, sum(counts) * rec, torch.uint8, dev).view(-1, rec)
+        if rebuild or not any((row[comm.world] + sum(info[r][q] for r in range(comm.world))) * 10 > row[comm.world + 1] * 8
+                              for q, row in enumerate(info)):
+            recv = comm.all_to_all_v(send, counts, cout)
             break
         rebuild = True
+    fence()
     mark()
     b.import_edges(recv.data_ptr() if recv.numel() else 0, recv.shape[0], rebuild)
     lo, hi = owner_range(R, comm.world, comm.rank)
@@ -232,7 +257,9 @@ def build_sharded(comm, b, labels, pb, mask=None, timings=None):
     mark()
     if timings is not None:
         torch.cuda.synchronize(dev)
-        timings.update(voxel_ms=ev[0].elapsed_time(ev[1]), exchange_ms=ev[1].elapsed_time(ev[2]),
-                       graph_ms=ev[2].elapsed_time(ev[3]), sent_records=int(sum(counts)),
-                       record_bytes=rec)
+        dt = [ev[i].elapsed_time(ev[i + 1]) for i in range(len(ev) - 1)]
+        timings.update(voxel_ms=dt[0], exchange_ms=dt[1] + dt[2] + dt[3], graph_ms=dt[4],
+                       exchange_detail_ms={"region_tables_all_reduce": dt[1], "regions+interest": dt[2],
+                                           "boundary_records_all_to_all": dt[3]},
+                       sent_records=int(sum(counts)), record_bytes=rec)
     return b

@@ -155,6 +155,28 @@ def test_rf_votes_bit_exact():
     assert vg.sum(axis=1).min() == 255 and vg.sum(axis=1).max() == 255
 
 
+def test_rf_probability_kernel_nan_inf_and_stump_trees():
+    """The probability-only path (rows staged in shared memory, walk-encoded nodes; the one the handle's
+    score_candidates and the C5 sweep use) against the oracle: rows with NaN / +-inf (NaN compares false, so
+    it goes right: alg/rf.hxx:35-36 -> classForest), rows on thresholds, trees that are a single leaf, and
+    row counts that do not fill the last block of 64."""
+    rng = np.random.default_rng(11)
+    D = 23
+    for n, depth in ((1, 9), (63, 0), (64, 5), (4097, 16)):
+        X = rng.random((n, D))
+        f = synth.random_forest(37, D, max_depth=depth, seed=n, thr_pool=X[: max(1, n // 2)], leaf_prob=0.2)
+        X[rng.random((n, D)) < 0.05] = np.nan
+        X[rng.random((n, D)) < 0.02] = np.inf
+        X[rng.random((n, D)) < 0.02] = -np.inf
+        orf = ol.OracleRF.from_arrays(f, D)
+        grf = api.Forest.from_arrays(f, D)
+        vo, po = orf.predict(X)
+        _, pg = grf.predict(X, want_votes=False)
+        vg, pg2 = grf.predict(X)
+        assert np.array_equal(po, pg), (n, depth)
+        assert np.array_equal(vo, vg) and np.array_equal(po, pg2)
+
+
 def test_rf_model_file_roundtrip(tmp_path):
     f = synth.random_forest(17, 9, max_depth=7, seed=2, nclass=3, orig_labels=(-1, 1, 4))
     orf = ol.OracleRF.from_arrays(f, 9)

@@ -69,6 +69,12 @@ def _exercise(comm, out):
     recv = comm.all_to_all_v(send, [int(c) for c in counts[r]]).numpy().view(np.int32).reshape(-1, 3)
     exp = [(s, r, j) for s in range(world) for j in range(counts[s, r])]
     assert [tuple(x) for x in recv.tolist()] == exp
+    # the same exchange when the receive counts are already known (build_sharded gathers them with the table load)
+    info = comm.all_gather_fixed(torch.tensor([int(c) for c in counts[r]] + [r], dtype=torch.int64))
+    info = info.view(world, world + 1).tolist()
+    assert [row[:world] for row in info] == counts.tolist() and [row[world] for row in info] == list(range(world))
+    recv2 = comm.all_to_all_v(send, [int(c) for c in counts[r]], [int(info[s][r]) for s in range(world)])
+    assert [tuple(x) for x in recv2.numpy().view(np.int32).reshape(-1, 3).tolist()] == exp
     g = comm.all_gather_v(torch.arange(r + 1, dtype=torch.int64) + 10 * r)
     assert g.tolist() == [10 * s + i for s in range(world) for i in range(s + 1)]
     comm.barrier()
