@@ -61,10 +61,10 @@ RF_SWEEP = dict(n=10_000_000, d=50, ntree=255, desc="RF scoring sweep: 255-tree 
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE voxel_pass_fast launch, from the committed
-# `ncu --set full` captures (profiles/r1_final_ncu_c2.txt, profiles/r1_v3_ncu_c4s.txt); None = not captured
-VOXEL_PASS_TRAFFIC = {"c2": 298.95e6 + 81.93e6, "c4s": 1.884e9 + 0.378e9}
-# the same for ONE rf_score_smem_kernel launch (profiles/r1_final_ncu_c2.txt)
-RF_SCORE_TRAFFIC = {"c2": 233.58e6 + 5.10e6}
+# `ncu --set full` captures (profiles/r1_end_ncu_c2.txt, profiles/r1_v3_ncu_c4s.txt); None = not captured
+VOXEL_PASS_TRAFFIC = {"c2": 299.82e6 + 81.76e6, "c4s": 1.884e9 + 0.378e9}
+# the same for ONE rf_score_smem_kernel launch (profiles/r1_end_ncu_c2.txt)
+RF_SCORE_TRAFFIC = {"c2": 233.01e6 + 4.95e6}
 
 
 def load_peaks():
@@ -370,7 +370,7 @@ def main():
         # two slices in flight per GPU (two handles, each with its own stream, driven by two host
         # threads): the upload of slice i+1 overlaps graph/featurise/RF of slice i.  Every step still
         # copies its inputs from pinned host memory and reads its saliencies back.
-        nin = 2 if 16 * nvox <= 4 * 2 ** 30 else 1
+        nin = int(os.environ.get("GLIA_BENCH_INFLIGHT", "2")) if 16 * nvox <= 4 * 2 ** 30 else 1
         host = []
         for j in range(nin):
             hl = torch.empty(nvox, dtype=torch.int32).pin_memory()
@@ -380,7 +380,7 @@ def main():
             host.append((hln, hpn, new_builder(hpn, False),
                          torch.empty(int(Cn * 1.5) + 64, dtype=torch.float64).pin_memory().numpy(), hl, hp))
         n_e2e = max(2, min(args.steps, 6))
-        n_e2e += n_e2e % nin
+        n_e2e = (n_e2e + nin - 1) // nin * nin
         for hln, hpn, hb, hsal, _, _ in host:
             for i in range(2):
                 hb.build(hln, hpn); hb.score_candidates(forest, hsal)
