@@ -140,7 +140,8 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
     const char* force = getenv("GLIA_B200_FORCE_GENERIC");
     const bool fast = !(force && force[0] == '1') && !P.mask && prm.n_rimg == 1 && prm.n_rlimg == 0 &&
                       prm.n_bimg == 1 && prm.n_thr <= 3 && h->vc.reg[0].data == P.pb &&
-                      h->vc.edge[0].data == P.pb && h->vc.reg[0].bins <= 16 && h->vc.edge[0].bins <= 16;
+                      h->vc.edge[0].data == P.pb && h->vc.reg[0].bins <= 16 && h->vc.edge[0].bins <= 16 &&
+                      (long long)P.X * P.Y * 4 < (1ll << 31);  // tile-relative voxel offsets are 32-bit
     h->usedFast = fast;
     if (fast) {
       FastParams F;
@@ -156,6 +157,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       const char* tzs = getenv("GLIA_B200_TZ");
       F.TZ = tzs ? atoi(tzs) : (useRuns ? (P.ndim == 3 ? 64 : 32) : (useRq ? 32 : 16));
       if (F.TZ < 1) F.TZ = 32;
+      while (F.TZ > 1 && (long long)P.X * P.Y * (F.TZ + 3) >= (1ll << 31)) F.TZ >>= 1;
       F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);
       F.tilesY = (P.Y + F.warpsY - 1) / F.warpsY;
       F.tilesZ = (P.zEnd - P.zBegin + F.TZ - 1) / F.TZ;

@@ -117,13 +117,14 @@ __device__ __forceinline__ SmemView carve(unsigned char* raw, const FastParams& 
   SmemView S;
   unsigned char* p = raw;
   S.queue = (QEntry*)p; p += sizeof(QEntry) * QCAP * nwarps;
+  // keys (filled with ones) first, then everything that starts at zero: one vectorised fill each
   S.ekeys = (unsigned long long*)p; p += 8 * (size_t)P.edgeSlots;
+  S.rkeys = (uint32_t*)p; p += 4 * (size_t)P.regSlots;
   S.esum = (double*)p; p += 16 * (size_t)P.edgeSlots;
   S.rsum = (double*)p; p += 16 * (size_t)P.regSlots;
   S.ecnt = (uint32_t*)p; p += 8 * (size_t)P.edgeSlots;
   S.ehist = (uint32_t*)p; p += 32 * (size_t)P.edgeSlots;
   S.emx = (uint32_t*)p; p += 8 * (size_t)P.edgeSlots;
-  S.rkeys = (uint32_t*)p; p += 4 * (size_t)P.regSlots;
   S.rcnt = (uint32_t*)p; p += 4 * (size_t)P.regSlots;
   S.rhist = (uint32_t*)p; p += 32 * (size_t)P.regSlots;
   S.rmx = (uint32_t*)p; p += 32 * (size_t)P.regSlots;
@@ -175,10 +176,14 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x;
   const SmemView S = carve(smem_raw, P, nthreads >> 5);
-  for (int i = tid; i < P.edgeSlots; i += nthreads) { S.ekeys[i] = EDGE_EMPTY; S.esum[2 * i] = 0.0; S.esum[2 * i + 1] = 0.0; S.ecnt[2 * i] = 0; S.ecnt[2 * i + 1] = 0; S.emx[2 * i] = 0; S.emx[2 * i + 1] = 0; }
-  for (int i = tid; i < P.edgeSlots * 8; i += nthreads) S.ehist[i] = 0;
-  for (int i = tid; i < P.regSlots; i += nthreads) { S.rkeys[i] = 0xFFFFFFFFu; S.rcnt[i] = 0; S.rsum[2 * i] = 0.0; S.rsum[2 * i + 1] = 0.0; }
-  for (int i = tid; i < P.regSlots * 8; i += nthreads) { S.rhist[i] = 0; S.rmx[i] = 0; }
+  {  // slot counts are multiples of 4, so both blocks are whole 16-byte words (carve)
+    uint4* ones = reinterpret_cast<uint4*>(S.ekeys);
+    const int nOnes = (8 * P.edgeSlots + 4 * P.regSlots) >> 4;
+    for (int i = tid; i < nOnes; i += nthreads) ones[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+    uint4* zeros = reinterpret_cast<uint4*>(S.esum);
+    const int nZeros = (64 * P.edgeSlots + 84 * P.regSlots) >> 4;
+    for (int i = tid; i < nZeros; i += nthreads) zeros[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
   if (tid < 32) S.qn[tid] = 0;
   if (tid < 16) { S.sRB[tid] = P.rBound[tid]; S.sEB[tid] = P.eBound[tid]; }
   __syncthreads();
@@ -210,28 +215,32 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
   int eCur = -1; double eS = 0.0, eS2 = 0.0; uint32_t eKmin = 0, eKmax = 0;
 
   if (rowOk && z0 < z1) {  // warp-uniform
-    const size_t col = (size_t)gy * strideY + (size_t)(active ? gx : 0);
+    // 32-bit voxel offsets from the tile's first voxel of this row (launch code keeps (TZ + 2) planes < 2^31)
+    const size_t rowBase = (size_t)(z0 - P.zBuf0) * strideZ + (size_t)gy * strideY + (size_t)x0warp;
+    const uint32_t* __restrict__ L = P.labels + rowBase;
+    const float* __restrict__ PB = P.pb + rowBase;
+    const int sZ = (int)strideZ, sY = (int)strideY;
+    int o = active ? lane : 0;
     uint32_t lm = 0, l0 = 0, lp = 0, ym = 0, yp = 0, xe = 0; float pv = 0.f;
     if (active) {
-      size_t p = (size_t)(z0 - P.zBuf0) * strideZ + col;
-      l0 = __ldg(P.labels + p);
-      if (z0 > 0) lm = __ldg(P.labels + p - strideZ);
-      if (z0 + 1 < P.Z) lp = __ldg(P.labels + p + strideZ);
-      if (vym) ym = __ldg(P.labels + p - strideY);
-      if (vyp) yp = __ldg(P.labels + p + strideY);
-      pv = __ldg(P.pb + p);
-      if (edgeLane) xe = __ldg(P.labels + p + edgeOff);
+      l0 = __ldg(L + o);
+      if (z0 > 0) lm = __ldg(L + (o - sZ));
+      if (z0 + 1 < P.Z) lp = __ldg(L + (o + sZ));
+      if (vym) ym = __ldg(L + (o - sY));
+      if (vyp) yp = __ldg(L + (o + sY));
+      pv = __ldg(PB + o);
+      if (edgeLane) xe = __ldg(L + (o + edgeOff));
     }
     for (int gz = z0; gz < z1; ++gz) {
       // ---- issue the next step's loads first
       uint32_t nlp = 0, nym = 0, nyp = 0, nxe = 0; float npv = 0.f;
+      o += sZ;
       if (active && gz + 1 < z1) {
-        size_t p = (size_t)(gz + 1 - P.zBuf0) * strideZ + col;
-        if (gz + 2 < P.Z) nlp = __ldg(P.labels + p + strideZ);
-        if (vym) nym = __ldg(P.labels + p - strideY);
-        if (vyp) nyp = __ldg(P.labels + p + strideY);
-        npv = __ldg(P.pb + p);
-        if (edgeLane) nxe = __ldg(P.labels + p + edgeOff);
+        if (gz + 2 < P.Z) nlp = __ldg(L + (o + sZ));
+        if (vym) nym = __ldg(L + (o - sY));
+        if (vyp) nyp = __ldg(L + (o + sY));
+        npv = __ldg(PB + o);
+        if (edgeLane) nxe = __ldg(L + (o + edgeOff));
       }
       uint32_t xm = __shfl_up_sync(0xffffffffu, l0, 1), xp = __shfl_down_sync(0xffffffffu, l0, 1);
       if (lane == 0) xm = xe;
