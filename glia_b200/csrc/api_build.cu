@@ -149,6 +149,10 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.labels = P.labels; F.pb = P.pb; F.ndim = P.ndim; F.X = P.X; F.Y = P.Y; F.Z = P.Z;
       F.zBegin = P.zBegin; F.zEnd = P.zEnd; F.zBuf0 = P.zBuf0;
       if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
+      if (getenv("GLIA_B200_WX") && getenv("GLIA_B200_WY") && P.ndim == 3) {  // tile-shape experiments (<= 8 warps)
+        F.warpsX = atoi(getenv("GLIA_B200_WX")); F.warpsY = atoi(getenv("GLIA_B200_WY"));
+        if (F.warpsX < 1 || F.warpsY < 1 || F.warpsX * F.warpsY > 8) { F.warpsX = 1; F.warpsY = 8; }
+      }
       // GLIA_B200_VOXEL=runs selects the experimental v4 kernel (register runs + warp-segment flush,
       // voxel_runs.cu: parity-green but slower, profiles/r1_v4_notes.txt); default is v3
       const char* vsel = getenv("GLIA_B200_VOXEL");

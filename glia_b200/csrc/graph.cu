@@ -42,7 +42,7 @@ __global__ void compact_edges_kernel(const unsigned long long* __restrict__ keys
                                      const uint32_t* __restrict__ flags, uint32_t labelBound,
                                      unsigned long long* __restrict__ outKey,
                                      uint32_t* __restrict__ outSlot, unsigned long long* counter,
-                                     int* errFlag) {
+                                     int* errFlag, int shift) {
   uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   unsigned long long k = (i < cap) ? keys[i] : EDGE_EMPTY;
   bool occ = k != EDGE_EMPTY;
@@ -56,7 +56,7 @@ __global__ void compact_edges_kernel(const unsigned long long* __restrict__ keys
     uint32_t a = (uint32_t)(k >> 32), b = (uint32_t)k;
     if (a >= labelBound || b >= labelBound || !flags[a] || !flags[b]) { atomicExch(errFlag, 3); return; }
     unsigned long long pos = base + __popc(m & ((1u << lane) - 1));
-    outKey[pos] = ((unsigned long long)rank[a] << 32) | rank[b];
+    outKey[pos] = ((unsigned long long)rank[a] << shift) | rank[b];  // 2 * shift key bits: fewer radix passes
     outSlot[pos] = (uint32_t)i;
   }
 }
@@ -67,12 +67,12 @@ __global__ void gather_edges_kernel(const unsigned long long* __restrict__ keySo
                                     const uint32_t* __restrict__ gMax,
                                     const double* __restrict__ gF64, int* __restrict__ ea,
                                     int* __restrict__ eb, uint32_t* __restrict__ sAdd,
-                                    uint32_t* __restrict__ sMax, double* __restrict__ sF64) {
+                                    uint32_t* __restrict__ sMax, double* __restrict__ sF64, int shift) {
   long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (w >= E) return;
   size_t s = slotSorted[w];
-  if (lane == 0) { unsigned long long k = keySorted[w]; ea[w] = (int)(k >> 32); eb[w] = (int)(uint32_t)k; }
+  if (lane == 0) { unsigned long long k = keySorted[w]; ea[w] = (int)(k >> shift); eb[w] = (int)(k & ((1ull << shift) - 1)); }
   for (int i = lane; i < L.nAdd; i += 32) sAdd[(size_t)w * L.nAdd + i] = gAdd[s * L.nAdd + i];
   for (int i = lane; i < L.nMax; i += 32) sMax[(size_t)w * L.nMax + i] = gMax[s * L.nMax + i];
   for (int i = lane; i < L.nF64; i += 32) sF64[(size_t)w * L.nF64 + i] = gF64[s * L.nF64 + i];
@@ -87,7 +87,7 @@ __global__ void gather_edges_vec_kernel(const unsigned long long* __restrict__ k
                                         const uint32_t* __restrict__ gAdd, const uint32_t* __restrict__ gMax,
                                         const double* __restrict__ gF64, int* __restrict__ ea,
                                         int* __restrict__ eb, uint32_t* __restrict__ sAdd,
-                                        uint32_t* __restrict__ sMax, double* __restrict__ sF64) {
+                                        uint32_t* __restrict__ sMax, double* __restrict__ sF64, int shift) {
   const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 3;
   const int sub = threadIdx.x & 7;
   if (w >= E) return;
@@ -102,7 +102,7 @@ __global__ void gather_edges_vec_kernel(const unsigned long long* __restrict__ k
   const double2* f2 = (const double2*)(gF64 + s * L.nF64);
   double2* of = (double2*)(sF64 + (size_t)w * L.nF64);
   for (int i = 7 - sub; i < nF2; i += 8) of[i] = f2[i];
-  if (sub == 6) { unsigned long long k = keySorted[w]; ea[w] = (int)(k >> 32); eb[w] = (int)(uint32_t)k; }
+  if (sub == 6) { unsigned long long k = keySorted[w]; ea[w] = (int)(k >> shift); eb[w] = (int)(k & ((1ull << shift) - 1)); }
 }
 
 // row[r] = first edge with a >= r (r in 0..R)
@@ -262,12 +262,13 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   // Upper bound on E is not known before compaction: count first with a null-output pass
   // would cost a second sweep, so size the outputs by the table capacity bound instead.
   size_t eCap = (size_t)P.edgeCap;
+  int rbits = 1; while ((1ll << rbits) < R + 1) ++rbits;  // key = index pair in 2 * rbits bits (<= 64: R < 2^32)
   CK(h->eKey.ensure(8 * eCap));
   CK(h->eSlot.ensure(4 * eCap));
   compact_edges_kernel<<<nblk((long long)eCap, 256), 256, 0, st>>>(
       (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(),
       h->flags.as<uint32_t>(), LB, h->eKey.as<unsigned long long>(), h->eSlot.as<uint32_t>(),
-      dCounter, dErr);
+      dCounter, dErr, rbits);
   h->launches++;
   unsigned long long E64 = 0; int errv = 0;
   CK(cudaMemcpyAsync(&E64, dCounter, 8, cudaMemcpyDeviceToHost, st));
@@ -280,8 +281,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   tr.mark("edges: compact+readback");
   CK(h->eKeySorted.ensure(8 * (size_t)(E + 1)));
   CK(h->eSlotSorted.ensure(4 * (size_t)(E + 1)));
-  int rbits = 1; while ((1ll << rbits) < R + 1) ++rbits;
-  int endBit = 32 + rbits > 64 ? 64 : 32 + rbits;
+  const int endBit = 2 * rbits > 64 ? 64 : 2 * rbits;
   if (E > 0) {
     tmpBytes = 0;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, h->eKey.as<unsigned long long>(),
@@ -308,14 +308,14 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
         h->eKeySorted.as<unsigned long long>(), h->eSlotSorted.as<uint32_t>(), E, P.edge,
         h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(),
         h->ea.as<int>(), h->eb.as<int>(), h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
-        h->sF64.as<double>());
+        h->sF64.as<double>(), rbits);
     h->launches++;
   } else if (E > 0) {
     gather_edges_kernel<<<nblk(E * 32, 256), 256, 0, st>>>(
         h->eKeySorted.as<unsigned long long>(), h->eSlotSorted.as<uint32_t>(), E, P.edge,
         h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(),
         h->ea.as<int>(), h->eb.as<int>(), h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
-        h->sF64.as<double>());
+        h->sF64.as<double>(), rbits);
     h->launches++;
   }
   tr.mark("edges: gather records");
