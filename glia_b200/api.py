@@ -57,7 +57,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_launch_count", "glia_b200_build_partial", "glia_b200_raw_region_tables",
            "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
            "glia_b200_import_edges", "glia_b200_table_load", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
-           "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble"]
+           "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble",
+           "glia_b200_region_presence", "glia_b200_index_regions", "glia_b200_gather_regions"]
 
 
 def lib():
@@ -100,6 +101,9 @@ def lib():
         L.glia_b200_build_partial.argtypes = [vp, vp, vp, vp]
         L.glia_b200_raw_region_tables.argtypes = [vp, vpp, vpp, vpp, i64p, i64p, i64p]
         L.glia_b200_finalize_regions.argtypes = [vp, i64p]
+        L.glia_b200_region_presence.argtypes = [vp, vpp, i64p]
+        L.glia_b200_index_regions.argtypes = [vp, i64p]
+        L.glia_b200_gather_regions.argtypes = [vp]
         L.glia_b200_edge_interest.argtypes = [vp, C.c_int, vpp, i64p]
         L.glia_b200_export_edges.argtypes = [vp, C.c_int, C.c_int, i64p, vpp, C.POINTER(C.c_int)]
         L.glia_b200_import_edges.argtypes = [vp, vp, C.c_int64, C.c_int]
@@ -407,6 +411,20 @@ class MergeTreeBuilder:
         p, rb = C.c_void_p(), C.c_int()
         self._check(lib().glia_b200_export_edges(self.h, world, self_rank, counts, C.byref(p), C.byref(rb)))
         return list(counts), p.value or 0, rb.value
+
+    def region_presence(self):
+        p, n = C.c_void_p(), C.c_int64()
+        self._check(lib().glia_b200_region_presence(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def index_regions(self):
+        r = C.c_int64()
+        self._check(lib().glia_b200_index_regions(self.h, C.byref(r)))
+        self.R = r.value
+        return r.value
+
+    def gather_regions(self):
+        self._check(lib().glia_b200_gather_regions(self.h))
 
     def table_load(self):
         o, c = C.c_int64(), C.c_int64()

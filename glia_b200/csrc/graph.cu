@@ -200,8 +200,21 @@ int glia_finalize_graph(glia_handle* h) {
   return glia_finalize_edges(h, 0, h->R);
 }
 
-// regions: presence -> dense index in ascending label order, compact records
-int glia_finalize_regions(glia_handle* h) {
+// regions: presence -> dense index in ascending label order, compact records.  Three steps so that a multi-GPU
+// caller can reduce the 4-byte presence flags first, index the regions and exchange the boundary records while
+// the all-reduce of the (30x larger) record tables is still in flight (glia_b200/parallel.py).
+int glia_region_presence(glia_handle* h) {
+  cudaStream_t st = h->stream;
+  const VoxParams& P = h->vp;
+  const uint32_t LB = P.labelBound;
+  CK(h->flags.ensure(4 * (size_t)LB + 4));
+  mark_present_kernel<<<nblk(LB, 256), 256, 0, st>>>(h->regAdd.as<uint32_t>(), P.reg.nAdd, LB,
+                                                     h->flags.as<uint32_t>());
+  h->launches++;
+  return cudaGetLastError() == cudaSuccess ? GLIA_OK : GLIA_E_CUDA;
+}
+
+int glia_index_regions(glia_handle* h) {
   cudaStream_t st = h->stream;
   PhaseTrace tr(st);
   const VoxParams& P = h->vp;
@@ -209,16 +222,7 @@ int glia_finalize_regions(glia_handle* h) {
   // scalars: [0] edge counter (u64), [1] cand count (int as u64 slot), [2] err flag
   CK(h->scalars.ensure(64));
   CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));
-  unsigned long long* dCounter = h->scalars.as<unsigned long long>();
-  int* dNumSel = (int*)(dCounter + 1);
-  int* dErr = (int*)(dCounter + 2);
-
-  // ---- regions: presence -> rank
-  CK(h->flags.ensure(4 * (size_t)LB + 4));
   CK(h->rank.ensure(4 * (size_t)LB + 4));
-  mark_present_kernel<<<nblk(LB, 256), 256, 0, st>>>(h->regAdd.as<uint32_t>(), P.reg.nAdd, LB,
-                                                     h->flags.as<uint32_t>());
-  h->launches++;
   size_t tmpBytes = 0;
   CK(cub::DeviceScan::ExclusiveSum(nullptr, tmpBytes, h->flags.as<uint32_t>(), h->rank.as<uint32_t>(), (int)LB, st));
   CK(h->cubTmp.ensure(tmpBytes));
@@ -229,8 +233,16 @@ int glia_finalize_regions(glia_handle* h) {
   CK(cudaMemcpyAsync(&lastFlag, h->flags.as<uint32_t>() + (LB - 1), 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   h->R = (long long)lastRank + lastFlag;
+  tr.mark("regions: scan+readback");
+  return GLIA_OK;
+}
+
+int glia_gather_regions(glia_handle* h) {
+  cudaStream_t st = h->stream;
+  PhaseTrace tr(st);
+  const VoxParams& P = h->vp;
+  const uint32_t LB = P.labelBound;
   const long long R = h->R;
-  tr.mark("regions: mark+scan+readback");
   CK(h->regLabel.ensure(4 * (size_t)(R + 1)));
   CK(h->cAdd.ensure(4 * (size_t)(R + 1) * P.reg.nAdd));
   CK(h->cMax.ensure(4 * (size_t)(R + 1) * P.reg.nMax));
@@ -243,6 +255,13 @@ int glia_finalize_regions(glia_handle* h) {
   CK(cudaGetLastError());
   tr.mark("regions: gather");
   return GLIA_OK;
+}
+
+int glia_finalize_regions(glia_handle* h) {
+  int s = glia_region_presence(h);
+  if (s == GLIA_OK) s = glia_index_regions(h);
+  if (s == GLIA_OK) s = glia_gather_regions(h);
+  return s;
 }
 
 // directed boundaries of the local table -> CSR, reverse links, candidates whose smaller end lies

@@ -17,6 +17,9 @@
 #include "handle.cuh"
 
 int glia_finalize_regions(glia_handle* h);
+int glia_region_presence(glia_handle* h);
+int glia_index_regions(glia_handle* h);
+int glia_gather_regions(glia_handle* h);
 int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi);
 int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);
 
@@ -140,6 +143,33 @@ extern "C" int glia_b200_finalize_regions(glia_handle* h, int64_t* R) {
   if (s != GLIA_OK) return s;
   if (R) *R = h->R;
   return GLIA_OK;
+}
+
+extern "C" int glia_b200_region_presence(glia_handle* h, void** flags, int64_t* n) {
+  if (!h || !flags || !n) return GLIA_E_ARG;
+  if (!h->partial) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  int s = glia_region_presence(h);
+  if (s != GLIA_OK) return s;
+  *flags = h->flags.p; *n = (int64_t)h->vp.labelBound;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_index_regions(glia_handle* h, int64_t* R) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->partial || !h->flags.p) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  int s = glia_index_regions(h);
+  if (s != GLIA_OK) return s;
+  if (R) *R = h->R;
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_gather_regions(glia_handle* h) {
+  if (!h) return GLIA_E_ARG;
+  if (!h->partial || !h->rank.p) return GLIA_E_STATE;
+  CK(cudaSetDevice(h->prm.device));
+  return glia_gather_regions(h);
 }
 
 extern "C" int glia_b200_edge_interest(glia_handle* h, int world, void** mask, int64_t* bytes) {

@@ -55,10 +55,15 @@ def dev_tensor(ptr, count, dtype, device):
 class TorchComm:
     """torch.distributed process group (NCCL for CUDA tensors, gloo for CPU tensors)."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, side_group=True):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        # a second communicator (its own NCCL stream): the all-reduce of the region record tables runs on it
+        # while the boundary records are exchanged on the first one.  new_group is collective: every rank
+        # constructs its TorchComm at the same point.
+        self.side = dist.new_group(ranks=dist.get_process_group_ranks(group) if group is not None else None) \
+            if side_group and self.world > 1 else group
 
     def all_reduce(self, t, op):
         if t.numel() == 0:
@@ -70,6 +75,25 @@ class TorchComm:
             t.bitwise_xor_(-2 ** 31)
         else:
             d.all_reduce(t, op=d.ReduceOp.SUM if op == "sum" else d.ReduceOp.MAX, group=self.group)
+
+    def all_reduce_start(self, t, op):
+        """all_reduce on the side communicator; returns a handle for all_reduce_finish."""
+        if t.numel() == 0:
+            return None
+        d = self.dist
+        if op == "max_u32":
+            t.bitwise_xor_(-2 ** 31)
+            return (d.all_reduce(t, op=d.ReduceOp.MAX, group=self.side, async_op=True), t, True)
+        return (d.all_reduce(t, op=d.ReduceOp.SUM if op == "sum" else d.ReduceOp.MAX, group=self.side, async_op=True),
+                t, False)
+
+    def all_reduce_finish(self, handle):
+        if handle is None:
+            return
+        work, t, flip = handle
+        work.wait()  # the current stream waits for the collective; the host does not block
+        if flip:
+            t.bitwise_xor_(-2 ** 31)
 
     def all_gather_fixed(self, t):
         """Concatenation over ranks of equally sized 1-D tensors."""
@@ -153,6 +177,13 @@ class ThreadComm:
     def all_gather_fixed(self, t):
         return self.all_gather_v(t)
 
+    def all_reduce_start(self, t, op):
+        self.all_reduce(t, op)
+        return None
+
+    def all_reduce_finish(self, handle):
+        pass
+
     def all_to_all_v(self, send, counts, cout=None):
         s = self.s
         self._sync(send)
@@ -219,13 +250,18 @@ def build_sharded(comm, b, labels, pb, mask=None, timings=None):
     b.build_partial(labels, pb, mask)
     mark()
     fence()
+    # The record tables (131 MB at C4) start their all-reduce on the side communicator; only the 4-byte presence
+    # flags are needed to index the regions, and the boundary exchange below needs the index, not the records.
     (pa, na), (pm, nm), (pf, nf) = b.raw_region_tables()
-    comm.all_reduce(dev_tensor(pa, na, torch.int32, dev), "sum")      # counts, histogram bins
-    comm.all_reduce(dev_tensor(pm, nm, torch.int32, dev), "max_u32")  # bbox, min/max codes
-    comm.all_reduce(dev_tensor(pf, nf, torch.float64, dev), "sum")    # sum v, sum v^2
+    ppres, npres = b.region_presence()
+    fence()
+    pending = [comm.all_reduce_start(dev_tensor(pa, na, torch.int32, dev), "sum"),      # counts, histogram bins
+               comm.all_reduce_start(dev_tensor(pm, nm, torch.int32, dev), "max_u32"),  # bbox, min/max codes
+               comm.all_reduce_start(dev_tensor(pf, nf, torch.float64, dev), "sum")]    # sum v, sum v^2
+    comm.all_reduce(dev_tensor(ppres, npres, torch.int32, dev), "max")
     fence()
     mark()
-    R = b.finalize_regions()
+    R = b.index_regions()
     pi, ni = b.edge_interest(comm.world)
     fence()
     comm.all_reduce(dev_tensor(pi, ni, torch.uint8, dev), "max")
@@ -254,12 +290,16 @@ def build_sharded(comm, b, labels, pb, mask=None, timings=None):
     b.import_edges(recv.data_ptr() if recv.numel() else 0, recv.shape[0], rebuild)
     lo, hi = owner_range(R, comm.world, comm.rank)
     b.finalize_edges(lo, hi)
+    for hnd in pending:
+        comm.all_reduce_finish(hnd)
+    fence()
+    b.gather_regions()
     mark()
     if timings is not None:
         torch.cuda.synchronize(dev)
         dt = [ev[i].elapsed_time(ev[i + 1]) for i in range(len(ev) - 1)]
         timings.update(voxel_ms=dt[0], exchange_ms=dt[1] + dt[2] + dt[3], graph_ms=dt[4],
-                       exchange_detail_ms={"region_tables_all_reduce": dt[1], "regions+interest": dt[2],
-                                           "boundary_records_all_to_all": dt[3]},
+                       exchange_detail_ms={"presence_all_reduce (record tables start on the side communicator)": dt[1],
+                                           "region_index+interest": dt[2], "boundary_records_all_to_all": dt[3]},
                        sent_records=int(sum(counts)), record_bytes=rec)
     return b

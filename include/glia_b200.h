@@ -142,6 +142,14 @@ GLIA_API int glia_b200_build_partial(glia_handle* h, const uint32_t* labels, con
 GLIA_API int glia_b200_raw_region_tables(glia_handle* h, void** add, void** mx, void** f64, int64_t* n_add,
                                          int64_t* n_max, int64_t* n_f64);
 GLIA_API int glia_b200_finalize_regions(glia_handle* h, int64_t* R);
+/* The same in three steps, for callers that overlap the all-reduce of the record tables with the exchange of
+ * the boundary records: region_presence returns the u32 presence flags [label_bound] of the LOCAL table
+ * (all-reduce max them), index_regions turns the reduced flags into the dense region index (R), and
+ * gather_regions compacts the records once the tables of raw_region_tables are reduced.  edge_interest,
+ * export_edges, import_edges and finalize_edges need only the index, not the records. */
+GLIA_API int glia_b200_region_presence(glia_handle* h, void** flags, int64_t* n);
+GLIA_API int glia_b200_index_regions(glia_handle* h, int64_t* R);
+GLIA_API int glia_b200_gather_regions(glia_handle* h);
 GLIA_API int glia_b200_edge_interest(glia_handle* h, int world, void** mask, int64_t* bytes);
 /* counts [world]: records for each destination rank, stored back to back in *buf in rank order.
  * self_rank >= 0: nothing is exported to that rank - its records stay in the handle's table and the

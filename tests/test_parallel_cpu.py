@@ -62,6 +62,14 @@ def _exercise(comm, out):
     np.testing.assert_allclose(t.numpy(), f.sum(0), rtol=1e-15)
     t = torch.from_numpy((mx[r] & 1).astype(np.uint8)); comm.all_reduce(t, "max")
     assert np.array_equal(t.numpy(), (mx & 1).max(0).astype(np.uint8))
+    # the same reductions started on the side communicator and finished later (build_sharded overlaps them)
+    ta = torch.from_numpy(add[r].copy()); tm = torch.from_numpy(mx[r].copy().view(np.int32)); tf = torch.from_numpy(f[r].copy())
+    pend = [comm.all_reduce_start(ta, "sum"), comm.all_reduce_start(tm, "max_u32"), comm.all_reduce_start(tf, "sum")]
+    t = torch.from_numpy((mx[r] & 1).astype(np.uint8)); comm.all_reduce(t, "max")  # other traffic in between
+    for hnd in pend:
+        comm.all_reduce_finish(hnd)
+    assert np.array_equal(ta.numpy(), add.sum(0)) and np.array_equal(tm.numpy().view(np.uint32), mx.max(0))
+    np.testing.assert_allclose(tf.numpy(), f.sum(0), rtol=1e-15)
     # all_to_all_v: record j sent by rank s to rank d carries (s, d, j)
     rec = 12
     rows = [np.array([r, d, j], np.int32).view(np.uint8) for d in range(world) for j in range(counts[r, d])]
