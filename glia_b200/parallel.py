@@ -255,10 +255,10 @@ def build_sharded(comm, b, labels, pb, mask=None, timings=None):
     (pa, na), (pm, nm), (pf, nf) = b.raw_region_tables()
     ppres, npres = b.region_presence()
     fence()
+    comm.all_reduce(dev_tensor(ppres, npres, torch.int32, dev), "max")  # first: the small one is on the critical path
     pending = [comm.all_reduce_start(dev_tensor(pa, na, torch.int32, dev), "sum"),      # counts, histogram bins
                comm.all_reduce_start(dev_tensor(pm, nm, torch.int32, dev), "max_u32"),  # bbox, min/max codes
                comm.all_reduce_start(dev_tensor(pf, nf, torch.float64, dev), "sum")]    # sum v, sum v^2
-    comm.all_reduce(dev_tensor(ppres, npres, torch.int32, dev), "max")
     fence()
     mark()
     R = b.index_regions()
