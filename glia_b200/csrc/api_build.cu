@@ -149,9 +149,9 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.labels = P.labels; F.pb = P.pb; F.ndim = P.ndim; F.X = P.X; F.Y = P.Y; F.Z = P.Z;
       F.zBegin = P.zBegin; F.zEnd = P.zEnd; F.zBuf0 = P.zBuf0;
       if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
-      if (getenv("GLIA_B200_WX") && getenv("GLIA_B200_WY") && P.ndim == 3) {  // tile-shape experiments (<= 8 warps)
+      if (getenv("GLIA_B200_WX") && getenv("GLIA_B200_WY")) {  // tile-shape experiments (<= 8 warps)
         F.warpsX = atoi(getenv("GLIA_B200_WX")); F.warpsY = atoi(getenv("GLIA_B200_WY"));
-        if (F.warpsX < 1 || F.warpsY < 1 || F.warpsX * F.warpsY > 8) { F.warpsX = 1; F.warpsY = 8; }
+        if (F.warpsX < 1 || F.warpsY < 1 || F.warpsX * F.warpsY > 8 || (P.ndim == 2 && F.warpsY != 1)) { F.warpsX = P.ndim == 2 ? 8 : 1; F.warpsY = P.ndim == 2 ? 1 : 8; }
       }
       // GLIA_B200_VOXEL=runs selects the experimental v4 kernel (register runs + warp-segment flush,
       // voxel_runs.cu: parity-green but slower, profiles/r1_v4_notes.txt); default is v3
@@ -181,7 +181,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       F.overflow = P.overflow;
       // v3: 256 boundary slots + 16-plane tiles keep a CTA at 54 KB / 62 registers -> 4 CTAs per SM
       // (profiles/r1_v4_notes.txt, "occupancy"); the experimental kernels keep the sizes they were measured with
-      F.regSlots = 128;
+      F.regSlots = getenv("GLIA_B200_RSLOTS") ? atoi(getenv("GLIA_B200_RSLOTS")) : 128;
       F.edgeSlots = getenv("GLIA_B200_ESLOTS") ? atoi(getenv("GLIA_B200_ESLOTS")) : ((useRuns || useRq) ? 512 : 256);
       for (int k = 0; k < nChunks; ++k) {
         if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));

@@ -350,23 +350,44 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     top2(r2);
     std::vector<uint32_t> yb1 = best1, yb2 = best2; std::vector<int> yo1 = owner1;
     uint32_t* p = hStage;
+    // records are written straight into the staging buffer; the two scratch records below are reused for
+    // every candidate (no allocation per candidate)
+    auto put_parts = [&](const uint32_t* add, size_t na, const uint32_t* mx, size_t nm, const double* f, size_t nf) {
+      if (na) memcpy(p, add, 4 * na);
+      if (nm) memcpy(p + na, mx, 4 * nm);
+      const size_t off = na + nm + ((na + nm) & 1);
+      if (nf) memcpy(p + off, f, 8 * nf);
+      p += off + 2 * nf;
+    };
+    Rec bzz, pb;
+    bzz.init(LE); pb.init(LE);
     for (int W : Ws) {
       const Rec& dWY = G.dm[W][r2]; const Rec& dYW = G.dm[r2][W];
       put_rec(p, G.reg[W]);
       put_rec(p, G.reg[r2]);
       top2(W);
-      Rec bx = G.btot[W]; bx.mx = best1;
-      Rec by = G.btot[r2]; by.mx = yb1;
-      Rec bzz; bzz.init(LE);
+      const Rec& bx = G.btot[W];   // boundary-of totals: add + f64; the max words are best1 / yb1
+      const Rec& by = G.btot[r2];
       for (int i = 0; i < LE.nAdd; ++i) bzz.add[i] = bx.add[i] + by.add[i] - dWY.add[i] - dYW.add[i];
       for (int i = 0; i < LE.nF64; ++i) bzz.f[i] = bx.f[i] + by.f[i] - dWY.f[i] - dYW.f[i];
       for (int i = 0; i < LE.nMax; ++i)
         bzz.mx[i] = std::max(owner1[i] == r2 ? best2[i] : best1[i], yo1[i] == W ? yb2[i] : yb1[i]);
-      Rec pb = dWY; pb.merge(dYW);  // pair boundary (util/struct.hxx:10-16)
-      for (int e : G.nmOut[W]) if (G.cur(G.eb[e]) == r2 && G.active(G.eb[e], r2)) pb.merge(G.edgeRec(e));
+      pb.add = dWY.add; pb.mx = dWY.mx; pb.f = dWY.f;  // pair boundary (util/struct.hxx:10-16)
+      pb.merge(dYW);
+      auto merge_base = [&](int e) {
+        const uint32_t* a = G.sAdd.data() + (size_t)e * LE.nAdd;
+        const uint32_t* m = G.sMax.data() + (size_t)e * LE.nMax;
+        const double* f = G.sF64.data() + (size_t)e * LE.nF64;
+        for (int i = 0; i < LE.nAdd; ++i) pb.add[i] += a[i];
+        for (int i = 0; i < LE.nMax; ++i) pb.mx[i] = std::max(pb.mx[i], m[i]);
+        for (int i = 0; i < LE.nF64; ++i) pb.f[i] += f[i];
+      };
+      for (int e : G.nmOut[W]) if (G.cur(G.eb[e]) == r2 && G.active(G.eb[e], r2)) merge_base(e);
       auto nt = nmByTarget.find(W);
-      if (nt != nmByTarget.end()) for (int e : nt->second) if (G.active(G.eb[e], W)) pb.merge(G.edgeRec(e));
-      put_rec(p, bx); put_rec(p, by); put_rec(p, bzz); put_rec(p, pb);
+      if (nt != nmByTarget.end()) for (int e : nt->second) if (G.active(G.eb[e], W)) merge_base(e);
+      put_parts(bx.add.data(), bx.add.size(), best1.data(), best1.size(), bx.f.data(), bx.f.size());
+      put_parts(by.add.data(), by.add.size(), yb1.data(), yb1.size(), by.f.data(), by.f.size());
+      put_rec(p, bzz); put_rec(p, pb);
     }
     const double tC = trace ? now() : 0.0;
     CK(cudaMemcpyAsync(dStage, hStage, 4 * m * stageWords, cudaMemcpyHostToDevice, st));
