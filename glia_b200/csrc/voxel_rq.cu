@@ -1,7 +1,7 @@
-// EXPERIMENTAL (GLIA_B200_VOXEL=queue; parity-green, 8.97 ms vs 3.57 ms for v3 at 512^3: the drain
-// costs ~670 warp-instructions per step at ~3 active lanes - region/boundary branches, contended CAS
-// loops on doubles, a second round for n - 32 leftovers; profiles/r1_v4_notes.txt has the numbers
-// and the fix: two typed queues, drain exactly 32, combine adjacent equal keys by segmented shuffles).
+// EXPERIMENTAL (GLIA_B200_VOXEL=queue; parity-green, 5.24 ms vs 3.40 ms for v3 at 512^3).  v5b: two typed
+// queues per warp, drains of exactly 32 runs, adjacent equal keys combined by segmented shuffles so that only
+// segment heads touch the tables.  It halves the shared atomics of v3 but needs 126 registers (2 CTAs/SM) and
+// 714 warp-instructions per 32 voxels; profiles/r1_v4_notes.txt has the numbers and what round 2 should keep.
 // K1+K3+K4 fused, v5 "run queue" (default hmt configuration: one image = the boundary probability
 // map as region image, boundary image and threshold source; <= 16 bins, <= 3 thresholds, no mask).
 // Same results as voxel_pass_generic / voxel_pass_fast; reference semantics as cited there
@@ -13,9 +13,9 @@
 // statistics of its current run of equal label / equal directed pair in registers (count, border,
 // 16 x 4-bit histogram, threshold counts, sum, sum^2, min, max, z-range); per voxel there is no
 // hashing and no atomic.  A finished run (label change, or 15 voxels) is appended to the warp's queue
-// with a ballot-computed position (no atomic, queue length is a warp-uniform register); when the
-// queue holds >= 32 runs the whole warp drains it, one run per lane: slot lookup in the CTA's
-// shared-memory tables, a handful of shared atomics per run.  Tables are flushed to the global
+// with a ballot-computed position (no atomic, queue lengths are warp-uniform registers); when a
+// queue holds >= 32 runs the whole warp drains 32 of them, one run per lane: segmented combine, then
+// slot lookup in the CTA's shared-memory tables and a handful of shared atomics per segment head.  Tables are flushed to the global
 // records once per tile, as in v3.
 #include "voxel_fast.cuh"
 
