@@ -39,6 +39,14 @@ __global__ void bench(unsigned long long* out, uint32_t* gbuf, int nwarps_active
     if (MODE == 14) { if (lane < 4) atomicAdd(&s64[(x >> 8) & 2047], 1ull); }
     if (MODE == 15) acc += __match_any_sync(0xffffffffu, (x >> 30));               // 4 groups
     if (MODE == 16) atomicAdd(&s32[((x >> 8) & 255) * 32 + (lane & 3)], 1u);       // random rows, 4 banks
+    // ---- questions left open by round 1 (profiles/r1_v4_notes.txt): what an f64 sum costs per finished run
+    if (MODE == 17) atomicAdd((double*)&s64[warp * 8], 1.0);                        // smem f64, all lanes same address
+    if (MODE == 18) atomicAdd((double*)&s64[(warp * 8 + (lane >> 3)) & 2047], 1.0); // smem f64, 4 addresses x 8 lanes (a drain)
+    if (MODE == 19) atomicAdd((double*)&s64[(x >> 8) & 2047], 1.0);                 // smem f64 random
+    if (MODE == 20) { if (lane < 4) atomicAdd((double*)&s64[(x >> 8) & 2047], 1.0); }  // smem f64 random, 4 lanes
+    if (MODE == 21) atomicAdd((double*)gbuf + (((size_t)blockIdx.x * 4096 + ((x >> 20) & 4095)) % (1u << 23)), 1.0);  // REDG.F64, 32 KB window per SM
+    if (MODE == 22) { if (lane < 4) atomicAdd((double*)gbuf + (((size_t)blockIdx.x * 4096 + ((x >> 20) & 4095)) % (1u << 23)), 1.0); }
+    if (MODE == 23) atomicAdd((double*)gbuf + ((x >> 9) & ((1u << 23) - 1)), 1.0);  // REDG.F64 random over 64 MB
   }
   long long t1 = clock64();
   if (tid == 0) out[blockIdx.x] = (unsigned long long)(t1 - t0);
@@ -48,7 +56,7 @@ __global__ void bench(unsigned long long* out, uint32_t* gbuf, int nwarps_active
 template <int MODE>
 void run(const char* name, int threads) {
   unsigned long long* out; uint32_t* g;
-  cudaMalloc(&out, 8 * 148); cudaMalloc(&g, 4u << 24); cudaMemset(g, 0, 4u << 24);
+  cudaMalloc(&out, 8 * 148); cudaMalloc(&g, 4u << 24); cudaMemset(g, 0, 4u << 24);  // 64 MB
   bench<MODE><<<148, threads>>>(out, g, threads / 32);
   cudaDeviceSynchronize();
   bench<MODE><<<148, threads>>>(out, g, threads / 32);
@@ -80,6 +88,13 @@ int main() {
     run<13>("ATOMS.ADD u32 random, 4 lanes active", th);
     run<14>("ATOMS.ADD u64 random, 4 lanes active", th);
     run<16>("ATOMS.ADD u32 random rows 4 banks", th);
+    run<17>("smem f64 add, same address", th);
+    run<18>("smem f64 add, 4 addresses x 8 lanes", th);
+    run<19>("smem f64 add, random", th);
+    run<20>("smem f64 add, random, 4 lanes active", th);
+    run<21>("RED.global f64, 32 KB window per SM", th);
+    run<22>("RED.global f64, 32 KB window, 4 lanes", th);
+    run<23>("RED.global f64, random over 64 MB", th);
     printf("\n");
   }
   return 0;
