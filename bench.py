@@ -256,7 +256,7 @@ def main():
         if rank != 0:
             return 0
         forest = forest_arrays_cpu(synth, dim, nd)
-        steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+        steps, warmup = max(1, min(args.steps, 200)), max(0, min(args.warmup, 20))  # ~0.75 s of host work per step
         r = cpu_reference(args.workload, forest, steps, warmup)
         line = {"impl": "reference", "metric": "Mvoxels/s, labels+pb -> scored initial merge candidates",
                 "value": r["mvox_s"], "unit": "Mvoxels/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,

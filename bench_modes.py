@@ -187,7 +187,7 @@ def run_rf_sweep(args, rank, world, local_rank):
         rng = np.random.default_rng(1)
         X = rng.random((n, d))
         X[: n // 20] = pool[rng.integers(0, len(pool), n // 20)]  # rows sitting exactly on thresholds
-        steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+        steps, warmup = max(1, min(args.steps, 200)), max(0, min(args.warmup, 20))  # ~0.2 s of host work per step
         ts = []
         for s in range(warmup + steps):
             t0 = time.perf_counter()
