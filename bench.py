@@ -60,11 +60,15 @@ RF_SWEEP = dict(n=10_000_000, d=50, ntree=255, desc="RF scoring sweep: 255-tree 
                 "with 50-dim bc features (BASELINE.json configs[4])")
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE voxel_pass_fast launch, from the committed
-# `ncu --set full` captures (profiles/r1_end_ncu_c2.txt, profiles/r1_v3_ncu_c4s.txt); None = not captured
-VOXEL_PASS_TRAFFIC = {"c2": 299.82e6 + 81.76e6, "c4s": 1.884e9 + 0.378e9}
-# the same for ONE rf_score_smem_kernel launch (profiles/r1_end_ncu_c2.txt)
-RF_SCORE_TRAFFIC = {"c2": 233.01e6 + 4.95e6}
+def load_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of `kernel`, from the `ncu --set full` capture
+    named in profiles/traffic.json (None = not captured for this workload)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            e = json.load(f).get(workload, {}).get(kernel)
+        return None if e is None else {"bytes": float(e["bytes"]), "capture": e["capture"]}
+    except Exception:  # noqa: BLE001
+        return None
 
 
 def load_peaks():
@@ -142,18 +146,40 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons), "window": getattr(self, "window", "")}
 
 
+FOREST_TRAIN = {2: ((384, 384), 9), 3: ((64, 96, 96), 8)}  # small synthetic image the bench forest is trained on
+
+
+def train_forest(synth, keys, rows, shape, cell):
+    """SURVEY §8d forest: 255 trees, 2 classes {-1, +1}, depth <= 20, trained with scikit-learn (seed 0) on the
+    feature rows of a small synthetic image against a synthetic ground truth (blocks of 3^D cells are one true
+    segment).  Falls back to the random-structure forest of round 1 when scikit-learn is unusable."""
+    try:
+        y = synth.gt_merge_labels(keys, shape, cell)
+        f = synth.sklearn_forest(rows, y, ntree=255, seed=0, max_depth=20)
+        kind = "sklearn-trained (seed 0, depth <= 20) on %d rows of a %s synthetic image" % (len(rows), "x".join(map(str, shape)))
+    except Exception as e:  # noqa: BLE001
+        f = synth.random_forest(255, rows.shape[1], max_depth=20, seed=0, thr_pool=rows, leaf_prob=0.3)
+        kind = "random structure (scikit-learn unusable: %s)" % type(e).__name__
+    info = {"kind": kind, "trees": int(len(f["ndbigtree"])), "nodes": int(f["ndbigtree"].sum()),
+            "mean_path_len": round(synth.mean_path_length(f, rows), 2)}
+    return f, info
+
+
 def make_forest(api, synth, torch, dim, ndim, device):
-    """255-tree forest over `dim` features (random structure, thresholds drawn from real feature
-    rows of a small synthetic image so that traversals are data-dependent)."""
-    shape = (192, 192) if ndim == 2 else (40, 48, 48)
-    lab, pb = synth.voronoi_volume(shape, 9 if ndim == 2 else 8, seed=99)
+    """The bench forest, trained on rows featurised by the GPU path itself (the product never touches oracle/)."""
+    shape, cell = FOREST_TRAIN[ndim]
+    lab, pb = synth.voronoi_volume(shape, cell, seed=99)
     spec = [(pb, 16, 0.0, 1.0)]
     g = api.MergeTreeBuilder(shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR), device=device).build(lab, pb)
-    _, rows = g.init_candidates()
+    keys, rows = g.init_candidates()
     g.close()
     assert rows.shape[1] == dim
-    f = synth.random_forest(255, dim, max_depth=20, seed=0, thr_pool=rows, leaf_prob=0.3)
+    f, info = train_forest(synth, keys, rows, shape, cell)
+    FOREST_INFO.clear(); FOREST_INFO.update(info)
     return f, api.Forest.from_arrays(f, dim, device=device)
+
+
+FOREST_INFO = {}
 
 
 # ------------------------------------------------------------------ reference arm (CPU)
@@ -211,16 +237,18 @@ def cpu_reference(wl, forest, steps, warmup, procs=None):
 
 
 def forest_arrays_cpu(synth, dim, ndim):
-    """Same forest recipe as make_forest, thresholds from oracle rows (reference arm: no GPU code)."""
+    """Same forest recipe as make_forest, trained on oracle rows (reference arm: no GPU code)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as ol
-    shape = (192, 192) if ndim == 2 else (40, 48, 48)
-    lab, pb = synth.voronoi_volume(shape, 9 if ndim == 2 else 8, seed=99)
+    shape, cell = FOREST_TRAIN[ndim]
+    lab, pb = synth.voronoi_volume(shape, cell, seed=99)
     spec = [(pb, 16, 0.0, 1.0)]
     o = ol.Oracle(lab, pb, ol.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR))
-    _, rows = o.init_candidates()
+    keys, rows = o.init_candidates()
     assert rows.shape[1] == dim
-    return synth.random_forest(255, dim, max_depth=20, seed=0, thr_pool=rows, leaf_prob=0.3)
+    f, info = train_forest(synth, keys, rows, shape, cell)
+    FOREST_INFO.clear(); FOREST_INFO.update(info)
+    return f
 
 
 def row_dim(ndim):
@@ -233,7 +261,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("GLIA_BENCH_WORKLOAD", "c2"),
+    # default = the largest single-GPU configuration of BASELINE.json (configs[3], north_star's target): one
+    # 1024^3 volume on one GPU; with N > 1 ranks the same volume z-slab sharded over NCCL (strong scaling)
+    ap.add_argument("--workload", default=os.environ.get("GLIA_BENCH_WORKLOAD", "c4"),
                     choices=sorted(WORKLOADS) + ["c5"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -262,7 +292,10 @@ def main():
                 "value": r["mvox_s"], "unit": "Mvoxels/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
                 "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u32 labels / f32 pb / f64 features", "data": "synthetic",
-                "config": {"workload": args.workload + ": " + desc, "sample": r["sample"]},
+                "config": {"workload": args.workload + ": " + desc, "sample": r["sample"], "forest": dict(FOREST_INFO),
+                           "same_config": False,
+                           "same_config_note": "the reference's point lists do not fit the full volume (SURVEY §5): each "
+                                               "host process runs a bounded tile of the same synthetic recipe"},
                 "candidates_per_s": r["cand_s"],
                 "cpu_baseline": {"value": r["mvox_s"], "unit": "Mvoxels/s", "cores": r["cores"], "kind": r["kind"],
                                  "sample": r["sample"]},
@@ -423,14 +456,15 @@ def main():
     # SURVEY §8d.  Voxel pass: label u32 + pb f32 read once.  RF scoring: 8*D + 8 bytes per candidate (row in,
     # probability out) + the forest once (16-byte nodes).  "roofline" is the kernel with the longer launch in
     # this run (RF scoring at C2, the voxel pass in 3D); "roofline_kernels" carries both.
-    def roof(kernel, alg, ms, traffic):
+    def roof(kernel, alg, ms):
         a = alg / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        tr = load_traffic(args.workload, kernel)
         return {"bound": "hbm", "kernel": kernel, "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
-                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
-                "launch_ms": ms}
-    roofs = [roof("voxel_pass_fast", 8.0 * nvox, kern_ms[0], VOXEL_PASS_TRAFFIC.get(args.workload)),
-             roof("rf_score_smem_kernel", float(Cn) * (8 * dim + 8) + 16.0 * float(forest_arrays["ndbigtree"].sum()),
-                  kern_ms[3], RF_SCORE_TRAFFIC.get(args.workload))]
+                "traffic": tr["bytes"] if tr else None, "traffic_capture": tr["capture"] if tr else None,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg, "launch_ms": ms}
+    roofs = [roof("voxel_pass_fast", 8.0 * nvox, kern_ms[0]),
+             roof("rf_score", float(Cn) * (8 * dim + 8) + 16.0 * float(forest_arrays["ndbigtree"].sum()),
+                  kern_ms[3])]
     dominant = max(roofs, key=lambda r: r["launch_ms"])
     line = {"metric": "Mvoxels/s, labels+pb -> scored initial merge candidates", "value": value, "unit": "Mvoxels/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": elapsed_ms / args.steps,
@@ -438,10 +472,12 @@ def main():
             "dtype": "u32 labels / f32 pb / f64 features", "data": "synthetic",
             "config": {"workload": args.workload + ": " + desc, "per_gpu": "one %s per step" % "x".join(map(str, shape)),
                        "regions": int(R), "directed_boundaries": int(E), "candidates": int(Cn), "row_dim": dim,
-                       "forest": "255 trees, %d nodes" % int(forest_arrays["ndbigtree"].sum()),
+                       "forest": dict(FOREST_INFO),
                        "l2": ("rotating %d distinct inputs (%d MB) through one handle; tables re-zeroed each step" % (nsets, nsets * 8 * nvox >> 20))
                        if nd == 2 else "input 8.6 GB >> 126 MB L2", "sharding": "independent inputs per rank, no collective"},
             "candidates_per_s": cands_all / (elapsed_ms * 1e-3),
+            "rf_node_visits_per_s": (float(Cn) * FOREST_INFO.get("trees", 0) * FOREST_INFO.get("mean_path_len", 0.0) /
+                                     (kern_ms[3] * 1e-3)) if kern_ms[3] > 0 else None,
             "stage_ms": {"table_init": kern_ms[4], "voxel_pass": kern_ms[0], "graph": kern_ms[1], "featurize": kern_ms[2],
                          "rf_score": kern_ms[3]},
             "roofline": dominant, "roofline_kernels": roofs,

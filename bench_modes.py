@@ -146,7 +146,7 @@ def run_slab(args, rank, world, local_rank, dist):
                            "sharding": "z-slabs of %d planes + 1-plane label halo; all-reduce of dense region tables, "
                                        "boundary records all-to-all keyed by label pair (NCCL)" % (z1 - z0),
                            "row_dim": dim, "candidates": int(cands),
-                           "forest": "255 trees, %d nodes" % int(forest_arrays["ndbigtree"].sum()),
+                           "forest": dict(B.FOREST_INFO),
                            "l2": "slab input %.2f GB >> 126 MB L2" % (8 * nloc / 1e9)},
                 "candidates_per_s": cands * args.steps / (elapsed_ms * 1e-3),
                 "stage_ms_rank0": {"voxel_pass+table_init": acc["voxel_ms"] / args.steps,
@@ -157,7 +157,13 @@ def run_slab(args, rank, world, local_rank, dist):
                 "roofline": {"bound": "hbm", "kernel": "voxel_pass_fast", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": alg},
+                "rf_node_visits_per_s_rank0": (float(b.Cn) * B.FOREST_INFO.get("trees", 0) * B.FOREST_INFO.get("mean_path_len", 0.0) /
+                                               (rf_ms / args.steps * 1e-3)) if rf_ms > 0 else None,
                 "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e}
+        if not args.no_cpu_baseline:
+            r = B.cpu_reference(args.workload, forest_arrays, 1, 0)
+            line["cpu_baseline"] = {"value": r["mvox_s"], "unit": "Mvoxels/s", "cores": r["cores"], "kind": r["kind"],
+                                    "sample": r["sample"], "candidates_per_s": r["cand_s"]}
         emit(line)
     b.close()
     dist.destroy_process_group()

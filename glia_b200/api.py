@@ -58,7 +58,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_finalize_regions", "glia_b200_edge_interest", "glia_b200_export_edges",
            "glia_b200_import_edges", "glia_b200_table_load", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
            "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble",
-           "glia_b200_region_presence", "glia_b200_index_regions", "glia_b200_gather_regions"]
+           "glia_b200_region_presence", "glia_b200_index_regions", "glia_b200_gather_regions",
+           "glia_b200_tune"]
 
 
 def lib():
@@ -75,6 +76,7 @@ def lib():
         L.glia_b200_last_error.argtypes = [vp]
         L.glia_b200_last_error.restype = C.c_char_p
         L.glia_b200_build.argtypes = [vp, vp, vp, vp]
+        L.glia_b200_tune.argtypes = [vp, C.c_char_p, C.c_int]
         L.glia_b200_counts.argtypes = [vp] + [C.POINTER(C.c_int64)] * 3
         L.glia_b200_row_dim.argtypes = [vp, C.c_int]
         L.glia_b200_get_regions.argtypes = [vp] * 6
@@ -280,6 +282,11 @@ class MergeTreeBuilder:
             self.close()
         except Exception:
             pass
+
+    def tune(self, key, value):
+        """Per-handle knob (include/glia_b200.h: glia_b200_tune)."""
+        self._check(lib().glia_b200_tune(self.h, key.encode(), int(value)))
+        return self
 
     def set_image(self, kind, i, data):
         """Re-point image i of kind 0 (rimg) / 1 (rlimg) / 2 (bimg) at another buffer of the same extent."""

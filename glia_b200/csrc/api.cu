@@ -140,7 +140,8 @@ extern "C" void glia_b200_destroy(glia_handle* h) {
                           &h->eSlotSorted, &h->eKeySorted, &h->sAdd, &h->sMax, &h->sF64, &h->ea,
                           &h->eb, &h->row, &h->rev, &h->cand, &h->bAggAdd, &h->bAggMax, &h->bAggF64,
                           &h->cubTmp, &h->scalars, &h->rows, &h->sal, &h->keysOut, &h->interest,
-                          &h->exportBuf, &h->exportCursor, &h->regBlocks, &h->bAggMax2, &h->bAggOwn};
+                          &h->exportBuf, &h->exportCursor, &h->regBlocks, &h->bAggMax2, &h->bAggOwn,
+                          &h->orient, &h->tieBuf, &h->firstVox};
   for (auto b : bufs) b->release();
   for (auto& b : h->inImg) b.release();
   for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);
@@ -157,6 +158,16 @@ extern "C" int glia_b200_set_image(glia_handle* h, int kind, int i, const float*
   if (kind == 0 && i < p.n_rimg) p.rimg[i].data = data;
   else if (kind == 1 && i < p.n_rlimg) p.rlimg[i].data = data;
   else if (kind == 2 && i < p.n_bimg) p.bimg[i].data = data;
+  else return GLIA_E_ARG;
+  return GLIA_OK;
+}
+
+// Tuning / test hooks of a handle (no environment variables are read on the data path).
+extern "C" int glia_b200_tune(glia_handle* h, const char* key, int value) {
+  if (!h || !key) return GLIA_E_ARG;
+  if (!strcmp(key, "generic")) h->forceGeneric = value != 0;
+  else if (!strcmp(key, "tz")) { if (value < 0 || value > 31) return GLIA_E_ARG; h->tuneTZ = value; }
+  else if (!strcmp(key, "slots")) { if (value < 0 || value > 2048) return GLIA_E_ARG; h->tuneSlots = value; }
   else return GLIA_E_ARG;
   return GLIA_OK;
 }

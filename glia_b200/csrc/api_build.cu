@@ -1,4 +1,5 @@
 // C ABI, part 2: glia_b200_build and the candidate entry points.
+#include <math.h>
 #include <string.h>
 #include <algorithm>
 #include <vector>
@@ -8,8 +9,6 @@
 
 namespace glia {
 cudaError_t launch_voxel_pass_fast(const FastParams& P, cudaStream_t st);
-cudaError_t launch_voxel_pass_runs(const FastParams& P, cudaStream_t st);
-cudaError_t launch_voxel_pass_rq(const FastParams& P, cudaStream_t st);
 cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
@@ -22,6 +21,61 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
 using namespace glia;
 #define CK(expr) GLIA_CUDA_CHECK(h, expr)
 static uint64_t pow2ceil(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
+
+
+// ---- value classes of the fast voxel kernel (voxel_fast.cuh) ---------------------------------
+// Reference comparisons, already turned into float compares by fill_channel (api.cu):
+//   util/image_stats.hxx:17-36  lo < v  <=> v >  lo_dn      v < hi <=> v < hi_up     v < bounds[i] <=> v < bound_up[i]
+//   type/feat.hxx:498           v >= t  <=> v >= thr_up
+// Each is a step function of v with one breakpoint c in the form "v >= c" (v > c <=> v >= nextup(c)); the
+// sorted union of the breakpoints partitions the floats into classes on which every statistic is constant.
+static int host_bin_of(const Channel& c, float v) {  // same as bin_of (voxel_pass.cu)
+  if (v > c.lo_dn && v < c.hi_up) {
+    for (int i = 0; i < c.bins; ++i) if (v < c.bound_up[i]) return i;
+    return -1;
+  }
+  return (v <= c.lo_dn) ? 0 : c.bins - 1;
+}
+static bool build_value_classes(const Channel& rc, const Channel& ec, int nThr, const float* thr_up, ValueClasses& V) {
+  memset(&V, 0, sizeof(V));
+  std::vector<float> bp;
+  const Channel* chs[2] = {&rc, &ec};
+  for (const Channel* c : chs) {
+    bp.push_back(nextafterf(c->lo_dn, INFINITY));
+    bp.push_back(c->hi_up);
+    for (int i = 0; i < c->bins; ++i) bp.push_back(c->bound_up[i]);
+  }
+  for (int t = 0; t < nThr; ++t) bp.push_back(thr_up[t]);
+  std::vector<float> u;
+  for (float b : bp) if (b == b && b > 0.0f && b <= 1.0f) u.push_back(b);  // the kernel only sees values in [0, 1]
+  std::sort(u.begin(), u.end());
+  u.erase(std::unique(u.begin(), u.end()), u.end());
+  if ((int)u.size() + 1 > GLIA_FAST_MAX_CLS || nThr > 3) return false;
+  V.nCls = (int)u.size() + 1;
+  for (size_t i = 0; i < u.size(); ++i) V.bound[i] = u[i];
+  for (int j = 0; j < V.nCls; ++j) {
+    const float rep = j == 0 ? 0.0f : u[j - 1];  // smallest member of the class
+    V.rBin[j] = (signed char)host_bin_of(rc, rep);
+    V.eBin[j] = (signed char)host_bin_of(ec, rep);
+    unsigned m = 0;
+    for (int t = 0; t < nThr; ++t) if (rep >= thr_up[t]) m |= 1u << t;
+    V.thr[j] = (unsigned char)m;
+  }
+  // lookup table: the kernel reads entry max(0, cell(v) - 1), which must never exceed the true class:
+  // entry q counts the breakpoints <= lower edge of cell q (entry 0: none, the value may lie below lutLo).
+  V.lutLo = u.empty() ? 0.0f : u.front();
+  const float span = u.empty() ? 0.0f : u.back() - u.front();
+  V.lutScale = span > 0.0f ? 256.0f / span : 0.0f;
+  for (int q = 0; q < 256; ++q) {
+    int n = 0;
+    if (q > 0 && span > 0.0f) {
+      const double edge = (double)V.lutLo + (double)q * ((double)span / 256.0);
+      for (float b : u) if ((double)b <= edge) ++n;
+    }
+    V.lut[q] = (unsigned char)n;
+  }
+  return true;
+}
 
 // inputs -> device, table initialisation, voxel pass (raw tables).  Leaves the stream running.
 int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb) {
@@ -137,59 +191,40 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
   // ---- voxel pass
   CK(cudaEventRecord(h->ev[6], st));
   {
-    const char* force = getenv("GLIA_B200_FORCE_GENERIC");
-    const bool fast = !(force && force[0] == '1') && !P.mask && prm.n_rimg == 1 && prm.n_rlimg == 0 &&
+    ValueClasses vcls;
+    const bool fast = !h->forceGeneric && !h->fastDomainFailed && !P.mask && prm.n_rimg == 1 && prm.n_rlimg == 0 &&
                       prm.n_bimg == 1 && prm.n_thr <= 3 && h->vc.reg[0].data == P.pb &&
                       h->vc.edge[0].data == P.pb && h->vc.reg[0].bins <= 16 && h->vc.edge[0].bins <= 16 &&
-                      (long long)P.X * P.Y * 4 < (1ll << 31);  // tile-relative voxel offsets are 32-bit
+                      (long long)P.X * P.Y * 4 < (1ll << 31) &&  // tile-relative voxel offsets are 32-bit
+                      build_value_classes(h->vc.reg[0], h->vc.edge[0], P.nThr, P.thr_up, vcls);
     h->usedFast = fast;
     if (fast) {
       FastParams F;
       memset(&F, 0, sizeof(F));
       F.labels = P.labels; F.pb = P.pb; F.ndim = P.ndim; F.X = P.X; F.Y = P.Y; F.Z = P.Z;
       F.zBegin = P.zBegin; F.zEnd = P.zEnd; F.zBuf0 = P.zBuf0;
+      // CTA = 8 warps: 256 x 1 voxels per row step in 2D, 32 x 8 in 3D, marching TZ rows / planes.
+      // 512 table slots keep a CTA at ~51 KB (3D) / ~66 KB (2D) of shared memory: 4 / 3 CTAs per SM.
       if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
-      if (getenv("GLIA_B200_WX") && getenv("GLIA_B200_WY")) {  // tile-shape experiments (<= 8 warps)
-        F.warpsX = atoi(getenv("GLIA_B200_WX")); F.warpsY = atoi(getenv("GLIA_B200_WY"));
-        if (F.warpsX < 1 || F.warpsY < 1 || F.warpsX * F.warpsY > 8 || (P.ndim == 2 && F.warpsY != 1)) { F.warpsX = P.ndim == 2 ? 8 : 1; F.warpsY = P.ndim == 2 ? 1 : 8; }
-      }
-      // GLIA_B200_VOXEL=runs selects the experimental v4 kernel (register runs + warp-segment flush,
-      // voxel_runs.cu: parity-green but slower, profiles/r1_v4_notes.txt); default is v3
-      const char* vsel = getenv("GLIA_B200_VOXEL");
-      const bool useRuns = vsel && vsel[0] == 'r';
-      const bool useRq = vsel && vsel[0] == 'q';  // GLIA_B200_VOXEL=queue: v5 run queue (voxel_rq.cu), experimental
-      const char* tzs = getenv("GLIA_B200_TZ");
-      F.TZ = tzs ? atoi(tzs) : (useRuns ? (P.ndim == 3 ? 64 : 32) : (useRq ? 32 : 16));
-      if (F.TZ < 1) F.TZ = 32;
+      F.TZ = h->tuneTZ > 0 ? h->tuneTZ : 16;
+      if (F.TZ + F.warpsY > 32) F.TZ = 32 - F.warpsY;  // y and z occupancy masks share one word
       while (F.TZ > 1 && (long long)P.X * P.Y * (F.TZ + 3) >= (1ll << 31)) F.TZ >>= 1;
       F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);
       F.tilesY = (P.Y + F.warpsY - 1) / F.warpsY;
       F.tilesZ = (P.zEnd - P.zBegin + F.TZ - 1) / F.TZ;
       F.nThr = P.nThr;
-      for (int t = 0; t < P.nThr; ++t) F.thr_up[t] = P.thr_up[t];
-      const Channel& rc = h->vc.reg[0]; const Channel& ec = h->vc.edge[0];
-      F.rBins = rc.bins; F.eBins = ec.bins;
-      F.rLo = rc.lo_dn; F.rHi = rc.hi_up; F.eLo = ec.lo_dn; F.eHi = ec.hi_up;
-      F.rInv = (float)(rc.bins / (prm.rimg[0].hi - prm.rimg[0].lo));
-      F.eInv = (float)(ec.bins / (prm.bimg[0].hi - prm.bimg[0].lo));
-      for (int i = 0; i < 16; ++i) { F.rBound[i] = rc.bound_up[i < rc.bins ? i : rc.bins - 1]; F.eBound[i] = ec.bound_up[i < ec.bins ? i : ec.bins - 1]; }
-      F.sameSpec = rc.bins == ec.bins && rc.lo_dn == ec.lo_dn && rc.hi_up == ec.hi_up &&
-                   memcmp(rc.bound_up, ec.bound_up, sizeof(float) * rc.bins) == 0;
+      F.rBins = h->vc.reg[0].bins; F.eBins = h->vc.edge[0].bins;
+      F.vc = vcls;
       F.reg = P.reg; F.edge = P.edge; F.labelBound = P.labelBound;
       F.regAdd = P.regAdd; F.regMax = P.regMax; F.regF64 = P.regF64;
       F.edgeCap = P.edgeCap; F.edgeKeys = P.edgeKeys; F.edgeAdd = P.edgeAdd; F.edgeMax = P.edgeMax; F.edgeF64 = P.edgeF64;
       F.overflow = P.overflow;
-      // v3: 256 boundary slots + 16-plane tiles keep a CTA at 54 KB / 62 registers -> 4 CTAs per SM
-      // (profiles/r1_v4_notes.txt, "occupancy"); the experimental kernels keep the sizes they were measured with
-      F.regSlots = getenv("GLIA_B200_RSLOTS") ? atoi(getenv("GLIA_B200_RSLOTS")) : 128;
-      F.edgeSlots = getenv("GLIA_B200_ESLOTS") ? atoi(getenv("GLIA_B200_ESLOTS")) : ((useRuns || useRq) ? 512 : 256);
+      F.slots = h->tuneSlots > 0 ? (int)pow2ceil((uint64_t)h->tuneSlots) : 512;
       for (int k = 0; k < nChunks; ++k) {
         if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));
         F.zBegin = zCut[k]; F.zEnd = zCut[k + 1];
         F.tilesZ = (F.zEnd - F.zBegin + F.TZ - 1) / F.TZ;
-        if (useRuns) CK(launch_voxel_pass_runs(F, st));
-        else if (useRq) CK(launch_voxel_pass_rq(F, st));
-        else CK(launch_voxel_pass_fast(F, st));
+        CK(launch_voxel_pass_fast(F, st));
       }
     } else {
       for (int k = 0; k < nChunks; ++k) {
@@ -206,8 +241,13 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
   int ovf = 0;
   CK(cudaMemcpyAsync(&ovf, P.overflow, 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  if (ovf == 2) { h->err = "label value >= label_bound"; return GLIA_E_ARG; }
-  if (ovf == 1) {
+  if (ovf & 2) { h->err = "label value >= label_bound (0xFFFFFFFF is reserved)"; return GLIA_E_ARG; }
+  if (ovf & 4) {  // a value outside [0, 1] (or NaN): the fast kernel's fixed-point sums do not cover it
+    h->fastDomainFailed = true;  // sticky: later volumes of this handle go to the generic kernel directly
+    nChunks = 1; zCut[0] = P.zBegin; zCut[1] = P.zEnd;  // the inputs are resident by now
+    continue;
+  }
+  if (ovf & 1) {
     if (prm.edge_capacity != 0 || cap >= capMax) { h->err = "directed-boundary table full: raise edge_capacity"; return GLIA_E_CAPACITY; }
     cap *= 4;
     if (cap > capMax) cap = capMax;

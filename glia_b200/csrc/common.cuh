@@ -56,7 +56,7 @@ struct VoxParams {
   uint64_t edgeCap;                                    // power of two
   unsigned long long* edgeKeys;                        // [edgeCap], EMPTY = ~0
   uint32_t* edgeAdd; uint32_t* edgeMax; double* edgeF64;
-  int* overflow;   // set to 1 when the edge table is full, 2 when a label >= labelBound
+  int* overflow;   // bit flags: 1 = boundary table full, 2 = label >= labelBound (or 0xFFFFFFFF), 4 = value outside the fast kernel's domain
   // shared-memory privatisation
   int regSlots, edgeSlots;  // powers of two
 };

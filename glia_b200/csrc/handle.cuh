@@ -86,6 +86,9 @@ struct glia_handle {
   bool built = false;
   bool partial = false;  // raw tables valid (glia_b200_build_partial / glia_b200_build)
   bool usedFast = false;
+  bool forceGeneric = false;      // glia_b200_tune(h, "generic", 1): test hook, run the generic voxel kernel
+  bool fastDomainFailed = false;  // a value outside [0, 1] was met: the fast voxel kernel is skipped from then on
+  int tuneTZ = 0, tuneSlots = 0;  // tile depth / table slots of the fast voxel kernel (0 = default)
   long long tableOccupied = 0;  // occupied slots of the boundary table at the last export (shard.cu)
   uint64_t capHint = 0;  // boundary-table capacity that turned out to be needed (grown tables are kept)
 
@@ -110,5 +113,8 @@ struct glia_handle {
   glia::DevBuf bAggMax2, bAggOwn;                         // second-best max words and the boundary holding the best
   glia::DevBuf cubTmp, scalars, rows, sal, keysOut;
   glia::DevBuf regBlocks;                                 // per-region x1/x2 row blocks (featurize.cu)
+  glia::DevBuf orient, tieBuf, firstVox;                  // equal-area orientation bits (orient.cu)
+  bool hasOrient = false;
+  long long orientC = 0;
   glia::DevBuf interest, exportBuf, exportCursor;         // multi-GPU exchange (shard.cu)
 };

@@ -60,7 +60,7 @@ __device__ __forceinline__ long long edge_slot_global(const VoxParams& P, unsign
     h = (h + 1) & mask;
     if (probe > 4096) break;
   }
-  atomicExch(P.overflow, 1);
+  atomicOr(P.overflow, 1);
   return -1;
 }
 
@@ -143,6 +143,7 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
       int c = ((zz + 1) * SY + (ty + hy)) * SX + tx + 1;
       if (!valid[c]) continue;
       uint32_t me = lab[c];
+      if (me == 0xFFFFFFFFu) { atomicOr(P.overflow, 2); continue; }  // reserved: the empty-slot marker of the tables
       // type/neighbor.hxx:78-88 order: d0-, d0+, d1-, d1+, d2-, d2+
       int nvalid = 0; bool found = false; uint32_t nb = 0;
 #define GLIA_VISIT(off)                                                   \
@@ -170,7 +171,7 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
           h = (h + 1) & (uint32_t)(P.regSlots - 1);
         }
         if (!ra) {
-          if (me >= P.labelBound) { atomicExch(P.overflow, 2); curLabel = 0xFFFFFFFFu; continue; }
+          if (me >= P.labelBound) { atomicOr(P.overflow, 2); curLabel = 0xFFFFFFFFu; continue; }
           ra = P.regAdd + (size_t)me * P.reg.nAdd; rm = P.regMax + (size_t)me * P.reg.nMax;
           rf = P.regF64 + (size_t)me * P.reg.nF64;
         }
@@ -219,7 +220,7 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
   for (int s = tid; s < P.regSlots; s += nthreads) {
     uint32_t l = rkeys[s];
     if (l == 0xFFFFFFFFu) continue;
-    if (l >= P.labelBound) { atomicExch(P.overflow, 2); continue; }
+    if (l >= P.labelBound) { atomicOr(P.overflow, 2); continue; }
     flush_rec(P.reg, radd + (size_t)s * P.reg.nAdd, rmax + (size_t)s * P.reg.nMax,
               rf64 + (size_t)s * P.reg.nF64, P.regAdd + (size_t)l * P.reg.nAdd,
               P.regMax + (size_t)l * P.reg.nMax, P.regF64 + (size_t)l * P.reg.nF64);

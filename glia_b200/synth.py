@@ -142,3 +142,67 @@ def random_forest(ntree, mdim, max_depth=12, seed=0, nclass=2, orig_labels=(-1, 
         f["nodeclass"][i, :n] = nc
         f["ndbigtree"][i] = n
     return f
+
+
+# ---- bench forest: 255 trees trained with scikit-learn on feature rows of a small
+# synthetic volume against a synthetic ground truth, exported to the rf_old array layout --------------
+def gt_merge_labels(keys, shape, cell, block=3):
+    """Synthetic ground truth for candidate pairs of a voronoi_volume: superpixels whose grid cells fall into
+    the same block^D group of cells form one true segment.  Returns -1 (merge, BC_LABEL_MERGE) / +1 per pair."""
+    sx = list(shape[::-1])
+    nc = [(s + cell - 1) // cell for s in sx]
+
+    def seg(lab):
+        ci = lab.astype(np.int64) - 1
+        s, mul = np.zeros_like(ci), 1
+        for d in range(len(sx)):
+            c = ci % nc[d]
+            ci = ci // nc[d]
+            s += (c // block) * mul
+            mul *= (nc[d] + block - 1) // block
+        return s
+    return np.where(seg(keys[:, 0]) == seg(keys[:, 1]), -1, 1).astype(np.int32)
+
+
+def sklearn_forest(rows, y, ntree=255, seed=0, max_depth=20):
+    """Trains a scikit-learn forest (x <= t goes left, as classForest) and exports it as rf_old arrays."""
+    from sklearn.ensemble import RandomForestClassifier
+    X = np.ascontiguousarray(rows, dtype=np.float32)  # sklearn trains on float32; thresholds are doubles
+    clf = RandomForestClassifier(n_estimators=ntree, max_depth=max_depth, random_state=seed, n_jobs=-1).fit(X, y)
+    trees = [e.tree_ for e in clf.estimators_]
+    classes = [int(c) for c in clf.classes_]
+    nr = max(t.node_count for t in trees)
+    f = dict(treemap=np.zeros((ntree, nr, 2), np.int32), nodestatus=np.zeros((ntree, nr), np.int32),
+             xbestsplit=np.zeros((ntree, nr)), bestvar=np.zeros((ntree, nr), np.int32),
+             nodeclass=np.zeros((ntree, nr), np.int32), ndbigtree=np.zeros(ntree, np.int32),
+             orig_labels=np.asarray(classes, np.int32))
+    for i, t in enumerate(trees):
+        n = t.node_count
+        leaf = t.children_left == -1
+        f["treemap"][i, :n, 0] = np.where(leaf, 0, t.children_left + 1)
+        f["treemap"][i, :n, 1] = np.where(leaf, 0, t.children_right + 1)
+        f["nodestatus"][i, :n] = np.where(leaf, -1, 1)
+        f["xbestsplit"][i, :n] = t.threshold
+        f["bestvar"][i, :n] = np.where(leaf, 0, t.feature + 1)
+        f["nodeclass"][i, :n] = np.where(leaf, t.value[:, 0, :].argmax(axis=1) + 1, 0)
+        f["ndbigtree"][i] = n
+    return f
+
+
+def mean_path_length(f, X, max_rows=2000):
+    """Mean number of internal nodes a row visits per tree (x <= t goes left): the work unit of RF scoring."""
+    X = np.asarray(X, np.float64)[:max_rows]
+    n, tot = len(X), 0
+    ar = np.arange(n)
+    for t in range(len(f["ndbigtree"])):
+        k = np.zeros(n, np.int64)
+        ns, bv, xb, tm = f["nodestatus"][t], f["bestvar"][t], f["xbestsplit"][t], f["treemap"][t]
+        while True:
+            act = ns[k] != -1
+            if not act.any():
+                break
+            tot += int(act.sum())
+            ka = k[act]
+            left = X[ar[act], bv[ka] - 1] <= xb[ka]
+            k[act] = np.where(left, tm[ka, 0], tm[ka, 1]) - 1
+    return tot / max(n * len(f["ndbigtree"]), 1)

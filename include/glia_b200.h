@@ -93,6 +93,11 @@ GLIA_API const char* glia_b200_last_error(const glia_handle* h);
  * reference's per-image process loop does (gadget/python/script_util.py:6-23). */
 GLIA_API int glia_b200_set_image(glia_handle* h, int kind, int i, const float* data);
 
+/* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
+ * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
+ * kernel, "slots": its shared-memory table slots (0 = default). */
+GLIA_API int glia_b200_tune(glia_handle* h, const char* key, int value);
+
 /* RAG + base statistics.  labels/mask: uint32 volumes (mask may be NULL); pb: float32. */
 GLIA_API int glia_b200_build(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);
 /* R regions, E directed boundaries, C mutual pairs (= initial merge candidates) */

@@ -32,7 +32,7 @@ def test_bench_line_small_2d():
     for k in ("bound", "achieved", "peak", "unit", "frac", "traffic", "kernel"):
         assert k in roof, k
     assert roof["bound"] == "hbm" and abs(roof["frac"] - roof["achieved"] / roof["peak"]) < 1e-12
-    assert {r["kernel"] for r in d["roofline_kernels"]} == {"voxel_pass_fast", "rf_score_smem_kernel"}
+    assert {r["kernel"] for r in d["roofline_kernels"]} == {"voxel_pass_fast", "rf_score"}
     assert roof["launch_ms"] == max(r["launch_ms"] for r in d["roofline_kernels"])
     assert d["gpu_launches"] > 0
     e = d["e2e"]

@@ -307,16 +307,14 @@ def test_merge_order_c1_voronoi():
     assert np.array_equal(rg["sal"], ro["sal"])
 
 
-def test_generic_and_fast_voxel_kernels_agree(monkeypatch):
+def test_generic_and_fast_voxel_kernels_agree():
     """The default configuration takes the fast kernel (voxel_fast.cu); forcing the generic one
     (voxel_pass.cu) must give identical records."""
     lab, pb = synth.voronoi_volume((40, 70, 90), 9, seed=21)
     co, cg = _cfg_pair(pb)
     o = ol.Oracle(lab, pb, co)
     g1 = api.MergeTreeBuilder(lab.shape, cg).build(lab, pb)
-    monkeypatch.setenv("GLIA_B200_FORCE_GENERIC", "1")
-    g2 = api.MergeTreeBuilder(lab.shape, cg).build(lab, pb)
-    monkeypatch.delenv("GLIA_B200_FORCE_GENERIC")
+    g2 = api.MergeTreeBuilder(lab.shape, cg).tune("generic", 1).build(lab, pb)
     for g in (g1, g2):
         _compare_graph(o, g, co)
 
