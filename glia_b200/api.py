@@ -59,7 +59,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_import_edges", "glia_b200_table_load", "glia_b200_finalize_edges", "glia_b200_synth_voronoi",
            "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble",
            "glia_b200_region_presence", "glia_b200_index_regions", "glia_b200_gather_regions",
-           "glia_b200_tune"]
+           "glia_b200_tune", "glia_b200_candidate_ties", "glia_b200_set_tie_orientation",
+           "glia_b200_reference_orientation"]
 
 
 def lib():
@@ -77,6 +78,9 @@ def lib():
         L.glia_b200_last_error.restype = C.c_char_p
         L.glia_b200_build.argtypes = [vp, vp, vp, vp]
         L.glia_b200_tune.argtypes = [vp, C.c_char_p, C.c_int]
+        L.glia_b200_candidate_ties.argtypes = [vp, vp, C.POINTER(C.c_int64)]
+        L.glia_b200_set_tie_orientation.argtypes = [vp, vp]
+        L.glia_b200_reference_orientation.argtypes = [vp, C.c_int64, vp]
         L.glia_b200_counts.argtypes = [vp] + [C.POINTER(C.c_int64)] * 3
         L.glia_b200_row_dim.argtypes = [vp, C.c_int]
         L.glia_b200_get_regions.argtypes = [vp] * 6
@@ -287,6 +291,29 @@ class MergeTreeBuilder:
         """Per-handle knob (include/glia_b200.h: glia_b200_tune)."""
         self._check(lib().glia_b200_tune(self.h, key.encode(), int(value)))
         return self
+
+    def candidate_ties(self):
+        """(tie[C] uint8, count): initial candidates whose two regions have equal areas."""
+        tie = np.zeros(max(self.Cn, 1), np.uint8)
+        n = C.c_int64(0)
+        self._check(lib().glia_b200_candidate_ties(self.h, _addr(tie), C.byref(n)))
+        return tie[:self.Cn], int(n.value)
+
+    def set_tie_orientation(self, second_first):
+        if second_first is None:
+            self._check(lib().glia_b200_set_tie_orientation(self.h, None))
+            return self
+        b = np.ascontiguousarray(second_first, np.uint8)
+        assert len(b) == self.Cn
+        self._keep_orient = b
+        self._check(lib().glia_b200_set_tie_orientation(self.h, _addr(b)))
+        return self
+
+    def reference_orientation(self, reserve_hint=0):
+        """Call order of a reference binary built with this libstdc++ (include/glia_b200.h)."""
+        b = np.zeros(max(self.Cn, 1), np.uint8)
+        self._check(lib().glia_b200_reference_orientation(self.h, int(reserve_hint), _addr(b)))
+        return b[:self.Cn]
 
     def set_image(self, kind, i, data):
         """Re-point image i of kind 0 (rimg) / 1 (rlimg) / 2 (bimg) at another buffer of the same extent."""

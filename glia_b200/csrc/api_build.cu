@@ -257,6 +257,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
   break;
   }
   h->partial = true;
+  h->hasOrient = false;  // orientation bits belong to one build
   return GLIA_OK;
 }
 

@@ -21,7 +21,7 @@ struct GraphView {
 
 __global__ void __launch_bounds__(128)
 init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G,
-                       uint32_t* __restrict__ keys, double* __restrict__ rows) {
+                       const unsigned char* __restrict__ orient, uint32_t* __restrict__ keys, double* __restrict__ rows) {
   long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (c >= G.C) return;
   const int e = G.cand[c], rv = G.rev[e];
@@ -50,7 +50,7 @@ init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant_
       for (int i = 0; i < LE.nF64; ++i) bz.f[i] += G.sF64[(size_t)k * LE.nF64 + i];
     }
   }
-  featurize_row(F, rx, ry, rz, bx, by, bz, pb, nullptr, rows + (size_t)c * F.dim);
+  featurize_row(F, rx, ry, rz, bx, by, bz, pb, nullptr, rows + (size_t)c * F.dim, -1, orient && orient[c]);
 }
 
 // ---- v2: the x1 / x2 blocks of a row depend on ONE base region only, and each region takes part in
@@ -77,8 +77,8 @@ region_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ 
 
 __global__ void __launch_bounds__(128)
 init_candidates_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G, int xi,
-                              const double* __restrict__ blk, uint32_t* __restrict__ keys,
-                              double* __restrict__ rows) {
+                              const double* __restrict__ blk, const unsigned char* __restrict__ orient,
+                              uint32_t* __restrict__ keys, double* __restrict__ rows) {
   long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (c >= G.C) return;
   const int e = G.cand[c], rv = G.rev[e];
@@ -123,7 +123,8 @@ init_candidates_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_co
   const int ld = xi + 2;
   const double* A = blk + (size_t)a * ld;
   const double* B = blk + (size_t)b * ld;
-  const bool swp = A[xi] > B[xi];  // strict >, hmt/main_merge_order_bc.cxx:77-80
+  // strict >, hmt/main_merge_order_bc.cxx:77-80; equal areas keep the reference's call order (orient.cu)
+  const bool swp = A[xi] > B[xi] || (orient && orient[c] && A[xi] == B[xi]);
   const double* B1 = swp ? B : A;
   const double* B2 = swp ? A : B;
   const double a1 = B1[xi], a2 = B2[xi], p1 = B1[xi + 1], p2 = B2[xi + 1];
@@ -200,13 +201,15 @@ int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows) {
   GraphView G = glia_graph_view(h);
   unsigned blocks = (unsigned)((h->C + 127) / 128);
   const glia_params& c = h->prm;
+  // orientation bits of equal-area pairs are only valid for the build they were installed after
+  const unsigned char* orient = (h->hasOrient && h->orientC == h->C) ? h->orient.as<unsigned char>() : nullptr;
   const int xi = c.ndim + 4 + 2 * c.n_thr + 5 * c.n_rimg + c.n_rlimg + 5 * c.n_bimg;
   if (h->fc.simple || !dRows) {
-    init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, dKeys, dRows);
+    init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, orient, dKeys, dRows);
   } else {
     GLIA_CUDA_CHECK(h, h->regBlocks.ensure(8 * (size_t)(h->R + 1) * (xi + 2)));
     region_blocks_kernel<<<(unsigned)((h->R + 127) / 128), 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>());
-    init_candidates_blocks_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>(), dKeys, dRows);
+    init_candidates_blocks_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>(), orient, dKeys, dRows);
     h->launches++;
   }
   h->launches++;

@@ -147,7 +147,9 @@ __device__ double* push_region(const FeatCfg& F, const ShapeFeat& s, const RR& r
 template <class RX, class RY, class RZ, class BX, class BY, class BZ, class PB>
 __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, const RZ& rz,
                               const BX& bx, const BY& by, const BZ& bz, const PB& pb,
-                              const double* sal, double* out, int part = -1) {
+                              const double* sal, double* out, int part = -1, bool tieSwap = false) {
+  // tieSwap: for EQUAL areas the reference keeps the call order; the caller says whether the reference's
+  // call order was (Y, X) (orient.cu) - only the x1 / x2 blocks depend on it.
   // part: -1 = whole row; 0 = x0 (pair terms), 1 / 2 = first / second region block, 3 = merged block.
   // The four parts write disjoint ranges, so four threads can build one row (merge_order.cu).
   ShapeFeat sx, sy, sz;
@@ -156,7 +158,7 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
   if (part < 0 || part == 3) shape_feat(F, rz, bz, sz);
   if (part > 0) {
     if (F.simple) return;
-    const bool sw = sx.area > sy.area;
+    const bool sw = sx.area > sy.area || (tieSwap && sx.area == sy.area);
     const int xi = F.D + 4 + 2 * F.nThr + 5 * F.nR + F.nRL + 5 * F.nB + (sal ? 1 : 0);
     const int x0len = F.dim + (sal ? 5 : 0) - 3 * xi;
     double* q = out + x0len + (size_t)(part - 1) * xi;
@@ -165,7 +167,7 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
     else push_region(F, sz, rz, bz, sal ? sal + 2 : nullptr, q);
     return;
   }
-  const bool swp = sx.area > sy.area;
+  const bool swp = sx.area > sy.area || (tieSwap && sx.area == sy.area);
   const ShapeFeat& s1 = swp ? sy : sx;
   const ShapeFeat& s2 = swp ? sx : sy;
   const int T = F.nThr, lg = F.useLog;

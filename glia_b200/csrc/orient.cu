@@ -12,9 +12,9 @@
 // the same keys in the same order - including the insertion of the scratch key BG_VAL = 0 during the loop
 // (util/struct_merge_bc.hxx:19-20), which can rehash the map in mid-iteration.
 #include <algorithm>
-#include <unordered_map>
 #include <vector>
 #include "handle.cuh"
+#include "host/ref_order.hpp"
 
 namespace glia {
 
@@ -113,34 +113,16 @@ extern "C" int glia_b200_reference_orientation(glia_handle* h, int64_t reserve_h
   std::vector<uint32_t> seq(R);
   for (size_t r = 0; r < R; ++r) seq[r] = (uint32_t)r;
   std::sort(seq.begin(), seq.end(), [&](uint32_t a, uint32_t b) { return first[label[a]] < first[label[b]]; });
-  // the reference's three containers (the mapped type does not influence the order)
-  std::unordered_map<uint32_t, uint32_t> cmap;   // genCountMap: cmap[key] = 1 at first appearance
-  for (uint32_t r : seq) cmap[label[r]] = 1;
-  std::unordered_map<uint32_t, uint32_t> pmap;   // genPointMap: pmap[cp.first] in cmap order
-  for (auto const& cp : cmap) pmap[cp.first];
-  std::unordered_map<uint32_t, uint32_t> rmap;   // TRegionMap::init: emplace in pmap order; value = region index
-  {
-    std::unordered_map<uint32_t, uint32_t> idx;
-    idx.reserve(R);
-    for (size_t r = 0; r < R; ++r) idx[label[r]] = (uint32_t)r;
-    for (auto const& pp : pmap) rmap.emplace(pp.first, idx[pp.first]);
+  std::vector<uint32_t> seqLabel(R);
+  std::vector<unsigned char> hasMutual(R, 0);
+  for (size_t i = 0; i < R; ++i) {
+    const uint32_t r = seq[i];
+    seqLabel[i] = label[r];
+    for (int e = row[r]; e < row[r + 1] && !hasMutual[i]; ++e) hasMutual[i] = rev[e] >= 0;
   }
-  if (reserve_hint > 0) rmap.reserve((size_t)reserve_hint);
-  // TBoundaryTable::init: the first table entry makes initFb insert the scratch region BG_VAL = 0
-  // (erase + merge, util/struct_merge_bc.hxx:19-20); afterwards the size stays constant.
-  std::vector<uint32_t> pos(R, 0xFFFFFFFFu);
-  uint32_t visit = 0;
-  bool scratch = false;
-  for (auto const& rp : rmap) {
-    if (rp.first == 0 && scratch) continue;  // the scratch entry itself (only reachable when a label shares bucket 0)
-    const uint32_t r = rp.second;
-    if (pos[r] == 0xFFFFFFFFu) pos[r] = visit++;
-    if (!scratch) {
-      bool mutual = false;
-      for (int e = row[r]; e < row[r + 1] && !mutual; ++e) mutual = rev[e] >= 0;
-      if (mutual) { rmap.erase(0u); rmap.emplace(0u, 0u); scratch = true; }
-    }
-  }
+  const std::vector<uint32_t> visit = glia_host::reference_visit_order(seqLabel, hasMutual, reserve_hint);
+  std::vector<uint32_t> pos(R);
+  for (size_t i = 0; i < R; ++i) pos[seq[i]] = visit[i];
   for (size_t c = 0; c < C; ++c) {
     const int e = cand[c];
     const uint32_t pa = pos[ea[e]], pb = pos[eb[e]];

@@ -118,8 +118,28 @@ GLIA_API int glia_b200_get_edge_stats(glia_handle* h, int i, uint32_t* hist, dou
 
 /* Initial candidates in ascending (min,max) label order: keys [C][2], rows [C][dim]
  * (host or device; either may be NULL).  Candidate (a,b), a<b, is featurised as
- * fBcFeat(reg a, reg b): for equal areas x1 = a. */
+ * fBcFeat(reg a, reg b): for equal areas x1 = a unless set_tie_orientation says otherwise (below). */
 GLIA_API int glia_b200_init_candidates(glia_handle* h, uint32_t* keys, double* rows);
+/* Equal-area candidates.  fBcFeat swaps its two regions on a strict ">" of the areas
+ * (hmt/main_merge_order_bc.cxx:76-80), so for EQUAL areas x1 is the region TBoundaryTable::init passed first,
+ * i.e. the one its loop over the std::unordered_map of regions meets first (type/boundary_table.hxx:92-107) -
+ * a property of the C++ library, not of the algorithm.  Default here: x1 = smaller label.
+ *   candidate_ties: tie[c] = 1 for initial candidates with equal areas (host buffer, may be NULL), *n_ties = count:
+ *     the complete list of rows that can differ from a reference run by an x1/x2 block swap.
+ *   set_tie_orientation: second_first[c] != 0 makes the larger label x1 when the areas of candidate c tie
+ *     (host buffer of C bytes; NULL restores the default).  Applies to init_candidates, score_candidates and
+ *     merge_order_bc until the next build.
+ *   reference_orientation: fills second_first[C] with the call order of a reference binary built with this
+ *     toolchain's libstdc++, by replaying the reference's three chained unordered_maps (count map in raster
+ *     order of first appearance -> point map -> region map, util/struct.hxx:61-92, type/region_map.hxx:79-95)
+ *     and its loop, including the scratch-region insertion of util/struct_merge_bc.hxx:19-20.  reserve_hint > 0
+ *     applies rmap.reserve(reserve_hint) first (harnesses that make the loop rehash-free do that);
+ *     0 = as hmt/main_merge_order_bc.cxx runs.  Needs the labels (and mask) of the last build still in place;
+ *     whole volumes only. */
+GLIA_API int glia_b200_candidate_ties(glia_handle* h, uint8_t* tie, int64_t* n_ties);
+GLIA_API int glia_b200_set_tie_orientation(glia_handle* h, const uint8_t* second_first);
+GLIA_API int glia_b200_reference_orientation(glia_handle* h, int64_t reserve_hint, uint8_t* second_first);
+
 /* Featurise + RF-score the initial candidates on the device: sal [C] (host or device). */
 GLIA_API int glia_b200_score_candidates(glia_handle* h, const glia_rf* rf, double* sal);
 

@@ -52,6 +52,21 @@ def test_oracle_reproduces_reference_golden(path):
     assert np.array_equal(o.bc_feat(z["order"], sal=z["sal"], init_sal=1.0, sal_bias=0.25), z["bcfeat_rows_sal"])
 
 
+def _swap_x1_x2(row, ndim, simple, dim):
+    """The reference row with the roles of x1 and x2 exchanged (hmt/bc_feat.hxx:232-238 layout)."""
+    r = row.copy()
+    if simple:  # selectFeatures: area1, area2, perim1, perim2, ... (hmt/bc_feat.hxx:247-279); the rest is symmetric
+        r[[0, 1, 2, 3]] = row[[1, 0, 3, 2]]
+        return r
+    xi = ndim + 4 + 2 * 3 + 5 + 5
+    x0 = dim - 3 * xi
+    # x0: |a1-a2|, ./a1, ./a2, |p1-p2|, ./p1, ./p2, bl, bl/a1, bl/a2, bl/p1, bl/p2, vb[t], vb/bl, vb/p1, vb/p2 (3 each)
+    r[[1, 2]] = row[[2, 1]]; r[[4, 5]] = row[[5, 4]]; r[[7, 8]] = row[[8, 7]]; r[[9, 10]] = row[[10, 9]]
+    r[17:20], r[20:23] = row[20:23].copy(), row[17:20].copy()
+    r[x0:x0 + xi], r[x0 + xi:x0 + 2 * xi] = row[x0 + xi:x0 + 2 * xi].copy(), row[x0:x0 + xi].copy()
+    return r
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p)[:-4] for p in GOLD])
 def test_cuda_reproduces_reference_golden(path):
@@ -63,20 +78,64 @@ def test_cuda_reproduces_reference_golden(path):
     assert np.array_equal(r["border"], z["reg_border"])
     assert np.array_equal(e["a"], z["edge_a"]) and np.array_equal(e["b"], z["edge_b"])
     assert np.array_equal(e["count"], z["edge_count"])
-    # initial candidates: the reference featurises equal-area pairs in unordered_map order; rows
-    # of pairs with different areas are orientation-free
     n0 = int(z["n_init"])
     keys, rows = g.init_candidates()
-    gold = {tuple(sorted(k[:2])): z["cand_rows"][i] for i, k in enumerate(z["cand_keys"][:n0])}
+    rk = z["cand_keys"][:n0]
+    gold = {tuple(sorted(k[:2])): (z["cand_rows"][i], int(k[0] > k[1])) for i, k in enumerate(rk)}
     assert len(gold) == len(keys)
     cnt = dict(zip(r["label"].tolist(), r["count"].tolist()))
-    for k, row in zip(keys, rows):
-        if cnt[int(k[0])] == cnt[int(k[1])] and k[0] != min(k):
-            continue
-        ref_row = gold[(int(k[0]), int(k[1]))]
-        if cnt[int(k[0])] == cnt[int(k[1])] and not np.allclose(row, ref_row, rtol=RTOL, atol=1e-12):
-            continue  # equal areas, reference took the other orientation
+    tie, nties = g.candidate_ties()
+    assert nties == int(tie.sum()) == sum(cnt[int(k[0])] == cnt[int(k[1])] for k in keys)
+    # (1) default orientation (x1 = smaller label on equal areas): every row equals the reference row, or - for an
+    #     enumerated equal-area pair that the reference happened to call the other way round - the reference row
+    #     with its x1 / x2 parts exchanged.  Nothing is skipped.
+    nswapped = 0
+    for i, (k, row) in enumerate(zip(keys, rows)):
+        ref_row, ref_second_first = gold[(int(k[0]), int(k[1]))]
+        if tie[i] and ref_second_first:
+            ref_row = _swap_x1_x2(ref_row, lab.ndim, kw["simple"], rows.shape[1]); nswapped += 1
         np.testing.assert_allclose(row, ref_row, rtol=RTOL, atol=1e-12)
+    # (2) the replay of the reference's unordered_map order gives the call order of EVERY candidate of the compiled
+    #     reference (oracle/ref_driver.cxx reserves 4 n + 16 buckets before the loop), ties or not
+    emu = g.reference_orientation(4 * g.R + 16)
+    ref_bits = np.array([gold[(int(k[0]), int(k[1]))][1] for k in keys], np.uint8)
+    assert np.array_equal(emu, ref_bits)
+    # (3) with those bits installed all rows match the reference as they stand
+    g.set_tie_orientation(emu)
+    _, rows2 = g.init_candidates()
+    for k, row in zip(keys, rows2):
+        np.testing.assert_allclose(row, gold[(int(k[0]), int(k[1]))][0], rtol=RTOL, atol=1e-12)
+    assert nswapped == int((tie & emu).sum())
+    g.set_tie_orientation(None)
     np.testing.assert_allclose(g.bc_feat(z["order"]), z["bcfeat_rows"], rtol=RTOL, atol=1e-12)
     np.testing.assert_allclose(g.bc_feat(z["order"], sal=z["sal"], init_sal=1.0, sal_bias=0.25),
                                z["bcfeat_rows_sal"], rtol=RTOL, atol=1e-12)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", [p for p in GOLD if "simple" not in p], ids=lambda p: os.path.basename(p)[:-4])
+def test_cuda_greedy_with_reference_call_order(path):
+    """Greedy merge order with the reference's equal-area call order installed: order and saliencies equal the
+    oracle run that is fed the compiled reference's own swap bits (the oracle is pinned to the reference with them)."""
+    from glia_b200 import api, synth
+    z, lab, pb, mask, kw = _load(path)
+    co, cg = ol.default_config(pb, **kw), api.default_config(pb, **kw)
+    o = ol.Oracle(lab, pb, co, mask=mask)
+    g = api.MergeTreeBuilder(lab.shape, cg).build(lab, pb, mask)
+    n0 = int(z["n_init"])
+    rk = z["cand_keys"][:n0]
+    ks = np.sort(rk[:, :2], axis=1)
+    perm = np.lexsort((ks[:, 1], ks[:, 0]))
+    swap = (rk[perm, 0] > rk[perm, 1]).astype(np.uint8)
+    assert np.array_equal(g.reference_orientation(4 * g.R + 16), swap)
+    g.set_tie_orientation(swap)
+    _, rowo = o.init_candidates(swap=swap)
+    _, rowg = g.init_candidates()
+    cols = np.flatnonzero((rowo == rowg).all(axis=0))
+    # the forest looks at the x1 / x2 blocks, where the orientation shows
+    f = synth.random_forest(15, o.row_dim(), max_depth=5, seed=3, thr_pool=rowg, features=cols)
+    orf, grf = ol.OracleRF.from_arrays(f, o.row_dim()), api.Forest.from_arrays(f, o.row_dim())
+    ro = o.greedy(rf=orf, init_swap=swap)
+    rg = g.merge_order_bc(grf)
+    assert np.array_equal(rg["order"], ro["order"])
+    assert np.array_equal(rg["sal"], ro["sal"])
