@@ -339,9 +339,13 @@ def main():
 
     def new_builder(pb_ptr, device_pointers):
         spec = [(pb_ptr, 16, 0.0, 1.0)]
-        return api.MergeTreeBuilder(shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR), device=local_rank,
-                                    device_pointers=device_pointers, label_bound=label_bound,
-                                    stream=stream if device_pointers else None)
+        b = api.MergeTreeBuilder(shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=THR), device=local_rank,
+                                 device_pointers=device_pointers, label_bound=label_bound,
+                                 stream=stream if device_pointers else None)
+        for key in ("tz", "slots"):  # kernel-shape experiments of the harness (the library reads no environment)
+            if os.environ.get("GLIA_BENCH_" + key.upper()):
+                b.tune(key, int(os.environ["GLIA_BENCH_" + key.upper()]))
+        return b
 
     # ONE handle for the stream of inputs (its tables are scratch); only the inputs rotate
     builders = [new_builder(sets[0][1].data_ptr(), True)]

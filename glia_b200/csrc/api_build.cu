@@ -15,6 +15,7 @@ cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cu
 int glia_finalize_graph(glia_handle* h);
 int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
 int glia_rf_label_index(const glia_rf* m, int label);
+int glia_score_fused_device(glia_handle* h, const glia_rf* rf, int labelIdx, double* dSal);
 int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, int labelIdx,
                          int* dVotes, double* dProb, cudaStream_t st);
 
@@ -417,17 +418,27 @@ extern "C" int glia_b200_score_candidates(glia_handle* h, const glia_rf* rf, dou
   CK(cudaSetDevice(h->prm.device));
   const size_t C = (size_t)h->C, dim = (size_t)h->fc.dim;
   if (!C) return GLIA_OK;
-  CK(h->rows.ensure(8 * C * dim));
   double* dSal = sal;
   if (!h->prm.device_pointers) { CK(h->sal.ensure(8 * C)); dSal = h->sal.as<double>(); }
   CK(cudaEventRecord(h->ev[3], h->stream));
-  int s = glia_featurize_init_device(h, nullptr, h->rows.as<double>());
-  if (s) return s;
-  CK(cudaEventRecord(h->ev[4], h->stream));
-  s = glia_rf_score_device(rf, h->rows.as<double>(), C, (int)dim, li, nullptr, dSal, h->stream);
-  h->launches++;
-  if (s) { h->err = "rf kernel launch failed"; return s; }
-  CK(cudaEventRecord(h->ev[5], h->stream));
+  // fused: rows are featurised into the shared-memory tile of the forest walk (score_fused.cu); ms[2] then holds the
+  // per-region block stage only and ms[3] the fused kernel
+  int s = h->noFuse ? GLIA_E_STATE : glia_score_fused_device(h, rf, li, dSal);
+  if (s == GLIA_OK) {
+    CK(cudaEventRecord(h->ev[4], h->stream));
+    CK(cudaEventRecord(h->ev[5], h->stream));
+    h->lastFused = true;
+  } else if (s == GLIA_E_STATE) {
+    h->lastFused = false;
+    CK(h->rows.ensure(8 * C * dim));
+    s = glia_featurize_init_device(h, nullptr, h->rows.as<double>());
+    if (s) return s;
+    CK(cudaEventRecord(h->ev[4], h->stream));
+    s = glia_rf_score_device(rf, h->rows.as<double>(), C, (int)dim, li, nullptr, dSal, h->stream);
+    h->launches++;
+    if (s) { h->err = "rf kernel launch failed"; return s; }
+    CK(cudaEventRecord(h->ev[5], h->stream));
+  } else return s;
   if (!h->prm.device_pointers) CK(cudaMemcpyAsync(sal, dSal, 8 * C, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   float ms = 0;

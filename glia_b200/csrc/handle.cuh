@@ -67,8 +67,9 @@ struct glia_rf {
   int* d_treeOff = nullptr;      // [ntree+1]
   void* d_nodes = nullptr;       // packed nodes
   void* d_nodesW = nullptr;      // walk encoding for rf_score_smem_kernel: leaves are self-loops (rf.cu)
-  void* d_nodes8 = nullptr;      // 8-byte nodes {float threshold, left << 8 | feature} (rf.cu v4)
-  double* d_thr = nullptr;       // exact thresholds, same indexing as d_nodes8
+  void* d_blocks = nullptr;      // two-level 32-byte blocks (rf.cu v5, two-class forests)
+  int* d_blockRoot = nullptr;    // [ntree] root block of every tree
+  long long nBlocks = 0;
   int maxDepth = 0;
   RfDist dist = {1, 0, 0, 0.0, {0, 0, 0}, {0, 0, 0}};  // dist.te[0] = ntree for a plain forest
 };
@@ -88,6 +89,7 @@ struct glia_handle {
   bool usedFast = false;
   bool forceGeneric = false;      // glia_b200_tune(h, "generic", 1): test hook, run the generic voxel kernel
   bool fastDomainFailed = false;  // a value outside [0, 1] was met: the fast voxel kernel is skipped from then on
+  bool noFuse = false, lastFused = false;  // glia_b200_tune(h, "nofuse", 1): score through materialised rows
   int tuneTZ = 0, tuneSlots = 0;  // tile depth / table slots of the fast voxel kernel (0 = default)
   long long tableOccupied = 0;  // occupied slots of the boundary table at the last export (shard.cu)
   uint64_t capHint = 0;  // boundary-table capacity that turned out to be needed (grown tables are kept)

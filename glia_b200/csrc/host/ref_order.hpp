@@ -6,6 +6,7 @@
 // resulting order belongs to the C++ library; replaying the same containers with the same keys reproduces it for
 // the libstdc++ this file is compiled with.  The mapped types do not influence the order.
 #pragma once
+#include <stddef.h>
 #include <stdint.h>
 #include <unordered_map>
 #include <vector>

@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <queue>
 #include "handle.cuh"
+#include "rf_walk.cuh"
 
 namespace glia {
 
@@ -63,11 +64,6 @@ rf_score_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOf
 
 // node as one 16-byte load: {thr.lo, thr.hi, left, feat}
 __device__ __forceinline__ int4 rf_node(const int4* np, int k) { return __ldg(np + k); }
-__device__ __forceinline__ double rf_lds(uint32_t a) {
-  double v;
-  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
-  return v;
-}
 // alg/rf.hxx:35-36 -> classForest: x <= threshold goes left, anything else (NaN too) goes right.
 // Nodes are in the walk encoding (rf_build_device): leaf = sign bit of the feature word, class in the low word.
 // A walk that has reached its leaf issues no loads.  Measured on B200 (profiles/r1_rf_v4_notes.txt): stepping
@@ -82,7 +78,6 @@ __device__ __forceinline__ double rf_lds(uint32_t a) {
 // copy; the v1 kernel re-streamed them from DRAM ~85 times, profiles/r1_v1_ncu_rf.txt); four
 // threads share a candidate and split the trees, two trees in flight per thread; sibling pairs
 // are 32-byte aligned so that one L2 sector serves either outcome of a split.
-#define RF_CPB 64
 template <bool ENS, int NS>  // NS: tree slices per candidate (CTA = 64 * NS threads); ENS: model ensemble, the tree range depends on the row (alg/rf.hxx:97-98)
 __global__ void __launch_bounds__(64 * NS, NS == 8 ? 3 : 6)
 rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ treeOff, const RfDist dist,
@@ -142,59 +137,44 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
 }
 
 
-// v4: 8-byte nodes {float(threshold), left << 8 | feature} and float rows in shared memory.  Rounding to
-// float (round-to-nearest, monotone) keeps the order: f(x) < f(t) => x < t and f(x) > f(t) => x > t, so
-// the float compare decides every split except when both round to the same float (ties, or values within
-// one float ulp); only then the exact doubles (row in global memory, threshold side array) are compared,
-// which keeps the votes bit-exact.  Half the node bytes = half the L1/L2 sectors per warp-level fetch.
-struct __align__(8) RfNode8 { float thr; uint32_t w; };  // w = left << 8 | feature (255 = leaf, left = class)
-#define RF8_CPB 64
-#define RF8_STEP(n, k)                                                                         \
-  { const int f_ = (int)(n.w & 255u); const float xf_ = x[f_];                                  \
-    bool le_ = xf_ < n.thr;                                                                     \
-    if (!(xf_ < n.thr) && !(xf_ > n.thr)) le_ = __ldg(xg + f_) <= __ldg(thr64 + k);             \
-    k = (int)(n.w >> 8) + (le_ ? 0 : 1); n = nodes[k]; }
-__global__ void __launch_bounds__(256)
-rf_score_f32_kernel(const RfNode8* __restrict__ nodes, const double* __restrict__ thr64,
-                    const int* __restrict__ treeOff, int ntree, int labelIdx,
-                    const double* __restrict__ X, size_t N, int D, int ldRow, double* __restrict__ prob) {
-  extern __shared__ __align__(16) float frow[];
-  __shared__ int svote[RF8_CPB];
-  const size_t c0 = (size_t)blockIdx.x * RF8_CPB;
-  const int ncand = (int)min((size_t)RF8_CPB, N - c0);
+template <bool ENS, int NS>  // NS tree slices per candidate (CTA = 64 * NS threads)
+__global__ void __launch_bounds__(64 * NS, NS == 8 ? 2 : 4)
+rf_score_blk_kernel(const RfBlock* __restrict__ blocks, const int* __restrict__ treeRoot, const RfDist dist,
+                    int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
+                    double* __restrict__ prob) {
+  extern __shared__ __align__(16) double srow[];
+  const size_t c0 = (size_t)blockIdx.x * RF_CPB;
+  const int ncand = (int)min((size_t)RF_CPB, N - c0);
   for (int i = threadIdx.x; i < ncand * D; i += blockDim.x) {
     int c = i / D, f = i - c * D;
-    frow[c * ldRow + f] = (float)X[c0 * D + i];
+    srow[c * ldRow + f] = X[c0 * D + i];
   }
-  if (threadIdx.x < RF8_CPB) svote[threadIdx.x] = 0;
+  __shared__ int svote[RF_CPB];
+  __shared__ int sntree[RF_CPB];
+  if (threadIdx.x < RF_CPB) svote[threadIdx.x] = 0;
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cand = (warp & 1) * 32 + lane, slice = warp >> 1;  // warp = 32 candidates on the same trees
+  const int cand = (warp & 1) * 32 + lane, slice = warp >> 1;
   if (cand < ncand) {
-    const float* x = frow + cand * ldRow;
-    const double* xg = X + (c0 + cand) * (size_t)D;
-    int hits = 0, t = slice;
-    for (; t + 12 < ntree; t += 16) {  // four trees in flight
-      int ka = __ldg(treeOff + t), kb = __ldg(treeOff + t + 4), kc = __ldg(treeOff + t + 8), kd = __ldg(treeOff + t + 12);
-      RfNode8 na = nodes[ka], nb = nodes[kb], nc = nodes[kc], nd = nodes[kd];
-      while ((na.w & 255u) != 255u || (nb.w & 255u) != 255u || (nc.w & 255u) != 255u || (nd.w & 255u) != 255u) {
-        if ((na.w & 255u) != 255u) RF8_STEP(na, ka)
-        if ((nb.w & 255u) != 255u) RF8_STEP(nb, kb)
-        if ((nc.w & 255u) != 255u) RF8_STEP(nc, kc)
-        if ((nd.w & 255u) != 255u) RF8_STEP(nd, kd)
-      }
-      hits += ((int)(na.w >> 8) == labelIdx) + ((int)(nb.w >> 8) == labelIdx) + ((int)(nc.w >> 8) == labelIdx) + ((int)(nd.w >> 8) == labelIdx);
+    const double* x = srow + cand * ldRow;
+    const int mdl = ENS ? dist.pick(x) : 0;
+    const int tbeg = ENS ? dist.begin(mdl) : 0, ntree = ENS ? dist.end(mdl) : dist.te[0];
+    if (slice == 0) sntree[cand] = ntree - tbeg;
+    const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
+    const RfBlock* bp = blocks;
+    int hits = 0, t = tbeg + slice;
+    for (; t + NS < ntree; t += 2 * NS) {  // two walks in flight
+      BlkRegs a = rf_block(bp, (uint32_t)__ldg(treeRoot + t)), b = rf_block(bp, (uint32_t)__ldg(treeRoot + t + NS));
+      while (!(a.base & b.base & RFB_DONE)) { RFB_STEP(a, hits) RFB_STEP(b, hits) }
     }
-    for (; t < ntree; t += 4) {
-      int k = __ldg(treeOff + t);
-      RfNode8 n = nodes[k];
-      while ((n.w & 255u) != 255u) RF8_STEP(n, k)
-      hits += ((int)(n.w >> 8) == labelIdx);
+    for (; t < ntree; t += NS) {
+      BlkRegs a = rf_block(bp, (uint32_t)__ldg(treeRoot + t));
+      while (!(a.base & RFB_DONE)) { RFB_STEP(a, hits) }
     }
     atomicAdd(&svote[cand], hits);
   }
   __syncthreads();
-  if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)ntree;
+  if (threadIdx.x < ncand) prob[c0 + threadIdx.x] = (double)svote[threadIdx.x] / (double)sntree[threadIdx.x];
 }
 
 }  // namespace glia
@@ -258,20 +238,52 @@ static int rf_build_device(glia_rf* m) {
     if (cudaMalloc(&m->d_nodesW, sizeof(RfNode) * w.size()) != cudaSuccess) return GLIA_E_CUDA;
     if (cudaMemcpy(m->d_nodesW, w.data(), sizeof(RfNode) * w.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
   }
-  // 8-byte nodes + exact thresholds for rf_score_f32_kernel (features < 255, node ids < 2^24)
-  if (m->mdim <= 254 && nodes.size() < (1u << 24)) {
-    std::vector<RfNode8> n8(nodes.size());
-    std::vector<double> thr(nodes.size());
-    for (size_t i = 0; i < nodes.size(); ++i) {
-      thr[i] = nodes[i].thr;
-      n8[i].thr = (float)nodes[i].thr;
-      n8[i].w = nodes[i].feat >= 0 ? ((uint32_t)nodes[i].left << 8) | (uint32_t)nodes[i].feat
-                                   : ((uint32_t)nodes[i].left << 8) | 255u;
+  // two-level blocks (rf_score_blk_kernel): two classes, features < 256, block ids < 2^31
+  if (m->nclass == 2 && m->mdim <= 255) {
+    std::vector<RfBlock> blk;
+    std::vector<int> root(m->ntree);
+    for (int t = 0; t < m->ntree; ++t) {
+      std::queue<std::pair<int, uint32_t>> q;  // (node index in `nodes`, block index)
+      root[t] = (int)blk.size();
+      blk.push_back(RfBlock{0.0, 0.0, 0.0, 0u, 0u});
+      q.push({treeOff[t], (uint32_t)root[t]});
+      while (!q.empty()) {
+        auto cur = q.front(); q.pop();
+        const RfNode& r = nodes[cur.first];
+        RfBlock B{0.0, 0.0, 0.0, 0u, 0u};
+        uint32_t leaf = 0, cls = 0;
+        int next[4] = {-1, -1, -1, -1};
+        if (r.feat < 0) {  // a tree that is a single leaf: every outcome ends here
+          leaf = 0xF; cls = r.left ? 0xFu : 0u;
+        } else {
+          B.t0 = r.thr; B.meta = (uint32_t)r.feat;
+          for (int c = 0; c < 2; ++c) {
+            const RfNode& ch = nodes[r.left + c];
+            if (ch.feat < 0) { leaf |= 3u << (2 * c); if (ch.left) cls |= 3u << (2 * c); continue; }
+            (c ? B.t2 : B.t1) = ch.thr;
+            B.meta |= (uint32_t)ch.feat << (8 + 8 * c);
+            for (int g = 0; g < 2; ++g) {
+              const RfNode& gc = nodes[ch.left + g];
+              const int o = 2 * c + g;
+              if (gc.feat < 0) { leaf |= 1u << o; if (gc.left) cls |= 1u << o; }
+              else next[o] = ch.left + g;
+            }
+          }
+        }
+        B.meta |= leaf << 24 | cls << 28;
+        B.base = (uint32_t)blk.size();
+        for (int o = 0; o < 4; ++o)
+          if (next[o] >= 0) { q.push({next[o], (uint32_t)blk.size()}); blk.push_back(RfBlock{0.0, 0.0, 0.0, 0u, 0u}); }
+        blk[cur.second] = B;
+      }
     }
-    if (cudaMalloc(&m->d_nodes8, sizeof(RfNode8) * n8.size()) != cudaSuccess) return GLIA_E_CUDA;
-    if (cudaMalloc((void**)&m->d_thr, 8 * thr.size()) != cudaSuccess) return GLIA_E_CUDA;
-    if (cudaMemcpy(m->d_nodes8, n8.data(), sizeof(RfNode8) * n8.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
-    if (cudaMemcpy(m->d_thr, thr.data(), 8 * thr.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+    if (blk.size() < 0x7FFFFFFFull) {
+      if (cudaMalloc(&m->d_blocks, sizeof(RfBlock) * blk.size()) != cudaSuccess) return GLIA_E_CUDA;
+      if (cudaMalloc((void**)&m->d_blockRoot, 4 * root.size()) != cudaSuccess) return GLIA_E_CUDA;
+      if (cudaMemcpy(m->d_blocks, blk.data(), sizeof(RfBlock) * blk.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+      if (cudaMemcpy(m->d_blockRoot, root.data(), 4 * root.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+      m->nBlocks = (long long)blk.size();
+    }
   }
   return GLIA_OK;
 }
@@ -436,8 +448,8 @@ extern "C" void glia_b200_rf_destroy(glia_rf* m) {
   if (m->d_nodes) cudaFree(m->d_nodes);
   if (m->d_treeOff) cudaFree(m->d_treeOff);
   if (m->d_nodesW) cudaFree(m->d_nodesW);
-  if (m->d_nodes8) cudaFree(m->d_nodes8);
-  if (m->d_thr) cudaFree(m->d_thr);
+  if (m->d_blocks) cudaFree(m->d_blocks);
+  if (m->d_blockRoot) cudaFree(m->d_blockRoot);
   delete m;
 }
 
@@ -463,39 +475,31 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
   if (dVotes)
     rf_score_kernel<true><<<blocks, 128, 128 * m->nclass * sizeof(int), st>>>(
         (const RfNode*)m->d_nodes, m->d_treeOff, m->dist, m->nclass, labelIdx, dX, N, D, dVotes, dProb);
-  else if (m->d_nodes8 && m->dist.n == 1 && getenv("GLIA_B200_RF_F32") &&  // experiment: exact, but 23 % slower than the 16-byte kernel on C5
-             sizeof(float) * (size_t)RF8_CPB * (D | 1) <= 200 * 1024) {
-    const int ldRow = D | 1;  // odd stride: the 32 candidates of a warp read one feature from 32 banks
-    const size_t smem = sizeof(float) * (size_t)RF8_CPB * ldRow;
-    static bool attr8 = false;
-    if (!attr8) { cudaFuncSetAttribute(rf_score_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr8 = true; }
-    rf_score_f32_kernel<<<(unsigned)((N + RF8_CPB - 1) / RF8_CPB), 256, smem, st>>>(
-        (const RfNode8*)m->d_nodes8, m->d_thr, m->d_treeOff, m->ntree, labelIdx, dX, N, D, ldRow, dProb);
-  } else {
-    int ldRow = D | 1;  // odd stride (in doubles): rows start on different banks
-    size_t smem = sizeof(double) * (size_t)RF_CPB * ldRow;
-    if (smem <= 200 * 1024) {
-      static bool attr = false;
-      if (!attr) {
-        cudaFuncSetAttribute(rf_score_smem_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        cudaFuncSetAttribute(rf_score_smem_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        cudaFuncSetAttribute(rf_score_smem_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr = true;
-      }
-      const unsigned nb = (unsigned)((N + RF_CPB - 1) / RF_CPB);
-      // wide rows leave room for only 3-4 CTAs of staged rows per SM: spread a candidate's trees over 8 warps
-      // instead of 4 so that the SM still holds 64 warps (C2: 0.91 -> 0.69 ms, profiles/r1_rf_v4_notes.txt)
-      static const int nsEnv = getenv("GLIA_B200_RF_NS") ? atoi(getenv("GLIA_B200_RF_NS")) : 0;
-      const int ns = nsEnv ? nsEnv : (smem > 28 * 1024 ? 8 : 4);
-      if (m->dist.n > 1)
-        rf_score_smem_kernel<true, 4><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
-      else if (ns == 8)
-        rf_score_smem_kernel<false, 8><<<nb, 512, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
-      else
-        rf_score_smem_kernel<false, 4><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
-    } else {
+  else {
+    const int ldRow = D | 1;  // odd stride (in doubles): rows start on different banks
+    const size_t smem = sizeof(double) * (size_t)RF_CPB * ldRow;
+    const unsigned nb = (unsigned)((N + RF_CPB - 1) / RF_CPB);
+    if (smem > 200 * 1024) {
       rf_score_kernel<false><<<blocks, 128, 0, st>>>((const RfNode*)m->d_nodes, m->d_treeOff, m->dist,
                                                      m->nclass, labelIdx, dX, N, D, nullptr, dProb);
+    } else if (m->d_blocks) {
+      // wide rows leave room for only a few CTAs of staged rows per SM: spread a candidate's trees over 8 warps
+      // instead of 4 so that the SM still holds enough warps (profiles/r1_rf_v4_notes.txt)
+      const bool wide = smem > 28 * 1024;
+      const RfBlock* bl = (const RfBlock*)m->d_blocks;
+#define RF_LAUNCH(ENS_, NS_)                                                                                    \
+      { cudaFuncSetAttribute(rf_score_blk_kernel<ENS_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
+        rf_score_blk_kernel<ENS_, NS_><<<nb, 64 * NS_, smem, st>>>(bl, m->d_blockRoot, m->dist, labelIdx, dX, N, D, ldRow, dProb); }
+      if (m->dist.n > 1) { if (wide) RF_LAUNCH(true, 8) else RF_LAUNCH(true, 4) }
+      else { if (wide) RF_LAUNCH(false, 8) else RF_LAUNCH(false, 4) }
+#undef RF_LAUNCH
+    } else {  // more than two classes: one 16-byte node per level
+      cudaFuncSetAttribute(rf_score_smem_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      cudaFuncSetAttribute(rf_score_smem_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (m->dist.n > 1)
+        rf_score_smem_kernel<true, 4><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
+      else
+        rf_score_smem_kernel<false, 4><<<nb, 256, smem, st>>>((const RfNode*)m->d_nodesW, m->d_treeOff, m->dist, labelIdx, dX, N, D, ldRow, dProb);
     }
   }
   return cudaGetLastError() == cudaSuccess ? GLIA_OK : GLIA_E_CUDA;
@@ -503,7 +507,7 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
 
 extern "C" int glia_b200_rf_score(const glia_rf* m, const double* X, size_t N, int D, int label,
                                   int* votes, double* prob, int device_pointers, void* stream) {
-  if (!m || !X || D < m->mdim) return GLIA_E_ARG;
+  if (!m || !X || D < m->mdim || (!votes && !prob)) return GLIA_E_ARG;
   int li = glia_rf_label_index(m, label);
   if (li < 0) return GLIA_E_ARG;  // ml/rf/rf.hxx:370 perr
   if (cudaSetDevice(m->device) != cudaSuccess) return GLIA_E_CUDA;

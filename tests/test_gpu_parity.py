@@ -362,11 +362,10 @@ def test_set_image_rebinds_inputs():
     _same_graph(g, api.MergeTreeBuilder(shape, cfg(pb_)).build(lb_, pb_))
 
 
-def test_rf_float_filter_is_exact_on_near_ties(monkeypatch):
-    """The prob-only RF kernel compares float-rounded features against float-rounded thresholds and
-    falls back to the exact doubles when they round to the same float (rf.cu v4): rows that sit
-    exactly on thresholds, one double ulp and 1e-9 relative beside them must score exactly as the
-    oracle (and as the 16-byte double kernel)."""
+def test_rf_block_kernel_is_exact_on_near_ties():
+    """The prob-only RF kernel walks two tree levels per 32-byte block (rf.cu v5, exact double thresholds):
+    rows that sit exactly on thresholds, one double ulp and 1e-9 relative beside them must score exactly
+    as the oracle (and as the per-node kernel that also returns the votes)."""
     rng = np.random.default_rng(3)
     d = 37
     pool = rng.random((512, d)) * rng.choice([1e-3, 1.0, 1e6], size=(1, d))
@@ -376,13 +375,10 @@ def test_rf_float_filter_is_exact_on_near_ties(monkeypatch):
                         base * (1 + 1e-9), base * (1 - 1e-9), rng.random((3000, d))])
     orf, grf = ol.OracleRF.from_arrays(f, d), api.Forest.from_arrays(f, d)
     vo, po = orf.predict(X)
-    monkeypatch.setenv("GLIA_B200_RF_F32", "1")
-    _, pg = grf.predict(X, want_votes=False)   # float-filter kernel (experimental, off by default)
-    monkeypatch.delenv("GLIA_B200_RF_F32")
-    _, pg3 = grf.predict(X, want_votes=False)  # default prob-only kernel
+    _, pg3 = grf.predict(X, want_votes=False)  # default prob-only kernel (two-level blocks)
     assert np.array_equal(po, pg3)
-    vg, pg2 = grf.predict(X, want_votes=True)  # 16-byte double nodes
-    assert np.array_equal(po, pg) and np.array_equal(po, pg2) and np.array_equal(vo, vg)
+    vg, pg2 = grf.predict(X, want_votes=True)  # one 16-byte node per level
+    assert np.array_equal(po, pg2) and np.array_equal(vo, vg)
 
 
 def _ensemble_pick(x, dim0, dim1, thr):
