@@ -407,28 +407,40 @@ def main():
         # two slices in flight per GPU (two handles, each with its own stream, driven by two host
         # threads): the upload of slice i+1 overlaps graph/featurise/RF of slice i.  Every step still
         # copies its inputs from pinned host memory and reads its saliencies back.
-        nin = int(os.environ.get("GLIA_BENCH_INFLIGHT", "2")) if 16 * nvox <= 4 * 2 ** 30 else 1
+        # A 3D volume is uploaded from ONE pinned host copy by both in-flight handles (8.6 GB of pinned memory per
+        # copy at 1024^3; the source of an upload is read-only); 2D slices rotate through distinct host buffers.
+        nin = int(os.environ.get("GLIA_BENCH_INFLIGHT", "2"))
         host = []
         for j in range(nin):
-            hl = torch.empty(nvox, dtype=torch.int32).pin_memory()
-            hp = torch.empty(nvox, dtype=torch.float32).pin_memory()
-            hl.copy_(sets[j % nsets][0]); hp.copy_(sets[j % nsets][1])
+            if nd == 3 and j > 0:
+                hl, hp = host[0][4], host[0][5]
+            else:
+                hl = torch.empty(nvox, dtype=torch.int32, pin_memory=True)
+                hp = torch.empty(nvox, dtype=torch.float32, pin_memory=True)
+                hl.copy_(sets[j % nsets][0]); hp.copy_(sets[j % nsets][1])
             hln, hpn = hl.numpy().view(np.uint32).reshape(shape), hp.numpy().reshape(shape)
             host.append((hln, hpn, new_builder(hpn, False),
                          torch.empty(int(Cn * 1.5) + 64, dtype=torch.float64).pin_memory().numpy(), hl, hp))
         n_e2e = max(2, min(args.steps, 6))
         n_e2e = (n_e2e + nin - 1) // nin * nin
         for hln, hpn, hb, hsal, _, _ in host:
-            for i in range(2):
+            for i in range(2 if nd == 2 else 1):
                 hb.build(hln, hpn); hb.score_candidates(forest, hsal)
         errs = []
+        # 3D: the two in-flight volumes take turns on the PCIe link (an upload runs at full rate while the other
+        # volume is being featurised and scored) instead of sharing it
+        turn = threading.Lock() if nd == 3 else None
 
         def worker(j):
             hln, hpn, hb, hsal, _, _ = host[j]
             try:
                 torch.cuda.set_device(local_rank)
                 for i in range(j, n_e2e, nin):
-                    hb.build(hln, hpn)
+                    if turn is not None:
+                        with turn:
+                            hb.build(hln, hpn)
+                    else:
+                        hb.build(hln, hpn)
                     hb.score_candidates(forest, hsal)
             except BaseException as e:  # noqa: BLE001
                 errs.append(e)
@@ -451,6 +463,21 @@ def main():
                "in_flight": nin}
         for x in host:
             x[2].close()
+        # the ceiling of this leg: the same pinned buffers copied to the device with no kernel at all
+        dl, dp = sets[0][0], sets[0][1]
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(n_e2e):
+            dl.copy_(host[i % nin][4], non_blocking=True); dp.copy_(host[i % nin][5], non_blocking=True)
+        torch.cuda.synchronize()
+        dth = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dth], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dth = float(t.item())
+        e2e["h2d_only_ms_per_step"] = 1e3 * dth / n_e2e
+        e2e["h2d_only_gb_s_per_gpu"] = 8 * nvox * n_e2e / dth / 1e9
+        e2e["frac_of_h2d_ceiling"] = dth / dt
 
     if rank != 0:
         if world > 1:

@@ -166,7 +166,6 @@ extern "C" int glia_b200_set_image(glia_handle* h, int kind, int i, const float*
 extern "C" int glia_b200_tune(glia_handle* h, const char* key, int value) {
   if (!h || !key) return GLIA_E_ARG;
   if (!strcmp(key, "generic")) h->forceGeneric = value != 0;
-  else if (!strcmp(key, "nofuse")) h->noFuse = value != 0;
   else if (!strcmp(key, "tz")) { if (value < 0 || value > 31) return GLIA_E_ARG; h->tuneTZ = value; }
   else if (!strcmp(key, "slots")) { if (value < 0 || value > 2048) return GLIA_E_ARG; h->tuneSlots = value; }
   else return GLIA_E_ARG;

@@ -15,7 +15,6 @@ cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cu
 int glia_finalize_graph(glia_handle* h);
 int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
 int glia_rf_label_index(const glia_rf* m, int label);
-int glia_score_fused_device(glia_handle* h, const glia_rf* rf, int labelIdx, double* dSal);
 int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, int labelIdx,
                          int* dVotes, double* dProb, cudaStream_t st);
 
@@ -74,6 +73,14 @@ static bool build_value_classes(const Channel& rc, const Channel& ec, int nThr, 
       for (float b : u) if ((double)b <= edge) ++n;
     }
     V.lut[q] = (unsigned char)n;
+  }
+  // the kernel starts from lut[max(0, cell - 1)] and takes at most two steps up: a value of cell c (or, by float
+  // rounding of the cell index, c + 1) must not lie more than two breakpoints above that entry
+  for (int c = 0; c < 256 && span > 0.0f; ++c) {
+    const double hi = (double)V.lutLo + (double)(c + 2) * ((double)span / 256.0);
+    int n = 0;
+    for (float b : u) if ((double)b <= hi) ++n;
+    if (n - (int)V.lut[c > 0 ? c - 1 : 0] > 2) return false;
   }
   return true;
 }
@@ -196,7 +203,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
     const bool fast = !h->forceGeneric && !h->fastDomainFailed && !P.mask && prm.n_rimg == 1 && prm.n_rlimg == 0 &&
                       prm.n_bimg == 1 && prm.n_thr <= 3 && h->vc.reg[0].data == P.pb &&
                       h->vc.edge[0].data == P.pb && h->vc.reg[0].bins <= 16 && h->vc.edge[0].bins <= 16 &&
-                      (long long)P.X * P.Y * 4 < (1ll << 31) &&  // tile-relative voxel offsets are 32-bit
+                      P.Y <= 8 * 65535 &&  // grid y extent
                       build_value_classes(h->vc.reg[0], h->vc.edge[0], P.nThr, P.thr_up, vcls);
     h->usedFast = fast;
     if (fast) {
@@ -421,24 +428,15 @@ extern "C" int glia_b200_score_candidates(glia_handle* h, const glia_rf* rf, dou
   double* dSal = sal;
   if (!h->prm.device_pointers) { CK(h->sal.ensure(8 * C)); dSal = h->sal.as<double>(); }
   CK(cudaEventRecord(h->ev[3], h->stream));
-  // fused: rows are featurised into the shared-memory tile of the forest walk (score_fused.cu); ms[2] then holds the
-  // per-region block stage only and ms[3] the fused kernel
-  int s = h->noFuse ? GLIA_E_STATE : glia_score_fused_device(h, rf, li, dSal);
-  if (s == GLIA_OK) {
-    CK(cudaEventRecord(h->ev[4], h->stream));
-    CK(cudaEventRecord(h->ev[5], h->stream));
-    h->lastFused = true;
-  } else if (s == GLIA_E_STATE) {
-    h->lastFused = false;
-    CK(h->rows.ensure(8 * C * dim));
-    s = glia_featurize_init_device(h, nullptr, h->rows.as<double>());
-    if (s) return s;
-    CK(cudaEventRecord(h->ev[4], h->stream));
-    s = glia_rf_score_device(rf, h->rows.as<double>(), C, (int)dim, li, nullptr, dSal, h->stream);
-    h->launches++;
-    if (s) { h->err = "rf kernel launch failed"; return s; }
-    CK(cudaEventRecord(h->ev[5], h->stream));
-  } else return s;
+  int s;
+  CK(h->rows.ensure(8 * C * dim));
+  s = glia_featurize_init_device(h, nullptr, h->rows.as<double>());
+  if (s) return s;
+  CK(cudaEventRecord(h->ev[4], h->stream));
+  s = glia_rf_score_device(rf, h->rows.as<double>(), C, (int)dim, li, nullptr, dSal, h->stream);
+  h->launches++;
+  if (s) { h->err = "rf kernel launch failed"; return s; }
+  CK(cudaEventRecord(h->ev[5], h->stream));
   if (!h->prm.device_pointers) CK(cudaMemcpyAsync(sal, dSal, 8 * C, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   float ms = 0;

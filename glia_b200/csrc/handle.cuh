@@ -89,7 +89,6 @@ struct glia_handle {
   bool usedFast = false;
   bool forceGeneric = false;      // glia_b200_tune(h, "generic", 1): test hook, run the generic voxel kernel
   bool fastDomainFailed = false;  // a value outside [0, 1] was met: the fast voxel kernel is skipped from then on
-  bool noFuse = false, lastFused = false;  // glia_b200_tune(h, "nofuse", 1): score through materialised rows
   int tuneTZ = 0, tuneSlots = 0;  // tile depth / table slots of the fast voxel kernel (0 = default)
   long long tableOccupied = 0;  // occupied slots of the boundary table at the last export (shard.cu)
   uint64_t capHint = 0;  // boundary-table capacity that turned out to be needed (grown tables are kept)

@@ -137,8 +137,10 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
 }
 
 
+// One walk per thread: measured on B200 (profiles/r2_rf_notes.txt) more resident warps beat more walks in flight
+// per thread (28 registers -> 4 CTAs of 512 threads = 64 warps per SM).
 template <bool ENS, int NS>  // NS tree slices per candidate (CTA = 64 * NS threads)
-__global__ void __launch_bounds__(64 * NS, NS == 8 ? 2 : 4)
+__global__ void __launch_bounds__(64 * NS, NS == 8 ? 4 : 8)
 rf_score_blk_kernel(const RfBlock* __restrict__ blocks, const int* __restrict__ treeRoot, const RfDist dist,
                     int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
                     double* __restrict__ prob) {
@@ -161,16 +163,9 @@ rf_score_blk_kernel(const RfBlock* __restrict__ blocks, const int* __restrict__ 
     const int tbeg = ENS ? dist.begin(mdl) : 0, ntree = ENS ? dist.end(mdl) : dist.te[0];
     if (slice == 0) sntree[cand] = ntree - tbeg;
     const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
-    const RfBlock* bp = blocks;
-    int hits = 0, t = tbeg + slice;
-    for (; t + NS < ntree; t += 2 * NS) {  // two walks in flight
-      BlkRegs a = rf_block(bp, (uint32_t)__ldg(treeRoot + t)), b = rf_block(bp, (uint32_t)__ldg(treeRoot + t + NS));
-      while (!(a.base & b.base & RFB_DONE)) { RFB_STEP(a, hits) RFB_STEP(b, hits) }
-    }
-    for (; t < ntree; t += NS) {
-      BlkRegs a = rf_block(bp, (uint32_t)__ldg(treeRoot + t));
-      while (!(a.base & RFB_DONE)) { RFB_STEP(a, hits) }
-    }
+    int hits = 0;
+    for (int t = tbeg + slice; t < ntree; t += NS)
+      hits += (int)rf_walk_blocks(blocks, (uint32_t)__ldg(treeRoot + t), xs, (uint32_t)labelIdx);
     atomicAdd(&svote[cand], hits);
   }
   __syncthreads();
@@ -238,10 +233,11 @@ static int rf_build_device(glia_rf* m) {
     if (cudaMalloc(&m->d_nodesW, sizeof(RfNode) * w.size()) != cudaSuccess) return GLIA_E_CUDA;
     if (cudaMemcpy(m->d_nodesW, w.data(), sizeof(RfNode) * w.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
   }
-  // two-level blocks (rf_score_blk_kernel): two classes, features < 256, block ids < 2^31
+  // two-level blocks (rf_score_blk_kernel): two classes, features < 256, block ids < 2^24
   if (m->nclass == 2 && m->mdim <= 255) {
     std::vector<RfBlock> blk;
     std::vector<int> root(m->ntree);
+    bool tooBig = false;
     for (int t = 0; t < m->ntree; ++t) {
       std::queue<std::pair<int, uint32_t>> q;  // (node index in `nodes`, block index)
       root[t] = (int)blk.size();
@@ -270,14 +266,19 @@ static int rf_build_device(glia_rf* m) {
             }
           }
         }
-        B.meta |= leaf << 24 | cls << 28;
-        B.base = (uint32_t)blk.size();
-        for (int o = 0; o < 4; ++o)
-          if (next[o] >= 0) { q.push({next[o], (uint32_t)blk.size()}); blk.push_back(RfBlock{0.0, 0.0, 0.0, 0u, 0u}); }
+        // the four child blocks sit at base + outcome; slots of leaf outcomes beyond the last continuing one are not allocated
+        int last = -1;
+        for (int o = 0; o < 4; ++o) if (next[o] >= 0) last = o;
+        if (blk.size() + 4 >= (1u << 24)) { tooBig = true; break; }
+        B.base = (uint32_t)blk.size() | leaf << 24 | cls << 28;
+        for (int o = 0; o <= last; ++o) {
+          if (next[o] >= 0) q.push({next[o], (uint32_t)blk.size()});
+          blk.push_back(RfBlock{0.0, 0.0, 0.0, 0u, 0u});
+        }
         blk[cur.second] = B;
       }
     }
-    if (blk.size() < 0x7FFFFFFFull) {
+    if (!tooBig) {
       if (cudaMalloc(&m->d_blocks, sizeof(RfBlock) * blk.size()) != cudaSuccess) return GLIA_E_CUDA;
       if (cudaMalloc((void**)&m->d_blockRoot, 4 * root.size()) != cudaSuccess) return GLIA_E_CUDA;
       if (cudaMemcpy(m->d_blocks, blk.data(), sizeof(RfBlock) * blk.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;

@@ -100,18 +100,30 @@ __device__ __forceinline__ uint32_t key_hash(uint32_t a, uint32_t b) {
   return ((a * 0x9E3779B1u) ^ (b * 0x85EBCA77u)) >> 10;
 }
 
-// find-or-insert in the CTA's table (used by the flush; the march has its own warp-convergent probe loop);
-// -1 when 8 probes found neither the key nor a free slot.  *inserted is set when this call claimed the slot.
-__device__ __forceinline__ int slot_of(unsigned long long* keys, uint32_t mask, uint32_t a, uint32_t b, bool* inserted) {
+// The CTA's table is probed in BUCKETS of two adjacent keys (one 16-byte load): bucket hash, hash + 1, ... (4 at most).
+// A key goes into the first empty slot of the first bucket that has one; slots never become empty again, so two
+// inserters of one key always meet in the same slot.
+// find-or-insert (used by the flush; the march has its own warp-convergent copy of this loop); -1 = no room.
+// *inserted is set when this call claimed the slot.
+__device__ __forceinline__ int slot_of(unsigned long long* keys, uint32_t bmask, uint32_t a, uint32_t b, bool* inserted) {
   const unsigned long long key = ((unsigned long long)a << 32) | b;
-  uint32_t h = key_hash(a, b) & mask;
+  uint32_t h = key_hash(a, b) & bmask;
+  int adv = 0;
   *inserted = false;
 #pragma unroll 1
   for (int probe = 0; probe < 8; ++probe) {
-    unsigned long long cur = keys[h];
-    if (cur == KEY_EMPTY) { cur = atomicCAS(keys + h, KEY_EMPTY, key); if (cur == KEY_EMPTY) { *inserted = true; return (int)h; } }
-    if (cur == key) return (int)h;
-    h = (h + 1) & mask;
+    const ulonglong2 kk = *reinterpret_cast<const ulonglong2*>(keys + 2 * h);
+    if (kk.x == key) return (int)(2 * h);
+    if (kk.y == key) return (int)(2 * h + 1);
+    if (kk.x == KEY_EMPTY || kk.y == KEY_EMPTY) {
+      const int j = kk.x == KEY_EMPTY ? 0 : 1;
+      const unsigned long long cur = atomicCAS(keys + 2 * h + j, KEY_EMPTY, key);
+      if (cur == KEY_EMPTY) { *inserted = true; return (int)(2 * h + j); }
+      if (cur == key) return (int)(2 * h + j);
+      continue;  // another key took the slot: look at this bucket again
+    }
+    h = (h + 1) & bmask;
+    if (++adv >= 4) return -1;  // four full buckets
   }
   return -1;
 }
@@ -250,9 +262,7 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
   }
   __syncthreads();
 
-  int t = blockIdx.x;
-  const int tileX = t % P.tilesX; t /= P.tilesX;
-  const int tileY = t % P.tilesY; t /= P.tilesY;
+  const int tileX = blockIdx.x, tileY = blockIdx.y, t = blockIdx.z;
   const int wx = warp % WX, wy = warp / WX;
   const int x0warp = (tileX * WX + wx) * 32;
   const int gx = x0warp + lane;
@@ -265,7 +275,7 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
   const bool vym = THREED && gy > 0, vyp = THREED && gy < P.Y - 1;  // warp-uniform
   const int nvalidXY = (int)vxm + (int)vxp + (int)vym + (int)vyp;
   constexpr int twoD = THREED ? 6 : 4;
-  constexpr uint32_t smask = (uint32_t)(NS - 1);
+  constexpr uint32_t bmask = (uint32_t)(NS / 2 - 1);  // buckets of two keys
   const int nB = P.vc.nCls - 1;
   const float lutLo = P.vc.lutLo, lutScale = P.vc.lutScale;
   uint32_t* const Tx = T + (W_X + wx) * LD;
@@ -333,23 +343,27 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
       int q = (int)((pv - lutLo) * lutScale) - 1;
       q = max(0, min(q, 255));
       int cls = sLut[q];
+      cls += (cls < nB && pv >= sBound[cls]) ? 1 : 0;  // at most two steps: build_value_classes checks the table
       cls += (cls < nB && pv >= sBound[cls]) ? 1 : 0;
-      cls += (cls < nB && pv >= sBound[cls]) ? 1 : 0;
-      while (__any_sync(0xffffffffu, cls < nB && pv >= sBound[cls])) cls += (cls < nB && pv >= sBound[cls]) ? 1 : 0;
       uint32_t lo, hi, lo2, hi2;
       fixed48(pv, lo, hi, lo2, hi2);
       const uint32_t kord = __float_as_uint(pv) | 0x80000000u;  // f2ord of a non-negative float
       // ---- slot of the key: warp-convergent linear probing
       const unsigned long long key = ((unsigned long long)me << 32) | nb;
-      uint32_t h = key_hash(me, nb) & smask;
-      int s = -1;
+      uint32_t h = key_hash(me, nb) & bmask;
+      int s = -1, adv = 0;
 #pragma unroll 1
       for (int probe = 0; probe < 8; ++probe) {
         if (need) {
-          unsigned long long cur = keys[h];
-          if (cur == KEY_EMPTY) cur = atomicCAS(keys + h, KEY_EMPTY, key);
-          if (cur == key || cur == KEY_EMPTY) { s = (int)h; need = false; }
-          else h = (h + 1) & smask;
+          const ulonglong2 kk = *reinterpret_cast<const ulonglong2*>(keys + 2 * h);
+          if (kk.x == key) s = (int)(2 * h);
+          else if (kk.y == key) s = (int)(2 * h + 1);
+          else if (kk.x == KEY_EMPTY || kk.y == KEY_EMPTY) {
+            const int j = kk.x == KEY_EMPTY ? 0 : 1;
+            const unsigned long long cur = atomicCAS(keys + 2 * h + j, KEY_EMPTY, key);
+            if (cur == KEY_EMPTY || cur == key) s = (int)(2 * h + j);  // else another key took it: same bucket again
+          } else { h = (h + 1) & bmask; if (++adv >= 4) need = false; }  // four full buckets: no room (global fallback)
+          if (s >= 0) need = false;
         }
         if (!__any_sync(0xffffffffu, need)) break;
       }
@@ -402,7 +416,7 @@ voxel_pass_fast(const __grid_constant__ FastParams P) {
     const unsigned long long key = keys[s];
     const uint32_t a = (uint32_t)(key >> 32);
     bool ins;
-    const int r = slot_of(keys, smask, a, a, &ins);
+    const int r = slot_of(keys, bmask, a, a, &ins);
     if (ins) listR[atomicAdd(listN + 1, 1u)] = (unsigned short)r;
     T[W_FOLD * LD + s] = (uint32_t)r;
     const long long g = edge_slot_global_fast(P, key);
@@ -443,7 +457,8 @@ static cudaError_t launch_fast(const FastParams& P, cudaStream_t st) {
   if (e != cudaSuccess) return e;
   const long long tiles = (long long)P.tilesX * P.tilesY * P.tilesZ;
   if (tiles <= 0) return cudaSuccess;
-  voxel_pass_fast<THREED, NS><<<(unsigned)tiles, 256, smem, st>>>(P);
+  if (P.tilesY > 65535 || P.tilesZ > 65535) return cudaErrorInvalidConfiguration;
+  voxel_pass_fast<THREED, NS><<<dim3((unsigned)P.tilesX, (unsigned)P.tilesY, (unsigned)P.tilesZ), 256, smem, st>>>(P);
   return cudaGetLastError();
 }
 

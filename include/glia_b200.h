@@ -95,8 +95,7 @@ GLIA_API int glia_b200_set_image(glia_handle* h, int kind, int i, const float* d
 
 /* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
  * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
- * kernel, "slots": its shared-memory table slots (0 = default); "nofuse": value != 0 makes score_candidates go
- * through materialised rows (featurise kernel + RF kernel) instead of the fused kernel. */
+ * kernel, "slots": its shared-memory table slots (0 = default). */
 GLIA_API int glia_b200_tune(glia_handle* h, const char* key, int value);
 
 /* RAG + base statistics.  labels/mask: uint32 volumes (mask may be NULL); pb: float32. */
