@@ -113,8 +113,8 @@ def run_slab(args, rank, world, local_rank, dist):
     # ---- e2e: this rank's slab from pinned host memory through the same path
     e2e = None
     if not args.no_e2e and 8 * nloc <= 5 * 2 ** 30:
-        hl_t = torch.empty(nloc, dtype=torch.int32).pin_memory(); hl_t.copy_(lab)
-        hp_t = torch.empty(nloc, dtype=torch.float32).pin_memory(); hp_t.copy_(pb)
+        hl_t = torch.empty(nloc, dtype=torch.int32, pin_memory=True); hl_t.copy_(lab)
+        hp_t = torch.empty(nloc, dtype=torch.float32, pin_memory=True); hp_t.copy_(pb)
         hln = hl_t.numpy().view(np.uint32).reshape(nplanes, ny, nx)
         hpn = hp_t.numpy().reshape(nplanes, ny, nx)
         hspec = [(hpn, 16, 0.0, 1.0)]
@@ -134,6 +134,16 @@ def run_slab(args, rank, world, local_rank, dist):
         e2e = {"value": nvox * n_e2e / dt / 1e6, "unit": "Mvoxels/s", "h2d_bytes_per_step": 8 * nloc * world,
                "d2h_bytes_per_step": int(8 * cands), "steps": n_e2e, "ms_per_step": 1e3 * dt / n_e2e}
         hb.close()
+        # the ceiling of this leg: every rank copies the same pinned slab to its GPU, no kernel at all
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(n_e2e):
+            lab.copy_(hl_t, non_blocking=True); pb.copy_(hp_t, non_blocking=True)
+        torch.cuda.synchronize()
+        dth = _max_over_ranks(torch, dist, world, dev, time.perf_counter() - t0)
+        e2e["h2d_only_ms_per_step"] = 1e3 * dth / n_e2e
+        e2e["h2d_only_gb_s_per_gpu"] = 8 * nloc * n_e2e / dth / 1e9
+        e2e["frac_of_h2d_ceiling"] = dth / dt
     if rank == 0:
         peak, peak_src = B.load_peaks()
         alg = 8.0 * (z1 - z0) * ny * nx  # this rank's launch: owned voxels x (u32 label + f32 pb)

@@ -6,8 +6,6 @@
 #include "handle.cuh"
 
 namespace glia {
-size_t voxel_pass_smem_bytes(const VoxParams& P);
-cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
 int glia_finalize_graph(glia_handle* h);
@@ -83,8 +81,10 @@ extern "C" int glia_b200_create(const glia_params* p, glia_handle** out) {
   P.ndim = p->ndim; P.X = h->KX; P.Y = h->KY; P.Z = h->KZ;
   P.zBegin = zb; P.zEnd = ze; P.zBuf0 = zb - hl; P.zBufN = (ze + hh) - (zb - hl);
   h->nvoxBuf = (size_t)P.X * P.Y * P.zBufN;
-  if (p->ndim == 2) { P.TX = std::min(256, ((P.X + 31) / 32) * 32); P.TY = 1; P.TZ = 16; }
+  // 2D rows of 128 + 2 halo voxels stay inside the 256-element box limit of a TMA tensor copy (voxel_pass.cu)
+  if (p->ndim == 2) { P.TX = std::min(128, ((P.X + 31) / 32) * 32); P.TY = 1; P.TZ = 16; }
   else { P.TX = 32; P.TY = 8; P.TZ = 16; }
+  P.SXp = ((P.TX + 2 + 3) / 4) * 4;
   P.tilesX = (P.X + P.TX - 1) / P.TX; P.tilesY = (P.Y + P.TY - 1) / P.TY;
   P.tilesZ = (ze - zb + P.TZ - 1) / P.TZ;
   P.nThr = p->n_thr;
@@ -166,6 +166,8 @@ extern "C" int glia_b200_set_image(glia_handle* h, int kind, int i, const float*
 extern "C" int glia_b200_tune(glia_handle* h, const char* key, int value) {
   if (!h || !key) return GLIA_E_ARG;
   if (!strcmp(key, "generic")) h->forceGeneric = value != 0;
+  else if (!strcmp(key, "notma")) h->noTma = value != 0;
+  else if (!strcmp(key, "used_tma")) return h->usedTma ? GLIA_OK : GLIA_E_STATE;  // query: did the last generic pass stage by TMA
   else if (!strcmp(key, "tz")) { if (value < 0 || value > 31) return GLIA_E_ARG; h->tuneTZ = value; }
   else if (!strcmp(key, "slots")) { if (value < 0 || value > 2048) return GLIA_E_ARG; h->tuneSlots = value; }
   else return GLIA_E_ARG;

@@ -4,12 +4,13 @@
 #include <algorithm>
 #include <vector>
 #include <stdlib.h>
+#include <cuda.h>
 #include "handle.cuh"
 #include "voxel_fast.cuh"
 
 namespace glia {
 cudaError_t launch_voxel_pass_fast(const FastParams& P, cudaStream_t st);
-cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st);
+cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, const CUtensorMap* tm, cudaStream_t st);
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
 int glia_finalize_graph(glia_handle* h);
@@ -83,6 +84,34 @@ static bool build_value_classes(const Channel& rc, const Channel& ec, int nThr, 
     if (n - (int)V.lut[c > 0 ? c - 1 : 0] > 2) return false;
   }
   return true;
+}
+
+
+// ---- TMA tensor maps of the generic voxel kernel (voxel_pass.cu): the label / mask volume as a rank-3 u32 tensor,
+// box = tile + halo.  The encoder is a driver entry point fetched at run time (no libcuda link dependency).
+// Returns false when the volume does not meet the copy engine's rules (16-byte aligned base and strides, box <= 256).
+static bool make_tile_map(CUtensorMap* out, const void* base, const VoxParams& P) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  static bool looked = false;
+  if (!looked) {
+    looked = true;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      encode = (EncodeFn)fn;
+  }
+  const int hy = P.ndim == 2 ? 0 : 1;
+  if (!encode || !base || ((uintptr_t)base & 15) || (P.X & 3) || P.SXp > 256 || P.TZ + 2 > 256) return false;
+  cuuint64_t dims[3] = {(cuuint64_t)P.X, (cuuint64_t)P.Y, (cuuint64_t)P.zBufN};
+  cuuint64_t strides[2] = {4ull * P.X, 4ull * P.X * P.Y};
+  cuuint32_t box[3] = {(cuuint32_t)P.SXp, (cuuint32_t)(P.TY + 2 * hy), (cuuint32_t)(P.TZ + 2)};
+  cuuint32_t estr[3] = {1, 1, 1};
+  return encode(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void*>(base), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 // inputs -> device, table initialisation, voxel pass (raw tables).  Leaves the stream running.
@@ -214,7 +243,7 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       // CTA = 8 warps: 256 x 1 voxels per row step in 2D, 32 x 8 in 3D, marching TZ rows / planes.
       // 512 table slots keep a CTA at ~51 KB (3D) / ~66 KB (2D) of shared memory: 4 / 3 CTAs per SM.
       if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
-      F.TZ = h->tuneTZ > 0 ? h->tuneTZ : 16;
+      F.TZ = h->tuneTZ > 0 ? h->tuneTZ : (P.ndim == 3 ? 24 : 16);  // measured: profiles/r2_voxel_notes.txt
       if (F.TZ + F.warpsY > 32) F.TZ = 32 - F.warpsY;  // y and z occupancy masks share one word
       while (F.TZ > 1 && (long long)P.X * P.Y * (F.TZ + 3) >= (1ll << 31)) F.TZ >>= 1;
       F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);
@@ -235,12 +264,17 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
         CK(launch_voxel_pass_fast(F, st));
       }
     } else {
+      // label (and mask) tiles are staged by TMA when the volume meets the copy engine's alignment rules
+      CUtensorMap tm[2];
+      memset(tm, 0, sizeof(tm));
+      const bool tma = !h->noTma && make_tile_map(&tm[0], P.labels, P) && (!P.mask || make_tile_map(&tm[1], P.mask, P));
+      h->usedTma = tma;
       for (int k = 0; k < nChunks; ++k) {
         if (nChunks > 1) CK(cudaStreamWaitEvent(st, h->evCopy[k + 1 < nChunks ? k + 1 : k], 0));
         VoxParams Pk = P;
         Pk.zBegin = zCut[k]; Pk.zEnd = zCut[k + 1];
         Pk.tilesZ = (Pk.zEnd - Pk.zBegin + Pk.TZ - 1) / Pk.TZ;
-        CK(launch_voxel_pass_generic(Pk, h->vc, st));
+        CK(launch_voxel_pass_generic(Pk, h->vc, tma ? tm : nullptr, st));
       }
     }
   }

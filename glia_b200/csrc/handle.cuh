@@ -67,7 +67,8 @@ struct glia_rf {
   int* d_treeOff = nullptr;      // [ntree+1]
   void* d_nodes = nullptr;       // packed nodes
   void* d_nodesW = nullptr;      // walk encoding for rf_score_smem_kernel: leaves are self-loops (rf.cu)
-  void* d_blocks = nullptr;      // two-level 32-byte blocks (rf.cu v5, two-class forests)
+  void* d_blocks = nullptr;      // two-level 16-byte blocks (rf_walk.cuh, two-class forests)
+  double* d_blockThr = nullptr;  // exact thresholds [3 * block + j] for the rare undecided compare
   int* d_blockRoot = nullptr;    // [ntree] root block of every tree
   long long nBlocks = 0;
   int maxDepth = 0;
@@ -87,6 +88,7 @@ struct glia_handle {
   bool built = false;
   bool partial = false;  // raw tables valid (glia_b200_build_partial / glia_b200_build)
   bool usedFast = false;
+  bool noTma = false, usedTma = false;  // generic voxel kernel: tile staged by plain loads instead of TMA ("notma")
   bool forceGeneric = false;      // glia_b200_tune(h, "generic", 1): test hook, run the generic voxel kernel
   bool fastDomainFailed = false;  // a value outside [0, 1] was met: the fast voxel kernel is skipped from then on
   int tuneTZ = 0, tuneSlots = 0;  // tile depth / table slots of the fast voxel kernel (0 = default)

@@ -11,6 +11,7 @@ int main(int argc, char** argv) {
     std::cerr << "Usage: merge_order_bc --bct 1 --bcm MODEL -s SEG --pb PB [--rbi IMG --rbb BINS --rbl LO --rbu HI]...\n"
                  "       [--rli/--rlb/--rll/--rlu] [--ri/--rb/--rl/--ru] [--bi/--bb/--bl/--bu] [--bt T...] [-m MASK]\n"
                  "       [--bcm M1 --bcm M2 --bcmd DIM0 DIM1 THR] [-n 0|1] [-l 0|1] [--simpf 0|1] -o ORDER [--sal SAL] [-b BCFEAT] [--device N]\n"
+                 "       [--ref-order N]  equal-area pairs follow the unordered_map call order of the reference (N = its rmap.reserve, 0 = none)\n"
                  "Images: .npy, .mha, .mhd (raw).\n";
     return a.has("help") ? EXIT_SUCCESS : EXIT_FAILURE;
   }
@@ -43,6 +44,11 @@ int main(int argc, char** argv) {
   const bool wantRows = a.has("bfeat") && !a.str("bfeat").empty();
   std::vector<uint32_t> order(3 * (size_t)(R > 0 ? R : 1));
   std::vector<double> sal((size_t)(R > 0 ? R : 1)), rows(wantRows ? (size_t)R * dim : 0);
+  if (a.has("ref-order")) {  // include/glia_b200.h: equal-area candidates keep the reference binary's call order
+    std::vector<uint8_t> secondFirst((size_t)(C > 0 ? C : 1));
+    H.check(glia_b200_reference_orientation(H.h, (int64_t)atoll(a.str("ref-order").c_str()), secondFirst.data()), "glia_b200_reference_orientation");
+    H.check(glia_b200_set_tie_orientation(H.h, secondFirst.data()), "glia_b200_set_tie_orientation");
+  }
   int64_t nm = 0, nf = 0;
   H.check(glia_b200_merge_order_bc(H.h, rf, order.data(), sal.data(), wantRows ? rows.data() : nullptr, &nm, &nf),
           "glia_b200_merge_order_bc");

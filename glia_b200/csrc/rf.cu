@@ -17,6 +17,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <math.h>
 #include <queue>
 #include "handle.cuh"
 #include "rf_walk.cuh"
@@ -141,15 +142,15 @@ rf_score_smem_kernel(const RfNode* __restrict__ nodes, const int* __restrict__ t
 // per thread (28 registers -> 4 CTAs of 512 threads = 64 warps per SM).
 template <bool ENS, int NS>  // NS tree slices per candidate (CTA = 64 * NS threads)
 __global__ void __launch_bounds__(64 * NS, NS == 8 ? 4 : 8)
-rf_score_blk_kernel(const RfBlock* __restrict__ blocks, const int* __restrict__ treeRoot, const RfDist dist,
+rf_score_blk_kernel(const uint4* __restrict__ blocks, const double* __restrict__ thr, const int* __restrict__ treeRoot, const RfDist dist,
                     int labelIdx, const double* __restrict__ X, size_t N, int D, int ldRow,
                     double* __restrict__ prob) {
-  extern __shared__ __align__(16) double srow[];
+  extern __shared__ __align__(16) uint32_t frow[];  // the CTA's rows as 25-bit order keys, odd stride: one bank per lane for equal features
   const size_t c0 = (size_t)blockIdx.x * RF_CPB;
   const int ncand = (int)min((size_t)RF_CPB, N - c0);
   for (int i = threadIdx.x; i < ncand * D; i += blockDim.x) {
     int c = i / D, f = i - c * D;
-    srow[c * ldRow + f] = X[c0 * D + i];
+    frow[c * ldRow + f] = rf_xkey(X[c0 * D + i]);
   }
   __shared__ int svote[RF_CPB];
   __shared__ int sntree[RF_CPB];
@@ -158,14 +159,14 @@ rf_score_blk_kernel(const RfBlock* __restrict__ blocks, const int* __restrict__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cand = (warp & 1) * 32 + lane, slice = warp >> 1;
   if (cand < ncand) {
-    const double* x = srow + cand * ldRow;
-    const int mdl = ENS ? dist.pick(x) : 0;
+    const double* xg = X + (c0 + cand) * (size_t)D;
+    const int mdl = ENS ? dist.pick(xg) : 0;
     const int tbeg = ENS ? dist.begin(mdl) : 0, ntree = ENS ? dist.end(mdl) : dist.te[0];
     if (slice == 0) sntree[cand] = ntree - tbeg;
-    const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
+    const uint32_t xs = (uint32_t)__cvta_generic_to_shared(frow + cand * ldRow);
     int hits = 0;
     for (int t = tbeg + slice; t < ntree; t += NS)
-      hits += (int)rf_walk_blocks(blocks, (uint32_t)__ldg(treeRoot + t), xs, (uint32_t)labelIdx);
+      hits += (int)rf_walk_blocks(blocks, thr, (uint32_t)__ldg(treeRoot + t), xs, xg, (uint32_t)labelIdx);
     atomicAdd(&svote[cand], hits);
   }
   __syncthreads();
@@ -233,57 +234,70 @@ static int rf_build_device(glia_rf* m) {
     if (cudaMalloc(&m->d_nodesW, sizeof(RfNode) * w.size()) != cudaSuccess) return GLIA_E_CUDA;
     if (cudaMemcpy(m->d_nodesW, w.data(), sizeof(RfNode) * w.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
   }
-  // two-level blocks (rf_score_blk_kernel): two classes, features < 256, block ids < 2^24
-  if (m->nclass == 2 && m->mdim <= 255) {
-    std::vector<RfBlock> blk;
+  // two-level blocks (rf_score_blk_kernel, rf_walk.cuh): two classes, features < 128, block ids < 2^20
+  if (m->nclass == 2 && m->mdim <= 128) {
+    struct HB { double t[3]; int f[3]; uint32_t leaf, cls, base; };
+    std::vector<HB> blk;
     std::vector<int> root(m->ntree);
     bool tooBig = false;
-    for (int t = 0; t < m->ntree; ++t) {
+    for (int t = 0; t < m->ntree && !tooBig; ++t) {
       std::queue<std::pair<int, uint32_t>> q;  // (node index in `nodes`, block index)
       root[t] = (int)blk.size();
-      blk.push_back(RfBlock{0.0, 0.0, 0.0, 0u, 0u});
+      blk.push_back(HB());
       q.push({treeOff[t], (uint32_t)root[t]});
       while (!q.empty()) {
         auto cur = q.front(); q.pop();
         const RfNode& r = nodes[cur.first];
-        RfBlock B{0.0, 0.0, 0.0, 0u, 0u};
-        uint32_t leaf = 0, cls = 0;
+        HB B = HB();
         int next[4] = {-1, -1, -1, -1};
         if (r.feat < 0) {  // a tree that is a single leaf: every outcome ends here
-          leaf = 0xF; cls = r.left ? 0xFu : 0u;
+          B.leaf = 0xF; B.cls = r.left ? 0xFu : 0u;
         } else {
-          B.t0 = r.thr; B.meta = (uint32_t)r.feat;
+          B.t[0] = r.thr; B.f[0] = r.feat;
           for (int c = 0; c < 2; ++c) {
             const RfNode& ch = nodes[r.left + c];
-            if (ch.feat < 0) { leaf |= 3u << (2 * c); if (ch.left) cls |= 3u << (2 * c); continue; }
-            (c ? B.t2 : B.t1) = ch.thr;
-            B.meta |= (uint32_t)ch.feat << (8 + 8 * c);
+            if (ch.feat < 0) { B.leaf |= 3u << (2 * c); if (ch.left) B.cls |= 3u << (2 * c); continue; }
+            B.t[1 + c] = ch.thr; B.f[1 + c] = ch.feat;
             for (int g = 0; g < 2; ++g) {
               const RfNode& gc = nodes[ch.left + g];
               const int o = 2 * c + g;
-              if (gc.feat < 0) { leaf |= 1u << o; if (gc.left) cls |= 1u << o; }
+              if (gc.feat < 0) { B.leaf |= 1u << o; if (gc.left) B.cls |= 1u << o; }
               else next[o] = ch.left + g;
             }
           }
         }
-        // the four child blocks sit at base + outcome; slots of leaf outcomes beyond the last continuing one are not allocated
+        // the four child blocks sit at base + outcome; slots beyond the last continuing outcome are not allocated
         int last = -1;
         for (int o = 0; o < 4; ++o) if (next[o] >= 0) last = o;
-        if (blk.size() + 4 >= (1u << 24)) { tooBig = true; break; }
-        B.base = (uint32_t)blk.size() | leaf << 24 | cls << 28;
+        if (blk.size() + 4 >= (1u << 20)) { tooBig = true; break; }
+        B.base = (uint32_t)blk.size();
         for (int o = 0; o <= last; ++o) {
           if (next[o] >= 0) q.push({next[o], (uint32_t)blk.size()});
-          blk.push_back(RfBlock{0.0, 0.0, 0.0, 0u, 0u});
+          blk.push_back(HB());
         }
         blk[cur.second] = B;
       }
     }
     if (!tooBig) {
-      if (cudaMalloc(&m->d_blocks, sizeof(RfBlock) * blk.size()) != cudaSuccess) return GLIA_E_CUDA;
+      std::vector<uint4> packed(blk.size());
+      std::vector<double> thr(3 * blk.size());
+      for (size_t i = 0; i < blk.size(); ++i) {
+        uint32_t w[3];
+        for (int j = 0; j < 3; ++j) {
+          float lo = (float)blk[i].t[j];  // floor_f32(t): largest float <= t
+          if ((double)lo > blk[i].t[j]) lo = nextafterf(lo, -INFINITY);
+          w[j] = (f2ord(lo) >> 7) | (uint32_t)blk[i].f[j] << RFB_KBITS;
+          thr[3 * i + j] = blk[i].t[j];
+        }
+        packed[i] = make_uint4(w[0], w[1], w[2], blk[i].base | blk[i].leaf << 24 | blk[i].cls << 28);
+      }
+      if (cudaMalloc(&m->d_blocks, sizeof(uint4) * packed.size()) != cudaSuccess) return GLIA_E_CUDA;
+      if (cudaMalloc((void**)&m->d_blockThr, 8 * thr.size()) != cudaSuccess) return GLIA_E_CUDA;
       if (cudaMalloc((void**)&m->d_blockRoot, 4 * root.size()) != cudaSuccess) return GLIA_E_CUDA;
-      if (cudaMemcpy(m->d_blocks, blk.data(), sizeof(RfBlock) * blk.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+      if (cudaMemcpy(m->d_blocks, packed.data(), sizeof(uint4) * packed.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
+      if (cudaMemcpy(m->d_blockThr, thr.data(), 8 * thr.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
       if (cudaMemcpy(m->d_blockRoot, root.data(), 4 * root.size(), cudaMemcpyHostToDevice) != cudaSuccess) return GLIA_E_CUDA;
-      m->nBlocks = (long long)blk.size();
+      m->nBlocks = (long long)packed.size();
     }
   }
   return GLIA_OK;
@@ -450,6 +464,7 @@ extern "C" void glia_b200_rf_destroy(glia_rf* m) {
   if (m->d_treeOff) cudaFree(m->d_treeOff);
   if (m->d_nodesW) cudaFree(m->d_nodesW);
   if (m->d_blocks) cudaFree(m->d_blocks);
+  if (m->d_blockThr) cudaFree(m->d_blockThr);
   if (m->d_blockRoot) cudaFree(m->d_blockRoot);
   delete m;
 }
@@ -487,10 +502,11 @@ int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, in
       // wide rows leave room for only a few CTAs of staged rows per SM: spread a candidate's trees over 8 warps
       // instead of 4 so that the SM still holds enough warps (profiles/r1_rf_v4_notes.txt)
       const bool wide = smem > 28 * 1024;
-      const RfBlock* bl = (const RfBlock*)m->d_blocks;
+      const size_t smemF = sizeof(float) * (size_t)RF_CPB * ldRow;  // float rows
+      const uint4* bl = (const uint4*)m->d_blocks;
 #define RF_LAUNCH(ENS_, NS_)                                                                                    \
       { cudaFuncSetAttribute(rf_score_blk_kernel<ENS_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
-        rf_score_blk_kernel<ENS_, NS_><<<nb, 64 * NS_, smem, st>>>(bl, m->d_blockRoot, m->dist, labelIdx, dX, N, D, ldRow, dProb); }
+        rf_score_blk_kernel<ENS_, NS_><<<nb, 64 * NS_, smemF, st>>>(bl, m->d_blockThr, m->d_blockRoot, m->dist, labelIdx, dX, N, D, ldRow, dProb); }
       if (m->dist.n > 1) { if (wide) RF_LAUNCH(true, 8) else RF_LAUNCH(true, 4) }
       else { if (wide) RF_LAUNCH(false, 8) else RF_LAUNCH(false, 4) }
 #undef RF_LAUNCH

@@ -12,38 +12,60 @@ __device__ __forceinline__ double rf_lds(uint32_t a) {
   return v;
 }
 
-// v5 (round 2): TWO tree levels per load.  A 32-byte block holds an internal node and its two children:
-//   {t0, t1, t2 : exact double thresholds of the node / left child / right child,
-//    meta       : f0 | f1 << 8 | f2 << 16 (features of the three nodes),
-//    base       : index of the first of the four child blocks | leaf mask << 24 | class bits << 28}
-// The four outcomes o = 2 * [x[f0] > t0] + [x[f(child)] > t(child)] either end in a leaf (bit o of the leaf
-// mask, its class = bit o of the class bits; a child that is itself a leaf sets both of its outcomes) or
-// continue in block (base & 0xFFFFFF) + o.  One LDG.E.256 per lane fetches a block, so a walk issues half as
-// many node loads and - with everything a step needs in one octet of registers - two thirds of the instructions of
-// the one-node-per-level walk.  Two classes only (the boundary classifier's {-1, +1}), at most 2^24 blocks and 256
-// features; other forests take rf_score_smem_kernel.
-struct __align__(32) RfBlock {
-  double t0, t1, t2;
-  uint32_t meta, base;
-};
+// v5 (round 2): TWO tree levels per 16-byte load, integer compares.
+//
+// A block holds an internal node and its two children.  Word j (j = 0 node, 1 left child, 2 right child) is
+//   K_j | f_j << 25      K_j = ord(floor_f32(threshold_j)) >> 7  (25 bits),  f_j = feature (7 bits)
+// and word 3 is  base | leaf mask << 24 | class bits << 28  (base = index of the first of the four child blocks).
+// ord() is the order-preserving map of float bit patterns to u32 (common.cuh); the CTA's rows are staged in shared
+// memory as kx = ord(RN_f32(x)) >> 7, so a split is decided by ONE integer subtraction:
+//   kx <  K      =>  RN(x) < floor_f32(t)  =>  x < t   (left)
+//   kx >  K + 1  =>  RN(x) > ceil_f32(t)   =>  x > t   (right)
+//   otherwise (x within 256 float ulps of t, ties included) the exact doubles decide: x from the row in global
+//   memory, t from a side array - votes stay bit-exact (classForest: x <= t goes left, NaN goes right).
+// The four outcomes o = 2 * right(node) + right(child) end in a leaf (bit o of the leaf mask, class = bit o of the
+// class bits; a child that is itself a leaf sets both of its outcomes) or continue in block base + o.
+// Why: the walk is bound by the SM's L1 data pipe - shared-memory wavefronts of the feature loads plus the
+// write-back of the node loads (96 % of peak with double rows and one 16-byte node per level; profiles/r2_rf_notes.txt).
+// This layout moves 8 bytes of node data and one conflict-free 4-byte feature per level, and needs no FP64.
+// Two classes, at most 128 features and 2^20 blocks; other forests take rf_score_smem_kernel.
+#define RFB_KBITS 25
+#define RFB_KMASK 0x1FFFFFFu
+
+__host__ __device__ inline uint32_t rf_xkey(double x) {  // kx of a feature value
+  const float xf = (float)x;
+  if (!(xf == xf)) return RFB_KMASK;  // NaN: right of every threshold
+  return f2ord(xf) >> 7;
+}
+
+// The rare undecided compare, kept out of line: if-converted into the walk its ~25 predicated instructions would
+// issue on every step (measured: 3.97 G instead of ~2 G warp instructions at c4s).
+__device__ __noinline__ bool rf_exact_right(const double* __restrict__ xg, const double* __restrict__ thr, uint32_t f, uint32_t ti) {
+  return !(__ldg(xg + f) <= __ldg(thr + ti));
+}
 
 // Walks one tree from block `k`; returns 1 when the leaf's class bit equals wantBit.  xs: shared-window address of
-// the candidate's row.  alg/rf.hxx:35-36 -> classForest: x <= threshold goes left, anything else (NaN too) right.
-__device__ __forceinline__ uint32_t rf_walk_blocks(const RfBlock* __restrict__ bp, uint32_t k, uint32_t xs, uint32_t wantBit) {
+// the candidate's row of keys, xg: the same row as exact doubles in global memory, thr: exact thresholds [3 * block + j].
+__device__ __forceinline__ uint32_t rf_walk_blocks(const uint4* __restrict__ bp, const double* __restrict__ thr, uint32_t k,
+                                                   uint32_t xs, const double* __restrict__ xg, uint32_t wantBit) {
   for (;;) {
-    uint32_t a0, a1, a2, a3, a4, a5, meta, base;
-    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3), "=r"(a4), "=r"(a5), "=r"(meta), "=r"(base)
-        : "l"(bp + k));
-    const double x0 = rf_lds(xs + 8u * (meta & 0xFFu));
-    const bool r0 = !(x0 <= __hiloint2double((int)a1, (int)a0));
-    const double tc = r0 ? __hiloint2double((int)a5, (int)a4) : __hiloint2double((int)a3, (int)a2);
-    const uint32_t fc = __byte_perm(meta, 0u, r0 ? 0x4442u : 0x4441u);
-    const double x1 = rf_lds(xs + 8u * fc);
-    const uint32_t o = (r0 ? 2u : 0u) + (!(x1 <= tc) ? 1u : 0u);
-    const uint32_t bits = base >> (24u + o);
+    const uint4 w = __ldg(bp + k);
+    const uint32_t f0 = w.x >> RFB_KBITS;
+    uint32_t kx;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(kx) : "r"(xs + 4u * f0));
+    int d = (int)(kx - (w.x & RFB_KMASK));
+    bool r0 = d > 1;
+    if ((uint32_t)d <= 1u) r0 = rf_exact_right(xg, thr, f0, 3u * k);
+    const uint32_t wc = r0 ? w.z : w.y;
+    const uint32_t fc = wc >> RFB_KBITS;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(kx) : "r"(xs + 4u * fc));
+    d = (int)(kx - (wc & RFB_KMASK));
+    bool r1 = d > 1;
+    if ((uint32_t)d <= 1u) r1 = rf_exact_right(xg, thr, fc, 3u * k + (r0 ? 2u : 1u));
+    const uint32_t o = (r0 ? 2u : 0u) + (r1 ? 1u : 0u);
+    const uint32_t bits = w.w >> (24u + o);
     if (bits & 1u) return ((bits >> 4) & 1u) == wantBit ? 1u : 0u;
-    k = (base & 0xFFFFFFu) + o;
+    k = (w.w & 0xFFFFFu) + o;
   }
 }
 

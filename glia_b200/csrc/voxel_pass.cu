@@ -16,9 +16,35 @@
 // staged in shared memory; statistics are privatised in shared-memory hash tables keyed by
 // label and by directed label pair and flushed once per tile with global atomics.  Keys that
 // do not fit the shared tables fall through to the global tables directly.
+#include <string.h>
+#include <cuda.h>  // CUtensorMap (type only: the encoder is fetched through cudaGetDriverEntryPoint, api_build.cu)
 #include "common.cuh"
 
 namespace glia {
+
+// ---- TMA + mbarrier (sm_100a): the label (and mask) tile with its one-voxel halo is ONE bulk tensor copy issued by
+// one thread; out-of-volume elements are zero-filled by the copy engine, completion is signalled on an mbarrier.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::
+          "r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!ok);
+}
 
 __device__ __forceinline__ int bin_of(const Channel& c, float v) {
   if (v > c.lo_dn && v < c.hi_up) {
@@ -72,14 +98,19 @@ __device__ __forceinline__ void flush_rec(const RecLayout& L, const uint32_t* sa
   for (int i = 0; i < L.nF64; ++i) { double v = sf[i]; if (v != 0.0) atomicAdd(gf + i, v); }
 }
 
+template <bool TMA>
 __global__ void __launch_bounds__(256)
-voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ VoxChannels C) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ VoxChannels C,
+                   const __grid_constant__ CUtensorMap tmLab, const __grid_constant__ CUtensorMap tmMask) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   const int hy = (P.ndim == 2) ? 0 : 1;
-  const int SX = P.TX + 2, SY = P.TY + 2 * hy, SZ = P.TZ + 2;
+  const int SX = P.SXp, SY = P.TY + 2 * hy, SZ = P.TZ + 2;  // SX = TX + 2 rounded up to whole 16-byte units (TMA box)
   const int ncell = SX * SY * SZ;
-  // carve shared memory (8-byte items first)
+  // carve shared memory: the TMA destinations first (128-byte aligned), then 8-byte items
   unsigned char* sp = smem_raw;
+  uint32_t* lab = (uint32_t*)sp; sp += ((4 * (size_t)ncell + 127) / 128) * 128;
+  uint32_t* msk = (uint32_t*)sp; if (TMA && P.mask) sp += ((4 * (size_t)ncell + 127) / 128) * 128;
+  __shared__ __align__(8) uint64_t mbar;
   unsigned long long* ekeys = (unsigned long long*)sp; sp += sizeof(unsigned long long) * P.edgeSlots;
   double* ef64 = (double*)sp; sp += sizeof(double) * (size_t)P.edgeSlots * P.edge.nF64;
   double* rf64 = (double*)sp; sp += sizeof(double) * (size_t)P.regSlots * P.reg.nF64;
@@ -88,7 +119,6 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
   uint32_t* radd = (uint32_t*)sp; sp += 4 * (size_t)P.regSlots * P.reg.nAdd;
   uint32_t* rmax = (uint32_t*)sp; sp += 4 * (size_t)P.regSlots * P.reg.nMax;
   uint32_t* rkeys = (uint32_t*)sp; sp += 4 * (size_t)P.regSlots;
-  uint32_t* lab = (uint32_t*)sp; sp += 4 * (size_t)ncell;
   unsigned char* valid = sp;
 
   const int nthreads = blockDim.x;
@@ -100,6 +130,16 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
   const int x0 = tileX * P.TX, y0 = tileY * P.TY, z0 = P.zBegin + tileZ * P.TZ;
   const size_t strideY = (size_t)P.X, strideZ = (size_t)P.X * P.Y;
 
+  if (TMA) {
+    if (tid == 0) mbar_init(&mbar, 1);
+    __syncthreads();
+    if (tid == 0) {  // one thread issues the bulk tensor copies; everybody else initialises the tables meanwhile
+      const uint32_t bytes = 4u * (uint32_t)ncell;
+      mbar_expect_tx(&mbar, P.mask ? 2u * bytes : bytes);
+      tma_load_3d(lab, &tmLab, &mbar, x0 - 1, y0 - hy, z0 - 1 - P.zBuf0);
+      if (P.mask) tma_load_3d(msk, &tmMask, &mbar, x0 - 1, y0 - hy, z0 - 1 - P.zBuf0);
+    }
+  }
   // ---- init shared tables
   for (int i = tid; i < P.edgeSlots; i += nthreads) ekeys[i] = EDGE_EMPTY;
   for (int i = tid; i < P.edgeSlots * P.edge.nF64; i += nthreads) ef64[i] = 0.0;
@@ -109,22 +149,36 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
   for (int i = tid; i < P.regSlots * P.reg.nAdd; i += nthreads) radd[i] = 0;
   for (int i = tid; i < P.regSlots * P.reg.nMax; i += nthreads) rmax[i] = 0;
   for (int i = tid; i < P.regSlots; i += nthreads) rkeys[i] = 0xFFFFFFFFu;
-  // ---- stage label + validity tile (halo 1)
-  for (int i = tid; i < ncell; i += nthreads) {
-    int cx = i % SX, r = i / SX;
-    int cy = r % SY, cz = r / SY;
-    int gx = x0 - 1 + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
-    int bz = gz - P.zBuf0;
-    bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 &&
-              bz < P.zBufN;
-    uint32_t l = 0;
-    if (ok) {
-      size_t q = (size_t)bz * strideZ + (size_t)gy * strideY + gx;
-      if (P.mask && __ldg(P.mask + q) == 0) ok = false;
-      else l = __ldg(P.labels + q);
+  if (TMA) {
+    mbar_wait(&mbar, 0);
+    // validity: inside the volume, inside the buffer (slab + halo), unmasked.  Labels outside were zero-filled.
+    for (int i = tid; i < ncell; i += nthreads) {
+      int cx = i % SX, r = i / SX;
+      int cy = r % SY, cz = r / SY;
+      int gx = x0 - 1 + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
+      int bz = gz - P.zBuf0;
+      bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 && bz < P.zBufN;
+      if (ok && P.mask && msk[i] == 0) ok = false;
+      valid[i] = ok ? 1 : 0;
     }
-    lab[i] = l;
-    valid[i] = ok ? 1 : 0;
+  } else {
+    // ---- stage label + validity tile (halo 1)
+    for (int i = tid; i < ncell; i += nthreads) {
+      int cx = i % SX, r = i / SX;
+      int cy = r % SY, cz = r / SY;
+      int gx = x0 - 1 + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
+      int bz = gz - P.zBuf0;
+      bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 &&
+                bz < P.zBufN;
+      uint32_t l = 0;
+      if (ok) {
+        size_t q = (size_t)bz * strideZ + (size_t)gy * strideY + gx;
+        if (P.mask && __ldg(P.mask + q) == 0) ok = false;
+        else l = __ldg(P.labels + q);
+      }
+      lab[i] = l;
+      valid[i] = ok ? 1 : 0;
+    }
   }
   __syncthreads();
 
@@ -246,23 +300,27 @@ __global__ void label_max_kernel(const uint32_t* __restrict__ labels, size_t n, 
   if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 
-size_t voxel_pass_smem_bytes(const VoxParams& P) {
+size_t voxel_pass_smem_bytes(const VoxParams& P, bool tmaMask) {
   const int hy = (P.ndim == 2) ? 0 : 1;
-  size_t ncell = (size_t)(P.TX + 2) * (P.TY + 2 * hy) * (P.TZ + 2);
-  size_t b = 8 * (size_t)P.edgeSlots + 8 * (size_t)P.edgeSlots * P.edge.nF64 +
+  size_t ncell = (size_t)P.SXp * (P.TY + 2 * hy) * (P.TZ + 2);
+  size_t tile = ((4 * ncell + 127) / 128) * 128;
+  size_t b = tile * (tmaMask ? 2 : 1) + 8 * (size_t)P.edgeSlots + 8 * (size_t)P.edgeSlots * P.edge.nF64 +
              8 * (size_t)P.regSlots * P.reg.nF64 + 4 * (size_t)P.edgeSlots * (P.edge.nAdd + P.edge.nMax) +
-             4 * (size_t)P.regSlots * (P.reg.nAdd + P.reg.nMax + 1) + 4 * ncell + ncell;
+             4 * (size_t)P.regSlots * (P.reg.nAdd + P.reg.nMax + 1) + ncell;
   return (b + 15) & ~(size_t)15;
 }
 
-cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, cudaStream_t st) {
-  size_t smem = voxel_pass_smem_bytes(P);
-  cudaError_t e = cudaFuncSetAttribute(voxel_pass_generic,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+// tm: label / mask tensor maps (api_build.cu) or null -> the tile is staged with plain loads
+cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, const CUtensorMap* tm, cudaStream_t st) {
+  const bool tma = tm != nullptr;
+  size_t smem = voxel_pass_smem_bytes(P, tma && P.mask);
+  cudaError_t e = tma ? cudaFuncSetAttribute(voxel_pass_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                      : cudaFuncSetAttribute(voxel_pass_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   long long tiles = (long long)P.tilesX * P.tilesY * P.tilesZ;
   if (tiles <= 0) return cudaSuccess;
-  voxel_pass_generic<<<(unsigned)tiles, P.TX * P.TY, smem, st>>>(P, C);
+  if (tma) voxel_pass_generic<true><<<(unsigned)tiles, P.TX * P.TY, smem, st>>>(P, C, tm[0], tm[1]);
+  else { CUtensorMap dummy; memset(&dummy, 0, sizeof(dummy)); voxel_pass_generic<false><<<(unsigned)tiles, P.TX * P.TY, smem, st>>>(P, C, dummy, dummy); }
   return cudaGetLastError();
 }
 

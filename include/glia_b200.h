@@ -95,7 +95,9 @@ GLIA_API int glia_b200_set_image(glia_handle* h, int kind, int i, const float* d
 
 /* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
  * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
- * kernel, "slots": its shared-memory table slots (0 = default). */
+ * kernel, "slots": its shared-memory table slots (0 = default); "notma": value != 0 makes the generic voxel kernel
+ * stage its label tile with plain loads instead of a TMA tensor copy; "used_tma" (query, value ignored): GLIA_OK when
+ * the last generic pass staged by TMA, GLIA_E_STATE otherwise. */
 GLIA_API int glia_b200_tune(glia_handle* h, const char* key, int value);
 
 /* RAG + base statistics.  labels/mask: uint32 volumes (mask may be NULL); pb: float32. */

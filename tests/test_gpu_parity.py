@@ -319,6 +319,29 @@ def test_generic_and_fast_voxel_kernels_agree():
         _compare_graph(o, g, co)
 
 
+@pytest.mark.parametrize("shape,masked", [((24, 40, 64), True), ((24, 40, 64), False), ((70, 96), True), ((20, 30, 50), True)])
+def test_generic_kernel_tma_staging_equals_plain_loads(shape, masked):
+    """voxel_pass_generic stages its label (+ mask) tile with one TMA tensor copy per tile when the row length is a
+    multiple of 4 voxels (16-byte strides); otherwise, or with tune("notma"), with plain loads.  Same records either way,
+    and equal to the oracle."""
+    lab, pb = synth.voronoi_volume(shape, 7, seed=31)
+    mask = (np.random.default_rng(5).random(shape) > 0.05).astype(np.uint32) if masked else None
+    co, cg = _cfg_pair(pb)
+    o = ol.Oracle(lab, pb, co, mask=mask)
+    g1 = api.MergeTreeBuilder(shape, cg).tune("generic", 1).build(lab, pb, mask)
+    aligned = shape[-1] % 4 == 0
+    if aligned:
+        g1.tune("used_tma", 0)  # raises GLIA_E_STATE if the pass did not go through TMA
+    else:
+        with pytest.raises(api.GliaError):
+            g1.tune("used_tma", 0)
+    g2 = api.MergeTreeBuilder(shape, cg).tune("generic", 1).tune("notma", 1).build(lab, pb, mask)
+    with pytest.raises(api.GliaError):
+        g2.tune("used_tma", 0)
+    for g in (g1, g2):
+        _compare_graph(o, g, co)
+
+
 def _same_graph(g1, g2):
     assert (g1.R, g1.E, g1.Cn) == (g2.R, g2.E, g2.Cn)
     r1, r2 = g1.regions(), g2.regions()
