@@ -3,6 +3,7 @@
 #include <math.h>
 #include <string.h>
 #include <algorithm>
+#include <vector>
 #include "handle.cuh"
 
 namespace glia {
@@ -126,6 +127,14 @@ extern "C" int glia_b200_create(const glia_params* p, glia_handle** out) {
   F.normArea = p->normalize ? vol : 1.0;
   F.normLen = p->normalize ? sqrt(diag) : 1.0;
   F.useLog = p->use_log; F.simple = p->simple;
+  {  // log2 of small counts (entropy terms, featurize.cuh)
+    std::vector<double> tab(4096);
+    tab[0] = 0.0;
+    for (int c = 1; c < 4096; ++c) tab[c] = log2((double)c);
+    if (h->log2tab.ensure(8 * tab.size()) != cudaSuccess ||
+        cudaMemcpy(h->log2tab.p, tab.data(), 8 * tab.size(), cudaMemcpyHostToDevice) != cudaSuccess) { glia_b200_destroy(h); return GLIA_E_CUDA; }
+    F.log2tab = h->log2tab.as<double>();
+  }
   *out = h;
   F.dim = glia_b200_row_dim(h, 0);
   return GLIA_OK;
@@ -141,7 +150,7 @@ extern "C" void glia_b200_destroy(glia_handle* h) {
                           &h->eb, &h->row, &h->rev, &h->cand, &h->bAggAdd, &h->bAggMax, &h->bAggF64,
                           &h->cubTmp, &h->scalars, &h->rows, &h->sal, &h->keysOut, &h->interest,
                           &h->exportBuf, &h->exportCursor, &h->regBlocks, &h->bAggMax2, &h->bAggOwn,
-                          &h->orient, &h->tieBuf, &h->firstVox};
+                          &h->orient, &h->tieBuf, &h->firstVox, &h->log2tab};
   for (auto b : bufs) b->release();
   for (auto& b : h->inImg) b.release();
   for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);

@@ -79,7 +79,7 @@ __device__ __forceinline__ void candidate_row_from_blocks(const FeatCfg& F, cons
     }
     ImgFeat g;
     for (int k = 0; k < F.nB; ++k) {
-      img_feat(pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g);
+      img_feat(F.log2tab, pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g);
       *p++ = g.entropy; *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
     }
     for (int k = 0; k < xi; ++k) out[x0len + k] = B1[k];

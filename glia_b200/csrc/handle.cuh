@@ -35,6 +35,7 @@ struct FeatCfg {
   double normArea, normLen;
   int useLog, simple;
   int dim;           // row length without saliency terms
+  const double* log2tab;  // device table: log2 of the counts 0 .. 4095 (featurize.cuh)
 };
 
 }  // namespace glia
@@ -116,6 +117,7 @@ struct glia_handle {
   glia::DevBuf bAggMax2, bAggOwn;                         // second-best max words and the boundary holding the best
   glia::DevBuf cubTmp, scalars, rows, sal, keysOut;
   glia::DevBuf regBlocks;                                 // per-region x1/x2 row blocks (featurize.cu)
+  glia::DevBuf log2tab;
   glia::DevBuf orient, tieBuf, firstVox;                  // equal-area orientation bits (orient.cu)
   bool hasOrient = false;
   long long orientC = 0;

@@ -289,6 +289,49 @@ def test_merge_order_bc_matches_oracle(case):
     np.testing.assert_allclose(rg["rows"], ro["rows"], rtol=RTOL, atol=1e-12)
 
 
+@pytest.mark.parametrize("shape,cell", [((512, 512), 11), ((40, 64, 64), 8)])
+def test_greedy_with_unrestricted_forest_first_divergence(shape, cell, record_property):
+    """Greedy chain scored by a forest over ALL columns (entropy, compactness, log terms included), depth 12.  The
+    transcendental columns agree to ~1e-15, not bit for bit, so a score may flip where a threshold falls between the two
+    values.  The run must equal the oracle's up to the first such flip, and that flip must be exactly that: the GPU score
+    is the oracle forest's score of the GPU row, the two rows agree within 1e-5, and a threshold of the forest separates
+    them in a differing column.  The index of the first divergence is reported (len == no divergence)."""
+    lab, pb = synth.voronoi_volume(shape, cell, seed=1234)
+    co, cg = _cfg_pair(pb)
+    o = ol.Oracle(lab, pb, co)
+    g = api.MergeTreeBuilder(shape, cg).build(lab, pb)
+    _, rowo = o.init_candidates()
+    f = synth.random_forest(63, o.row_dim(), max_depth=12, seed=7, thr_pool=rowo, leaf_prob=0.1)
+    orf, grf = ol.OracleRF.from_arrays(f, o.row_dim()), api.Forest.from_arrays(f, o.row_dim())
+    ro = o.greedy(rf=orf, want_cands=True)
+    rg = g.merge_order_bc(grf, want_rows=True)
+    m = min(len(ro["order"]), len(rg["order"]))
+    same = np.all(ro["order"][:m] == rg["order"][:m], axis=1) & (ro["sal"][:m] == rg["sal"][:m])
+    n = m if same.all() else int(np.argmin(same))
+    record_property("first_divergent_merge", n)
+    record_property("merges", m)
+    print("first divergent merge: %d of %d" % (n, m))
+    np.testing.assert_allclose(rg["rows"][:n], ro["rows"][:n], rtol=RTOL, atol=1e-12)
+    if n == m:
+        assert len(ro["order"]) == len(rg["order"])
+        return
+    # the candidate the GPU popped at step n, as the oracle saw it (latest featurisation of that key)
+    key = tuple(sorted(int(x) for x in rg["order"][n][:2]))
+    ck = np.sort(ro["cand_keys"][:, :2].astype(np.int64), axis=1)
+    hit = np.flatnonzero((ck[:, 0] == key[0]) & (ck[:, 1] == key[1]))
+    assert len(hit), "the oracle never featurised the pair the GPU merged"
+    row_o, row_g = ro["cand_rows"][hit[-1]], rg["rows"][n]
+    np.testing.assert_allclose(row_g, row_o, rtol=RTOL, atol=1e-12)
+    _, p = orf.predict(row_g[None, :])
+    assert p[0] == rg["sal"][n]                      # votes are bit-exact on identical rows
+    assert p[0] != ro["cand_scores"][hit[-1]]        # ... so the two scores differ by a decision flip
+    thr = np.unique(f["xbestsplit"][f["nodestatus"] != -1])
+    d = np.flatnonzero(row_g != row_o)
+    lo, hi = np.minimum(row_g[d], row_o[d]), np.maximum(row_g[d], row_o[d])
+    i = np.searchsorted(thr, lo, side="left")
+    assert np.any((i < len(thr)) & (thr[np.minimum(i, len(thr) - 1)] <= hi))
+
+
 def test_merge_order_c1_voronoi():
     """configs[0]: 512x512, ~2.2k superpixels: the full greedy run the reference does on CPU."""
     lab, pb = synth.voronoi_volume((512, 512), 11, seed=1234)
