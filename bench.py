@@ -52,6 +52,9 @@ WORKLOADS = {
     "c1": ((512, 512), 11, "2D 512x512, ~2.2k superpixels (BASELINE.json configs[0])"),
     "c2": ((4096, 4096), 13, "2D 4096x4096 synthetic EM slice, ~100k superpixels (BASELINE.json configs[1])"),
     "c3": ((2048, 2048), 13, "2D 2048x2048 slices, ~25k superpixels each (BASELINE.json configs[2])"),
+    # the same slice / volume with a mask (1 % of the voxels masked out): the generic voxel kernel (TMA-staged tiles)
+    "c2m": ((4096, 4096), 13, "2D 4096x4096 slice of configs[1] WITH a mask: generic voxel kernel"),
+    "c4sm": ((512, 512, 512), 10, "3D 512^3 cut of configs[3] WITH a mask: generic voxel kernel"),
     "c4s": ((512, 512, 512), 10, "3D 512^3 synthetic EM volume, ~137k supervoxels (profiling-size cut of configs[3])"),
     "c4": ((1024, 1024, 1024), 10, "3D 1024^3 synthetic EM volume, ~1.09M supervoxels (BASELINE.json configs[3])"),
 }
@@ -264,7 +267,7 @@ def main():
     # default = the largest single-GPU configuration of BASELINE.json (configs[3], north_star's target): one
     # 1024^3 volume on one GPU; with N > 1 ranks the same volume z-slab sharded over NCCL (strong scaling)
     ap.add_argument("--workload", default=os.environ.get("GLIA_BENCH_WORKLOAD", "c4"),
-                    choices=sorted(WORKLOADS) + ["c5"])
+                    choices=sorted(WORKLOADS) + ["c5"])  # c2m / c4sm: masked inputs -> voxel_pass_generic
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -334,6 +337,11 @@ def main():
         sets.append((lab, pb))
     torch.cuda.synchronize()
     label_bound = int(ncells.value) + 1
+    masked = args.workload.endswith("m")
+    mask_dev = None
+    if masked:
+        g = torch.Generator(device=dev); g.manual_seed(5)
+        mask_dev = (torch.rand(nvox, device=dev, generator=g) > 0.01).to(torch.int32)
 
     forest_arrays, forest = make_forest(api, synth, torch, dim, nd, local_rank)
 
@@ -356,7 +364,7 @@ def main():
         b = builders[0]
         lab, pb = sets[i % nsets]
         b.set_image(0, 0, pb.data_ptr()); b.set_image(2, 0, pb.data_ptr())
-        b.build(lab.data_ptr(), pb.data_ptr())
+        b.build(lab.data_ptr(), pb.data_ptr(), mask_dev.data_ptr() if mask_dev is not None else None)
         if sal_dev.numel() < b.Cn:
             sal_dev = torch.empty(int(b.Cn * 1.2) + 64, dtype=torch.float64, device=dev)
         b.score_candidates(forest, sal_dev.data_ptr())
@@ -403,7 +411,7 @@ def main():
 
     # ---- e2e: host (pinned) buffers through the C ABI, H2D + D2H inside the timed region
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and not masked:
         # two slices in flight per GPU (two handles, each with its own stream, driven by two host
         # threads): the upload of slice i+1 overlaps graph/featurise/RF of slice i.  Every step still
         # copies its inputs from pinned host memory and reads its saliencies back.
@@ -493,7 +501,7 @@ def main():
         return {"bound": "hbm", "kernel": kernel, "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
                 "traffic": tr["bytes"] if tr else None, "traffic_capture": tr["capture"] if tr else None,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": alg, "launch_ms": ms}
-    roofs = [roof("voxel_pass_fast", 8.0 * nvox, kern_ms[0]),
+    roofs = [roof("voxel_pass_generic" if masked else "voxel_pass_fast", (12.0 if masked else 8.0) * nvox, kern_ms[0]),
              roof("rf_score", float(Cn) * (8 * dim + 8) + 16.0 * float(forest_arrays["ndbigtree"].sum()),
                   kern_ms[3])]
     dominant = max(roofs, key=lambda r: r["launch_ms"])

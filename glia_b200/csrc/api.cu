@@ -85,7 +85,7 @@ extern "C" int glia_b200_create(const glia_params* p, glia_handle** out) {
   // 2D rows of 128 + 2 halo voxels stay inside the 256-element box limit of a TMA tensor copy (voxel_pass.cu)
   if (p->ndim == 2) { P.TX = std::min(128, ((P.X + 31) / 32) * 32); P.TY = 1; P.TZ = 16; }
   else { P.TX = 32; P.TY = 8; P.TZ = 16; }
-  P.SXp = ((P.TX + 2 + 3) / 4) * 4;
+  P.SXp = P.TX + 8;  // 4 voxels of padding on either side: 16-byte aligned tile rows (voxel_pass.cu)
   P.tilesX = (P.X + P.TX - 1) / P.TX; P.tilesY = (P.Y + P.TY - 1) / P.TY;
   P.tilesZ = (ze - zb + P.TZ - 1) / P.TZ;
   P.nThr = p->n_thr;

@@ -45,7 +45,7 @@ struct VoxParams {
   int zBuf0;        // global z of buffer plane 0
   int zBufN;        // planes in the buffer
   int TX, TY, TZ;   // tile extent (threads = TX*TY, each marches TZ planes)
-  int SXp;          // row pitch of the staged label tile: TX + 2 rounded up to whole 16-byte units
+  int SXp;          // row pitch of the staged label tile: TX + 8 (the tile starts 4 voxels left of the CTA's columns)
   int tilesX, tilesY, tilesZ;
   int nThr;
   float thr_up[GLIA_MAX_THR];  // (double)pb >= t  <=>  pb >= ceil_f32(t)

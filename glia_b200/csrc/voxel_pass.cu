@@ -22,6 +22,7 @@
 
 namespace glia {
 
+#define GLIA_TILE_XOFF 4
 // ---- TMA + mbarrier (sm_100a): the label (and mask) tile with its one-voxel halo is ONE bulk tensor copy issued by
 // one thread; out-of-volume elements are zero-filled by the copy engine, completion is signalled on an mbarrier.
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -104,7 +105,10 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
                    const __grid_constant__ CUtensorMap tmLab, const __grid_constant__ CUtensorMap tmMask) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int hy = (P.ndim == 2) ? 0 : 1;
-  const int SX = P.SXp, SY = P.TY + 2 * hy, SZ = P.TZ + 2;  // SX = TX + 2 rounded up to whole 16-byte units (TMA box)
+  // The staged tile starts GLIA_TILE_XOFF = 4 voxels left of the CTA's first column and is TX + 8 wide: a TMA tensor copy
+  // needs its innermost start coordinate on a 16-byte boundary (measured: profiles/microbench/tma_probe.cu - a start of
+  // x0 - 1 raises "illegal instruction", x0 - 4 with zero-filled out-of-volume elements is fine).
+  const int SX = P.SXp, SY = P.TY + 2 * hy, SZ = P.TZ + 2;
   const int ncell = SX * SY * SZ;
   // carve shared memory: the TMA destinations first (128-byte aligned), then 8-byte items
   unsigned char* sp = smem_raw;
@@ -136,8 +140,8 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
     if (tid == 0) {  // one thread issues the bulk tensor copies; everybody else initialises the tables meanwhile
       const uint32_t bytes = 4u * (uint32_t)ncell;
       mbar_expect_tx(&mbar, P.mask ? 2u * bytes : bytes);
-      tma_load_3d(lab, &tmLab, &mbar, x0 - 1, y0 - hy, z0 - 1 - P.zBuf0);
-      if (P.mask) tma_load_3d(msk, &tmMask, &mbar, x0 - 1, y0 - hy, z0 - 1 - P.zBuf0);
+      tma_load_3d(lab, &tmLab, &mbar, x0 - GLIA_TILE_XOFF, y0 - hy, z0 - 1 - P.zBuf0);
+      if (P.mask) tma_load_3d(msk, &tmMask, &mbar, x0 - GLIA_TILE_XOFF, y0 - hy, z0 - 1 - P.zBuf0);
     }
   }
   // ---- init shared tables
@@ -155,7 +159,7 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
     for (int i = tid; i < ncell; i += nthreads) {
       int cx = i % SX, r = i / SX;
       int cy = r % SY, cz = r / SY;
-      int gx = x0 - 1 + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
+      int gx = x0 - GLIA_TILE_XOFF + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
       int bz = gz - P.zBuf0;
       bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 && bz < P.zBufN;
       if (ok && P.mask && msk[i] == 0) ok = false;
@@ -166,7 +170,7 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
     for (int i = tid; i < ncell; i += nthreads) {
       int cx = i % SX, r = i / SX;
       int cy = r % SY, cz = r / SY;
-      int gx = x0 - 1 + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
+      int gx = x0 - GLIA_TILE_XOFF + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
       int bz = gz - P.zBuf0;
       bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 &&
                 bz < P.zBufN;
@@ -194,7 +198,7 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
     for (int zz = 0; zz < P.TZ; ++zz) {
       int gz = z0 + zz;
       if (gz >= P.zEnd) break;
-      int c = ((zz + 1) * SY + (ty + hy)) * SX + tx + 1;
+      int c = ((zz + 1) * SY + (ty + hy)) * SX + tx + GLIA_TILE_XOFF;
       if (!valid[c]) continue;
       uint32_t me = lab[c];
       if (me == 0xFFFFFFFFu) { atomicOr(P.overflow, 2); continue; }  // reserved: the empty-slot marker of the tables
