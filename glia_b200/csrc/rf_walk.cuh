@@ -63,8 +63,7 @@ __device__ __forceinline__ uint32_t rf_walk_blocks(const uint4* __restrict__ bp,
     bool r1 = d > 1;
     if ((uint32_t)d <= 1u) r1 = rf_exact_right(xg, thr, fc, 3u * k + (r0 ? 2u : 1u));
     const uint32_t o = (r0 ? 2u : 0u) + (r1 ? 1u : 0u);
-    const uint32_t bits = w.w >> (24u + o);
-    if (bits & 1u) return ((bits >> 4) & 1u) == wantBit ? 1u : 0u;
+    if (w.w & (0x01000000u << o)) return ((w.w >> (28u + o)) & 1u) == wantBit ? 1u : 0u;  // leaf: one shift + one test
     k = (w.w & 0xFFFFFu) + o;
   }
 }
