@@ -105,6 +105,12 @@ def run_slab(args, rank, world, local_rank, dist):
     clocks = sampler.stop()
     elapsed_ms = _max_over_ranks(torch, dist, world, dev, e0.elapsed_time(e1))
     cands = _sum_over_ranks(torch, dist, world, dev, b.Cn)
+    # per-rank picture (who waits for whom): candidates owned and mean stage times of every rank
+    mine = torch.tensor([float(b.Cn), acc["voxel_ms"] / args.steps, acc["exchange_ms"] / args.steps, acc["graph_ms"] / args.steps,
+                         feat_ms / args.steps, rf_ms / args.steps], device=dev, dtype=torch.float64)
+    allr = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allr, mine)
+    per_rank = [[round(float(x), 3) for x in t.tolist()] for t in allr]
     sent_all = _sum_over_ranks(torch, dist, world, dev, sent / args.steps)
     vox_kernel_ms = _max_over_ranks(torch, dist, world, dev, b.last_ms()[0])
     launches = b.launch_count() - launches0
@@ -164,6 +170,7 @@ def run_slab(args, rank, world, local_rank, dist):
                                    "featurize": feat_ms / args.steps, "rf_score": rf_ms / args.steps},
                 "exchange_detail_ms_rank0": {k: v / args.steps for k, v in detail.items()},
                 "exchange_bytes_per_step": sent_all,
+                "per_rank": {"columns": ["candidates", "voxel_ms", "exchange_ms", "graph_ms", "featurize_ms", "rf_ms"], "rows": per_rank},
                 "roofline": {"bound": "hbm", "kernel": "voxel_pass_fast", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": alg},

@@ -66,6 +66,9 @@ region_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ 
   o[xi] = s.area; o[xi + 1] = s.perim;
 }
 
+// One thread per candidate.  The kernel is bound by the latency of its scattered record loads (long-scoreboard stalls, 16 %
+// issue utilisation at 24 warps / SM: profiles/r2_ncu_featurize_c4s.txt); splitting a row over two threads (more loads in
+// flight) was measured SLOWER (C4 7.6 -> 9.0 ms: both halves re-read the shared records and the row writes interleave).
 __global__ void __launch_bounds__(128)
 init_candidates_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G, int xi,
                               const double* __restrict__ blk, const unsigned char* __restrict__ orient,
