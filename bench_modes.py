@@ -63,10 +63,25 @@ def run_slab(args, rank, world, local_rank, dist):
     cfg = api.FeatureConfig(rimgs=spec, bimgs=spec, thr=B.THR)
     b = par.slab_builder(shape, cfg, comm, label_bound, device=local_rank, device_pointers=True, stream=stream)
     sal = torch.empty(64, dtype=torch.float64, device=dev)
+    # exchange: the library's own stream-ordered NCCL sequence (glia_b200_build_sharded) unless GLIA_BENCH_EXCHANGE=torch
+    # asks for the torch.distributed-driven one (glia_b200/parallel.py, also what the CPU / thread-emulated tests drive)
+    native = None
+    if os.environ.get("GLIA_BENCH_EXCHANGE", "native") == "native":
+        native = par.native_comm(dist, world, rank, local_rank)
+
+    def build(bb, l, p, tm=None):
+        if native is None:
+            return par.build_sharded(comm, bb, l, p, timings=tm)
+        bb.build_sharded(native, l, p)
+        if tm is not None:
+            ms = bb.last_ms()
+            tm.update(voxel_ms=ms[0] + ms[4], exchange_ms=native.last_exchange_ms(), graph_ms=ms[1],
+                      exchange_detail_ms={"native (one stream-ordered call)": native.last_exchange_ms()},
+                      sent_records=0, record_bytes=0)
 
     def step(tm=None):
         nonlocal sal
-        par.build_sharded(comm, b, lab.data_ptr(), pb.data_ptr(), timings=tm)
+        build(b, lab.data_ptr(), pb.data_ptr(), tm)
         if sal.numel() < b.Cn:
             sal = torch.empty(int(b.Cn * 1.2) + 64, dtype=torch.float64, device=dev)
         if b.Cn:
@@ -132,7 +147,7 @@ def run_slab(args, rank, world, local_rank, dist):
             if i == 1:
                 barrier()
                 t0 = time.perf_counter()
-            par.build_sharded(comm, hb, hln, hpn)
+            build(hb, hln, hpn)
             if hb.Cn:
                 hb.score_candidates(forest, hsal)
         torch.cuda.synchronize()
@@ -160,7 +175,9 @@ def run_slab(args, rank, world, local_rank, dist):
                 "vs_baseline": None, "dtype": "u32 labels / f32 pb / f64 features", "data": "synthetic",
                 "config": {"workload": args.workload + ": " + desc,
                            "sharding": "z-slabs of %d planes + 1-plane label halo; all-reduce of dense region tables, "
-                                       "boundary records all-to-all keyed by label pair (NCCL)" % (z1 - z0),
+                                       "boundary records exchanged and reduced by label pair (NCCL)" % (z1 - z0),
+                           "exchange": "native: glia_b200_build_sharded (C++, stream-ordered)" if native is not None
+                                       else "torch.distributed collectives driven from glia_b200/parallel.py",
                            "row_dim": dim, "candidates": int(cands),
                            "forest": dict(B.FOREST_INFO),
                            "l2": "slab input %.2f GB >> 126 MB L2" % (8 * nloc / 1e9)},
@@ -183,6 +200,8 @@ def run_slab(args, rank, world, local_rank, dist):
                                     "sample": r["sample"], "candidates_per_s": r["cand_s"]}
         emit(line)
     b.close()
+    if native is not None:
+        native.close()
     dist.destroy_process_group()
     return 0
 

@@ -60,7 +60,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_synth_voronoi_slab", "glia_b200_set_image", "glia_b200_rf_ensemble",
            "glia_b200_region_presence", "glia_b200_index_regions", "glia_b200_gather_regions",
            "glia_b200_tune", "glia_b200_candidate_ties", "glia_b200_set_tie_orientation",
-           "glia_b200_reference_orientation"]
+           "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
+           "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms"]
 
 
 def lib():
@@ -78,6 +79,13 @@ def lib():
         L.glia_b200_last_error.restype = C.c_char_p
         L.glia_b200_build.argtypes = [vp, vp, vp, vp]
         L.glia_b200_tune.argtypes = [vp, C.c_char_p, C.c_int]
+        L.glia_b200_comm_unique_id.argtypes = [vp]
+        L.glia_b200_comm_create.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+        L.glia_b200_comm_destroy.argtypes = [vp]
+        L.glia_b200_comm_destroy.restype = None
+        L.glia_b200_build_sharded.argtypes = [vp, vp, vp, vp, vp]
+        L.glia_b200_comm_last_exchange_ms.argtypes = [vp]
+        L.glia_b200_comm_last_exchange_ms.restype = C.c_double
         L.glia_b200_candidate_ties.argtypes = [vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_set_tie_orientation.argtypes = [vp, vp]
         L.glia_b200_reference_orientation.argtypes = [vp, C.c_int64, vp]
@@ -221,6 +229,35 @@ class Forest:
             self.close()
         except Exception:
             pass
+
+
+class NativeComm:
+    """NCCL communicator pair owned by the library (include/glia_b200.h: glia_b200_comm_*), for
+    MergeTreeBuilder.build_sharded.  `id256`: the 256 bytes of unique_id() of one rank, identical on all ranks."""
+
+    def __init__(self, id256, world, rank, device=0):
+        self.h = C.c_void_p()
+        buf = (C.c_ubyte * 256).from_buffer_copy(bytes(id256))
+        st = lib().glia_b200_comm_create(buf, world, rank, device, C.byref(self.h))
+        if st:
+            raise GliaError(st, "glia_b200_comm_create")
+        self.world, self.rank = world, rank
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_ubyte * 256)()
+        st = lib().glia_b200_comm_unique_id(buf)
+        if st:
+            raise GliaError(st, "glia_b200_comm_unique_id (is libnccl.so.2 loadable?)")
+        return bytes(buf)
+
+    def last_exchange_ms(self):
+        return float(lib().glia_b200_comm_last_exchange_ms(self.h))
+
+    def close(self):
+        if self.h:
+            lib().glia_b200_comm_destroy(self.h)
+            self.h = C.c_void_p()
 
 
 class MergeTreeBuilder:
@@ -412,6 +449,17 @@ class MergeTreeBuilder:
         v = [C.c_int64() for _ in range(3)]
         self._check(lib().glia_b200_counts(self.h, *[C.byref(x) for x in v]))
         self.R, self.E, self.Cn = (x.value for x in v)
+
+    def build_sharded(self, comm, labels, pb, mask=None):
+        """The whole z-slab sequence (voxel pass, NCCL exchange, graph) in one stream-ordered library call."""
+        if not self.device_pointers:
+            labels = np.ascontiguousarray(labels, np.uint32)
+            pb = np.ascontiguousarray(pb, np.float32)
+            mask = None if mask is None else np.ascontiguousarray(mask, np.uint32)
+            self._keep += [labels, pb, mask]
+        self._check(lib().glia_b200_build_sharded(self.h, comm.h, _addr(labels), _addr(mask), _addr(pb)))
+        self._counts()
+        return self
 
     def build_partial(self, labels, pb, mask=None):
         if not self.device_pointers:

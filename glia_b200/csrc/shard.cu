@@ -292,3 +292,224 @@ extern "C" int glia_b200_finalize_edges(glia_handle* h, int64_t own_lo, int64_t 
   h->err.clear();
   return GLIA_OK;
 }
+
+// ================================================================================================
+// The exchange as ONE stream-ordered call over NCCL (C++; no Python between the steps).
+//
+// glia_b200/parallel.py drives the entry points above with torch.distributed collectives: every step there is a
+// Python call and most of them end in a host synchronisation, which at 8 GPUs costs about as much as the voxel pass
+// of a 128-plane slab (profiles/r2_bench_c4_n8.json).  glia_b200_build_sharded issues the same sequence from C++:
+// NCCL calls go on the handle's stream, the all-reduce of the record tables runs on a second communicator and a side
+// stream, and the host only waits where it needs a number to size a buffer (R, the send / receive counts, E, C).
+// NCCL is bound at run time (dlopen "libnccl.so.2": the copy the process already holds - torch's in bench.py, the
+// system's in a C++ host), so libglia_b200.so has no link-time dependency on it.
+#include <dlfcn.h>
+#include <nccl.h>
+#include <string.h>
+#include <vector>
+
+namespace {
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*GroupStart)();
+  ncclResult_t (*GroupEnd)();
+  const char* (*GetErrorString)(ncclResult_t);
+  bool ok;
+};
+NcclApi* nccl_api() {
+  static NcclApi a;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    memset(&a, 0, sizeof(a));
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (lib) {
+#define GLIA_SYM(field, name) *(void**)(&a.field) = dlsym(lib, name)
+      GLIA_SYM(GetUniqueId, "ncclGetUniqueId"); GLIA_SYM(CommInitRank, "ncclCommInitRank");
+      GLIA_SYM(CommDestroy, "ncclCommDestroy"); GLIA_SYM(AllReduce, "ncclAllReduce");
+      GLIA_SYM(AllGather, "ncclAllGather"); GLIA_SYM(Send, "ncclSend"); GLIA_SYM(Recv, "ncclRecv");
+      GLIA_SYM(GroupStart, "ncclGroupStart"); GLIA_SYM(GroupEnd, "ncclGroupEnd");
+      GLIA_SYM(GetErrorString, "ncclGetErrorString");
+#undef GLIA_SYM
+      a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllReduce && a.AllGather && a.Send && a.Recv &&
+             a.GroupStart && a.GroupEnd && a.GetErrorString;
+    }
+  }
+  return a.ok ? &a : nullptr;
+}
+}  // namespace
+
+struct glia_comm {
+  ncclComm_t main = nullptr, side = nullptr;  // boundary exchange | all-reduce of the region record tables
+  int world = 1, rank = 0, device = 0;
+  cudaStream_t sideStream = nullptr;
+  cudaEvent_t evTables = nullptr, evSide = nullptr, evA = nullptr, evB = nullptr, evC = nullptr;
+  glia::DevBuf recv, counts;
+  double exchangeMs = -1.0;
+};
+
+#define NK(h, expr)                                                                                   \
+  do {                                                                                                \
+    ncclResult_t r_ = (expr);                                                                         \
+    if (r_ != ncclSuccess) { (h)->err = std::string(#expr) + ": " + N->GetErrorString(r_); return GLIA_E_CUDA; } \
+  } while (0)
+
+extern "C" int glia_b200_comm_unique_id(void* id256) {
+  NcclApi* N = nccl_api();
+  if (!N || !id256) return GLIA_E_ARG;
+  ncclUniqueId ids[2];
+  if (N->GetUniqueId(&ids[0]) != ncclSuccess || N->GetUniqueId(&ids[1]) != ncclSuccess) return GLIA_E_CUDA;
+  memcpy(id256, ids, sizeof(ids));
+  return GLIA_OK;
+}
+
+extern "C" int glia_b200_comm_create(const void* id256, int world, int rank, int device, glia_comm** out) {
+  NcclApi* N = nccl_api();
+  if (!N || !id256 || !out || world < 1 || world > 64 || rank < 0 || rank >= world) return GLIA_E_ARG;
+  if (cudaSetDevice(device) != cudaSuccess) return GLIA_E_CUDA;
+  ncclUniqueId ids[2];
+  memcpy(ids, id256, sizeof(ids));
+  glia_comm* c = new glia_comm();
+  c->world = world; c->rank = rank; c->device = device;
+  if (N->CommInitRank(&c->main, world, ids[0], rank) != ncclSuccess || N->CommInitRank(&c->side, world, ids[1], rank) != ncclSuccess ||
+      cudaStreamCreateWithFlags(&c->sideStream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete c; return GLIA_E_CUDA;
+  }
+  cudaEventCreateWithFlags(&c->evTables, cudaEventDisableTiming); cudaEventCreateWithFlags(&c->evSide, cudaEventDisableTiming);
+  cudaEventCreate(&c->evA); cudaEventCreate(&c->evB); cudaEventCreate(&c->evC);
+  *out = c;
+  return GLIA_OK;
+}
+
+extern "C" void glia_b200_comm_destroy(glia_comm* c) {
+  if (!c) return;
+  NcclApi* N = nccl_api();
+  cudaSetDevice(c->device);
+  if (N) { if (c->main) N->CommDestroy(c->main); if (c->side) N->CommDestroy(c->side); }
+  if (c->sideStream) cudaStreamDestroy(c->sideStream);
+  cudaEvent_t evs[5] = {c->evTables, c->evSide, c->evA, c->evB, c->evC};
+  for (auto e : evs) if (e) cudaEventDestroy(e);
+  c->recv.release(); c->counts.release();
+  delete c;
+}
+
+extern "C" double glia_b200_comm_last_exchange_ms(const glia_comm* c) { return c ? c->exchangeMs : -1.0; }
+
+// labels / mask / pb hold planes [z_begin - halo_lo, z_end + halo_hi) of the volume, as for glia_b200_build_partial.
+// On return the handle is finalised and answers init_candidates / score_candidates for the candidates this rank owns.
+extern "C" int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint32_t* labels, const uint32_t* mask,
+                                       const float* pb) {
+  NcclApi* N = nccl_api();
+  if (!h || !c || !N) return GLIA_E_ARG;
+  if (c->device != h->prm.device) { h->err = "communicator lives on another device"; return GLIA_E_ARG; }
+  const int world = c->world, me = c->rank;
+  int s = glia_b200_build_partial(h, labels, mask, pb);  // voxel pass; ends with the overflow check
+  if (s != GLIA_OK) return s;
+  cudaStream_t st = h->stream;
+  const VoxParams& P = h->vp;
+  const uint32_t LB = P.labelBound;
+  CK(cudaEventRecord(c->evA, st));
+  // presence flags from the LOCAL table first: the all-reduce below rewrites the table in place
+  s = glia_region_presence(h);
+  if (s != GLIA_OK) return s;
+  // record tables: all-reduce on the side communicator / side stream, needed only by gather_regions at the very end
+  CK(cudaEventRecord(c->evTables, st));
+  CK(cudaStreamWaitEvent(c->sideStream, c->evTables, 0));
+  NK(h, N->AllReduce(h->regAdd.p, h->regAdd.p, (size_t)LB * P.reg.nAdd, ncclUint32, ncclSum, c->side, c->sideStream));
+  NK(h, N->AllReduce(h->regMax.p, h->regMax.p, (size_t)LB * P.reg.nMax, ncclUint32, ncclMax, c->side, c->sideStream));
+  if (P.reg.nF64) NK(h, N->AllReduce(h->regF64.p, h->regF64.p, (size_t)LB * P.reg.nF64, ncclFloat64, ncclSum, c->side, c->sideStream));
+  CK(cudaEventRecord(c->evSide, c->sideStream));
+  NK(h, N->AllReduce(h->flags.p, h->flags.p, (size_t)LB, ncclUint32, ncclMax, c->main, st));
+  s = glia_index_regions(h);  // scan + read-back of R
+  if (s != GLIA_OK) return s;
+  const long long R = h->R;
+  // interest mask
+  {
+    const size_t n = (size_t)std::max<long long>(R, 1) * world;
+    CK(h->interest.ensure(n));
+    CK(cudaMemsetAsync(h->interest.p, 0, n, st));
+    const uint32_t chunk = (uint32_t)std::max<long long>(1, (R + world - 1) / world);
+    edge_interest_kernel<<<nblk(P.edgeCap, 256), 256, 0, st>>>((const unsigned long long*)h->edgeKeys.p, P.edgeCap,
+                                                               h->rank.as<uint32_t>(), chunk, world, h->interest.as<unsigned char>());
+    h->launches += 2;
+    CK(cudaGetLastError());
+    if (R > 0) NK(h, N->AllReduce(h->interest.p, h->interest.p, (size_t)R * world, ncclUint8, ncclMax, c->main, st));
+  }
+  // boundary records: count per destination, exchange the counts, pack, send / receive, merge
+  const int rw = rec_words(P.edge);
+  CK(h->exportCursor.ensure(8 * 65));
+  CK(c->counts.ensure(8 * (size_t)(world + 2) * (world + 1)));
+  unsigned long long* cursor = h->exportCursor.as<unsigned long long>();
+  unsigned long long* mine = c->counts.as<unsigned long long>();          // [world + 2]: counts, occupied, capacity
+  unsigned long long* all = mine + (world + 2);                           // [world][world + 2]
+  bool rebuild = false;
+  std::vector<unsigned long long> info((size_t)world * (world + 2)), off(world), roff(world);
+  unsigned long long total = 0, rtotal = 0;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const int skip = rebuild ? -1 : me;
+    CK(cudaMemsetAsync(cursor, 0, 8 * 65, st));
+    export_edges_kernel<0><<<nblk(P.edgeCap, 256), 256, 0, st>>>(
+        (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), h->interest.as<unsigned char>(), world,
+        P.edge, nullptr, nullptr, nullptr, cursor, rw, nullptr, skip);
+    h->launches += 2;
+    CK(cudaMemcpyAsync(mine, cursor, 8 * (size_t)world, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(mine + world, cursor + 64, 8, cudaMemcpyDeviceToDevice, st));
+    const unsigned long long capv = P.edgeCap;
+    CK(cudaMemcpyAsync(mine + world + 1, &capv, 8, cudaMemcpyHostToDevice, st));
+    NK(h, N->AllGather(mine, all, (size_t)world + 2, ncclUint64, c->main, st));
+    CK(cudaMemcpyAsync(info.data(), all, 8 * info.size(), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    h->tableOccupied = (long long)info[(size_t)me * (world + 2) + world];
+    bool tight = false;  // would some rank's table be more than 80 % full after the merge?
+    for (int q = 0; q < world && !rebuild; ++q) {
+      unsigned long long in = 0;
+      for (int r = 0; r < world; ++r) in += info[(size_t)r * (world + 2) + q];
+      tight = tight || (info[(size_t)q * (world + 2) + world] + in) * 10 > info[(size_t)q * (world + 2) + world + 1] * 8;
+    }
+    if (tight && !rebuild) { rebuild = true; continue; }
+    total = rtotal = 0;
+    for (int d = 0; d < world; ++d) { off[d] = total; total += info[(size_t)me * (world + 2) + d]; }
+    for (int r = 0; r < world; ++r) { roff[r] = rtotal; rtotal += info[(size_t)r * (world + 2) + me]; }
+    break;
+  }
+  CK(h->exportBuf.ensure(4 * (size_t)rw * (size_t)std::max<unsigned long long>(total, 1)));
+  CK(c->recv.ensure(4 * (size_t)rw * (size_t)std::max<unsigned long long>(rtotal, 1)));
+  CK(cudaMemcpyAsync(cursor, off.data(), 8 * (size_t)world, cudaMemcpyHostToDevice, st));
+  export_edges_kernel<1><<<nblk(P.edgeCap, 256), 256, 0, st>>>(
+      (const unsigned long long*)h->edgeKeys.p, P.edgeCap, h->rank.as<uint32_t>(), h->interest.as<unsigned char>(), world,
+      P.edge, h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), cursor, rw,
+      h->exportBuf.as<uint32_t>(), rebuild ? -1 : me);
+  h->launches++;
+  CK(cudaGetLastError());
+  NK(h, N->GroupStart());
+  for (int p = 0; p < world; ++p) {
+    const unsigned long long ns = info[(size_t)me * (world + 2) + p], nr = info[(size_t)p * (world + 2) + me];
+    if (ns) NK(h, N->Send(h->exportBuf.as<uint32_t>() + (size_t)off[p] * rw, (size_t)ns * rw, ncclUint32, p, c->main, st));
+    if (nr) NK(h, N->Recv(c->recv.as<uint32_t>() + (size_t)roff[p] * rw, (size_t)nr * rw, ncclUint32, p, c->main, st));
+  }
+  NK(h, N->GroupEnd());
+  CK(cudaEventRecord(c->evB, st));
+  s = glia_b200_import_edges(h, rtotal ? c->recv.p : nullptr, (int64_t)rtotal, rebuild ? 1 : 0);
+  if (s != GLIA_OK) return s;
+  const long long chunkR = std::max<long long>(1, (R + world - 1) / world);
+  const long long lo = std::min<long long>(R, (long long)me * chunkR);
+  const long long hi = me == world - 1 ? R : std::min<long long>(R, lo + chunkR);
+  s = glia_b200_finalize_edges(h, lo, hi);
+  if (s != GLIA_OK) return s;
+  CK(cudaStreamWaitEvent(st, c->evSide, 0));  // the reduced record tables
+  s = glia_gather_regions(h);
+  if (s != GLIA_OK) return s;
+  CK(cudaEventRecord(c->evC, st));
+  CK(cudaStreamSynchronize(st));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->evA, c->evB); c->exchangeMs = ms;
+  cudaEventElapsedTime(&ms, c->evB, c->evC); h->ms[1] = ms;  // graph: import + CSR + candidates + region gather
+  return GLIA_OK;
+}

@@ -225,6 +225,17 @@ def slab_builder(shape, cfg, comm, label_bound, device=0, device_pointers=False,
                                 stream=stream)
 
 
+def native_comm(dist, world, rank, device):
+    """The library's own NCCL communicator pair (api.NativeComm): rank 0 draws the unique ids, torch.distributed only
+    carries the 256 bytes to the other ranks."""
+    dev = torch.device("cuda", device)
+    t = torch.zeros(256, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        t.copy_(torch.frombuffer(bytearray(api.NativeComm.unique_id()), dtype=torch.uint8))
+    dist.broadcast(t, src=0)
+    return api.NativeComm(bytes(t.cpu().numpy().tobytes()), world, rank, device)
+
+
 def build_sharded(comm, b, labels, pb, mask=None, timings=None):
     """Voxel pass on the owned planes, then the exchange steps listed in include/glia_b200.h.
     labels/pb/mask hold planes [z_begin - halo_lo, z_end + halo_hi).  On return `b` is finalised and

@@ -191,6 +191,19 @@ GLIA_API int glia_b200_table_load(const glia_handle* h, int64_t* occupied, int64
 GLIA_API int glia_b200_import_edges(glia_handle* h, const void* buf, int64_t n, int clear_first);
 GLIA_API int glia_b200_finalize_edges(glia_handle* h, int64_t own_lo, int64_t own_hi);
 
+/* The same sequence as ONE call over NCCL, stream-ordered on the handle's stream (shard.cu): the host waits only where
+ * it needs a number to size a buffer.  NCCL is bound at run time (dlopen of libnccl.so.2), the library has no link-time
+ * dependency on it.  glia_b200_comm_unique_id fills 256 bytes (two ncclUniqueId: boundary exchange / record-table
+ * all-reduce) on one rank; the caller hands them to every rank (any transport), which then calls glia_b200_comm_create
+ * collectively.  One communicator per handle / GPU; ranks may be processes or threads of one process. */
+typedef struct glia_comm glia_comm;
+GLIA_API int glia_b200_comm_unique_id(void* id256);
+GLIA_API int glia_b200_comm_create(const void* id256, int world, int rank, int device, glia_comm** out);
+GLIA_API void glia_b200_comm_destroy(glia_comm* c);
+GLIA_API int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint32_t* labels, const uint32_t* mask,
+                                     const float* pb);
+GLIA_API double glia_b200_comm_last_exchange_ms(const glia_comm* c);
+
 /* ---- random forest ---- */
 GLIA_API int glia_b200_rf_load(const char* path, int device, glia_rf** out);
 /* Native layouts after readModelFromBinaryFile's transposes (ml_rf_model.cxx:542-557):
