@@ -244,6 +244,10 @@ int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask,
       // 512 table slots keep a CTA at ~51 KB (3D) / ~66 KB (2D) of shared memory: 4 / 3 CTAs per SM.
       if (P.ndim == 2) { F.warpsX = 8; F.warpsY = 1; } else { F.warpsX = 1; F.warpsY = 8; }
       F.TZ = h->tuneTZ > 0 ? h->tuneTZ : (P.ndim == 3 ? 24 : 16);  // measured: profiles/r2_voxel_notes.txt
+      if (h->tuneTZ <= 0 && P.ndim == 3) {  // even out the tiles of a short slab: 128 planes -> 6 tiles of 22, not 5 x 24 + 8
+        const int planes = P.zEnd - P.zBegin, nt = (planes + F.TZ - 1) / F.TZ;
+        if (nt > 0) F.TZ = (planes + nt - 1) / nt;
+      }
       if (F.TZ + F.warpsY > 32) F.TZ = 32 - F.warpsY;  // y and z occupancy masks share one word
       while (F.TZ > 1 && (long long)P.X * P.Y * (F.TZ + 3) >= (1ll << 31)) F.TZ >>= 1;
       F.tilesX = (P.X + 32 * F.warpsX - 1) / (32 * F.warpsX);

@@ -445,7 +445,7 @@ extern "C" int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint3
   // boundary records: count per destination, exchange the counts, pack, send / receive, merge
   const int rw = rec_words(P.edge);
   CK(h->exportCursor.ensure(8 * 65));
-  CK(c->counts.ensure(8 * (size_t)(world + 2) * (world + 1)));
+  CK(c->counts.ensure(8 * (size_t)(world + 2) * (world + 1) + 16));
   unsigned long long* cursor = h->exportCursor.as<unsigned long long>();
   unsigned long long* mine = c->counts.as<unsigned long long>();          // [world + 2]: counts, occupied, capacity
   unsigned long long* all = mine + (world + 2);                           // [world][world + 2]
@@ -496,18 +496,36 @@ extern "C" int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint3
   }
   NK(h, N->GroupEnd());
   CK(cudaEventRecord(c->evB, st));
-  s = glia_b200_import_edges(h, rtotal ? c->recv.p : nullptr, (int64_t)rtotal, rebuild ? 1 : 0);
-  if (s != GLIA_OK) return s;
+  bool checkImport = false;
+  if (rebuild) {  // rare path (labels far from spatial order): rebuild / grow the table from the received runs
+    s = glia_b200_import_edges(h, rtotal ? c->recv.p : nullptr, (int64_t)rtotal, 1);
+    if (s != GLIA_OK) return s;
+  } else if (rtotal) {  // merge the received records into the table that already holds this rank's own; checked at the end
+    VoxParams& PW = h->vp;
+    CK(cudaMemsetAsync(PW.overflow, 0, 4, st));
+    import_edges_kernel<<<nblk(rtotal, 256), 256, 0, st>>>(
+        c->recv.as<uint32_t>(), (long long)rtotal, rw, PW.edge, (unsigned long long*)h->edgeKeys.p, PW.edgeCap,
+        h->edgeAdd.as<uint32_t>(), h->edgeMax.as<uint32_t>(), h->edgeF64.as<double>(), PW.overflow);
+    // glia_finalize_edges re-zeroes the scalar block that holds the flag: keep a copy for the check at the end
+    CK(cudaMemcpyAsync(c->counts.as<unsigned long long>() + (size_t)(world + 2) * (world + 1), PW.overflow, 4, cudaMemcpyDeviceToDevice, st));
+    h->launches += 2;
+    checkImport = true;
+  }
   const long long chunkR = std::max<long long>(1, (R + world - 1) / world);
   const long long lo = std::min<long long>(R, (long long)me * chunkR);
   const long long hi = me == world - 1 ? R : std::min<long long>(R, lo + chunkR);
-  s = glia_b200_finalize_edges(h, lo, hi);
+  s = glia_finalize_edges(h, lo, std::min<long long>(hi, R));
   if (s != GLIA_OK) return s;
   CK(cudaStreamWaitEvent(st, c->evSide, 0));  // the reduced record tables
   s = glia_gather_regions(h);
   if (s != GLIA_OK) return s;
   CK(cudaEventRecord(c->evC, st));
+  int importOvf = 0;
+  if (checkImport) CK(cudaMemcpyAsync(&importOvf, c->counts.as<unsigned long long>() + (size_t)(world + 2) * (world + 1), 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  if (importOvf) { h->err = "directed-boundary table full while merging received records: raise edge_capacity"; return GLIA_E_CAPACITY; }
+  h->built = true;
+  h->err.clear();
   float ms = 0;
   cudaEventElapsedTime(&ms, c->evA, c->evB); c->exchangeMs = ms;
   cudaEventElapsedTime(&ms, c->evB, c->evC); h->ms[1] = ms;  // graph: import + CSR + candidates + region gather
