@@ -36,6 +36,7 @@ class Params(C.Structure):
         ("label_bound", C.c_uint32), ("edge_capacity", C.c_uint64),
         ("z_begin", C.c_int), ("z_end", C.c_int), ("halo_lo", C.c_int), ("halo_hi", C.c_int),
         ("stream", C.c_void_p),
+        ("use_hist_feat", C.c_int), ("use_median_feat", C.c_int),
     ]
 
 
@@ -147,10 +148,12 @@ class FeatureConfig:
     --ns, --logs, --simpf).  Each image entry: (array-or-device-address, bins, lo, hi)."""
 
     def __init__(self, rimgs=(), rlimgs=(), bimgs=(), thr=(0.2, 0.5, 0.8), normalize=False,
-                 use_log=False, simple=False):
+                 use_log=False, simple=False, use_hist=False, use_median=False):
         self.rimgs, self.rlimgs, self.bimgs = list(rimgs), list(rlimgs), list(bimgs)
         self.thr = list(thr)
         self.normalize, self.use_log, self.simple = normalize, use_log, simple
+        # the reference's GLIA_USE_HISTOGRAM_AS_FEATS / GLIA_USE_MEDIAN_AS_FEATS builds (CMakeLists.txt:53-64)
+        self.use_hist, self.use_median = use_hist, use_median
 
 
 def default_config(pb, **kw):
@@ -296,6 +299,7 @@ class MergeTreeBuilder:
         for i, t in enumerate(cfg.thr):
             p.thr[i] = t
         p.normalize, p.use_log, p.simple = int(cfg.normalize), int(cfg.use_log), int(cfg.simple)
+        p.use_hist_feat, p.use_median_feat = int(getattr(cfg, "use_hist", False)), int(getattr(cfg, "use_median", False))
         p.device_pointers, p.device = int(device_pointers), device
         p.label_bound, p.edge_capacity = label_bound, edge_capacity
         if slab is not None:

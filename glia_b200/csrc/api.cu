@@ -127,6 +127,7 @@ extern "C" int glia_b200_create(const glia_params* p, glia_handle** out) {
   F.normArea = p->normalize ? vol : 1.0;
   F.normLen = p->normalize ? sqrt(diag) : 1.0;
   F.useLog = p->use_log; F.simple = p->simple;
+  F.hist = p->use_hist_feat != 0; F.median = p->use_median_feat != 0;
   {  // log2 of small counts (entropy terms, featurize.cuh)
     std::vector<double> tab(4096);
     tab[0] = 0.0;
@@ -187,11 +188,7 @@ extern "C" const char* glia_b200_last_error(const glia_handle* h) { return h ? h
 
 extern "C" int glia_b200_row_dim(const glia_handle* h, int with_sal) {
   if (!h) return -1;
-  const glia_params& c = h->prm;
-  if (c.simple) return 5 + c.n_bimg + 4 * c.n_rimg + 2 * c.n_rlimg;
-  int x0 = 11 + 4 * c.n_thr + 7 * c.n_rimg + 3 * c.n_rlimg + 5 * c.n_bimg + (with_sal ? 2 : 0);
-  int xi = c.ndim + 4 + 2 * c.n_thr + 5 * c.n_rimg + c.n_rlimg + 5 * c.n_bimg + (with_sal ? 1 : 0);
-  return x0 + 3 * xi;
+  return h->fc.rowLen(with_sal);
 }
 
 extern "C" int glia_b200_counts(const glia_handle* h, int64_t* R, int64_t* E, int64_t* C) {

@@ -100,7 +100,7 @@ GraphView glia_graph_view(const glia_handle* h) {
 // per-region x1 / x2 blocks (once per build; the candidates of a region copy them)
 int glia_region_blocks_device(glia_handle* h, int* xiOut) {
   const glia_params& c = h->prm;
-  const int xi = c.ndim + 4 + 2 * c.n_thr + 5 * c.n_rimg + c.n_rlimg + 5 * c.n_bimg;
+  const int xi = h->fc.xiLen();
   if (xiOut) *xiOut = xi;
   if (h->R == 0) return GLIA_OK;
   GraphView G = glia_graph_view(h);
@@ -119,7 +119,7 @@ int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows) {
   const glia_params& c = h->prm;
   // orientation bits of equal-area pairs are only valid for the build they were installed after
   const unsigned char* orient = (h->hasOrient && h->orientC == h->C) ? h->orient.as<unsigned char>() : nullptr;
-  const int xi = c.ndim + 4 + 2 * c.n_thr + 5 * c.n_rimg + c.n_rlimg + 5 * c.n_bimg;
+  const int xi = h->fc.xiLen();
   if (h->fc.simple || !dRows) {
     init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, orient, dKeys, dRows);
   } else {

@@ -46,7 +46,7 @@ struct RecBoundaryZ {
   __device__ double f64(int i) const { return f[i]; }
 };
 
-struct ImgFeat { double entropy, mean, stddev, mn, mx; };
+struct ImgFeat { double entropy, mean, stddev, mn, mx, median; };
 
 // util/image_stats.hxx:39-53 (normalise by n), util/stats.hxx:145-152, type/feat.hxx:706-738
 // log2 of a voxel count: table (host log2, FeatCfg::log2tab) for counts below GLIA_LOG2_TAB, else computed
@@ -57,7 +57,10 @@ __device__ __forceinline__ double log2_count(const double* __restrict__ tab, uin
 
 template <class Rec>
 __device__ void img_feat(const double* __restrict__ l2tab, const Rec& r, uint32_t n, int bins, int addOff, int maxOff,
-                         int f64Off, ImgFeat& o) {
+                         int f64Off, ImgFeat& o, double* histOut = nullptr) {
+  // histOut: the normalised histogram itself (GLIA_USE_HISTOGRAM_AS_FEATS, type/feat.hxx:608-626; util/stats.hxx:125-131)
+  if (histOut) for (int i = 0; i < bins; ++i) histOut[i] = n ? r.add(addOff + i) / (double)n : 0.0;
+  o.median = 0.0;
   // stats::entropy (util/stats.hxx:145-152): - sum p log2 p over bins with |p| >= FEPS, p = c / n.  log2 p is taken as
   // log2 c - log2 n from the count table (the FP64 log2 and the division per bin were ~60 % of the featurise kernels);
   // a bin holding all n voxels contributes exactly 0 as in the reference.  Agreement with the reference's
@@ -125,9 +128,22 @@ __device__ void shape_feat(const FeatCfg& F, const RR& reg, const RB& bnd, Shape
   }
 }
 
+// Serialises ImageFeats = ImageLabelFeats + ImageRealFeats (type/feat.hxx:826-840): [bins] entropy [median] mean stddev
+// min max; `real` false = ImageLabelFeats alone.
+__device__ __forceinline__ double* push_img(const FeatCfg& F, const ImgFeat& g, bool real, double* p) {
+  *p++ = g.entropy;
+  if (!real) return p;
+  if (F.median) *p++ = g.median;
+  *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
+  return p;
+}
+
+// rm / bm: medians of the region images / boundary images of THIS region (element i at rm[i * rmStride]); read only
+// when F.median.
 template <class RR, class RB>
 __device__ double* push_region(const FeatCfg& F, const ShapeFeat& s, const RR& reg, const RB& bnd,
-                               const double* sal, double* p) {
+                               const double* sal, double* p, const double* rm = nullptr, int rmStride = 0,
+                               const double* bm = nullptr, int bmStride = 0) {
   const int lg = F.useLog;
   *p++ = lg ? slog(s.area, 0) : s.area;
   *p++ = lg ? slog(s.perim, 0) : s.perim;
@@ -138,16 +154,21 @@ __device__ double* push_region(const FeatCfg& F, const ShapeFeat& s, const RR& r
   for (int t = 0; t < F.nThr; ++t) *p++ = s.rValidPerims[t];
   ImgFeat g;
   for (int i = 0; i < F.nR; ++i) {
-    img_feat(F.log2tab, reg, s.nReg, F.rBins[i], F.rAdd[i], F.rMax[i], F.rF64[i], g);
-    *p++ = g.entropy; *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
+    img_feat(F.log2tab, reg, s.nReg, F.rBins[i], F.rAdd[i], F.rMax[i], F.rF64[i], g, F.hist ? p : nullptr);
+    if (F.hist) p += F.rBins[i];
+    if (F.median && rm) g.median = rm[i * rmStride];
+    p = push_img(F, g, true, p);
   }
   for (int i = 0; i < F.nRL; ++i) {
-    img_feat(F.log2tab, reg, s.nReg, F.rlBins[i], F.rlAdd[i], -1, 0, g);
-    *p++ = g.entropy;
+    img_feat(F.log2tab, reg, s.nReg, F.rlBins[i], F.rlAdd[i], -1, 0, g, F.hist ? p : nullptr);
+    if (F.hist) p += F.rlBins[i];
+    p = push_img(F, g, false, p);
   }
   for (int i = 0; i < F.nB; ++i) {
-    img_feat(F.log2tab, bnd, s.nBnd, F.bBins[i], F.bAdd[i], F.bMax[i], F.bF64[i], g);
-    *p++ = g.entropy; *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
+    img_feat(F.log2tab, bnd, s.nBnd, F.bBins[i], F.bAdd[i], F.bMax[i], F.bF64[i], g, F.hist ? p : nullptr);
+    if (F.hist) p += F.bBins[i];
+    if (F.median && bm) g.median = bm[i * bmStride];
+    p = push_img(F, g, true, p);
   }
   if (sal) *p++ = *sal;
   return p;
@@ -158,7 +179,10 @@ __device__ double* push_region(const FeatCfg& F, const ShapeFeat& s, const RR& r
 template <class RX, class RY, class RZ, class BX, class BY, class BZ, class PB>
 __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, const RZ& rz,
                               const BX& bx, const BY& by, const BZ& bz, const PB& pb,
-                              const double* sal, double* out, int part = -1, bool tieSwap = false) {
+                              const double* sal, double* out, int part = -1, bool tieSwap = false,
+                              const double* med = nullptr) {
+  // med (F.median): medians of this row's seven voxel sets, [3 * i + w] for region image i of w = X, Y, Z and
+  // [3 * nR + 4 * j + w] for boundary image j of w = boundary-of X, Y, Z and the pair boundary (median.cu).
   // tieSwap: for EQUAL areas the reference keeps the call order; the caller says whether the reference's
   // call order was (Y, X) (orient.cu) - only the x1 / x2 blocks depend on it.
   // part: -1 = whole row; 0 = x0 (pair terms), 1 / 2 = first / second region block, 3 = merged block.
@@ -170,12 +194,14 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
   if (part > 0) {
     if (F.simple) return;
     const bool sw = sx.area > sy.area || (tieSwap && sx.area == sy.area);
-    const int xi = F.D + 4 + 2 * F.nThr + 5 * F.nR + F.nRL + 5 * F.nB + (sal ? 1 : 0);
+    const int xi = F.xiLen() + (sal ? 1 : 0);
     const int x0len = F.dim + (sal ? 5 : 0) - 3 * xi;
     double* q = out + x0len + (size_t)(part - 1) * xi;
-    if (part == 1) { if (sw) push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, q); else push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, q); }
-    else if (part == 2) { if (sw) push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, q); else push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, q); }
-    else push_region(F, sz, rz, bz, sal ? sal + 2 : nullptr, q);
+    const double* mb = med ? med + 3 * F.nR : nullptr;
+    const bool first = (part == 1) != sw;  // X is written by part 1 unless swapped
+    if (part == 3) push_region(F, sz, rz, bz, sal ? sal + 2 : nullptr, q, med ? med + 2 : nullptr, 3, mb ? mb + 2 : nullptr, 4);
+    else if (first) push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, q, med, 3, mb, 4);
+    else push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, q, med ? med + 1 : nullptr, 3, mb ? mb + 1 : nullptr, 4);
     return;
   }
   const bool swp = sx.area > sy.area || (tieSwap && sx.area == sy.area);
@@ -196,6 +222,7 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
     for (int k = 0; k < F.nB; ++k) {
       img_feat(F.log2tab, pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g);
       *p++ = g.mean;
+      if (F.median) *p++ = med ? med[3 * F.nR + 4 * k + 3] : 0.0;  // bc_feat.hxx:265-267
     }
     for (int i = 0; i < F.nR; ++i) {
       double l1, x2;
@@ -234,7 +261,9 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
     img_feat(F.log2tab, ry, sy.nReg, F.rBins[i], F.rAdd[i], F.rMax[i], F.rF64[i], g2);
     hist_dists(rx, sx.nReg, ry, sy.nReg, F.rBins[i], F.rAdd[i], l1, x2);  // symmetric in (X,Y)
     *p++ = l1; *p++ = x2;
-    *p++ = fabs(g1.entropy - g2.entropy); *p++ = fabs(g1.mean - g2.mean);
+    *p++ = fabs(g1.entropy - g2.entropy);
+    if (F.median) *p++ = med ? fabs(med[3 * i] - med[3 * i + 1]) : 0.0;  // type/feat.hxx:803-805
+    *p++ = fabs(g1.mean - g2.mean);
     *p++ = fabs(g1.stddev - g2.stddev); *p++ = fabs(g1.mn - g2.mn); *p++ = fabs(g1.mx - g2.mx);
   }
   for (int i = 0; i < F.nRL; ++i) {
@@ -245,8 +274,10 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
     *p++ = l1; *p++ = x2; *p++ = fabs(g1.entropy - g2.entropy);
   }
   for (int k = 0; k < F.nB; ++k) {
-    img_feat(F.log2tab, pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g);
-    *p++ = g.entropy; *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
+    img_feat(F.log2tab, pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g, F.hist ? p : nullptr);
+    if (F.hist) p += F.bBins[k];
+    if (F.median && med) g.median = med[3 * F.nR + 4 * k + 3];
+    p = push_img(F, g, true, p);
   }
   if (sal) {  // bc_feat.hxx:208-213; sal = {X, Y, Z}
     double s1v = swp ? sal[1] : sal[0], s2v = swp ? sal[0] : sal[1];
@@ -255,14 +286,15 @@ __device__ void featurize_row(const FeatCfg& F, const RX& rx, const RY& ry, cons
     *p++ = d02 < d12 ? d12 : d02;
   }
   if (part == 0) return;
+  const double* mb = med ? med + 3 * F.nR : nullptr;
   if (swp) {
-    p = push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, p);
-    p = push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, p);
+    p = push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, p, med ? med + 1 : nullptr, 3, mb ? mb + 1 : nullptr, 4);
+    p = push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, p, med, 3, mb, 4);
   } else {
-    p = push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, p);
-    p = push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, p);
+    p = push_region(F, sx, rx, bx, sal ? sal + 0 : nullptr, p, med, 3, mb, 4);
+    p = push_region(F, sy, ry, by, sal ? sal + 1 : nullptr, p, med ? med + 1 : nullptr, 3, mb ? mb + 1 : nullptr, 4);
   }
-  push_region(F, sz, rz, bz, sal ? sal + 2 : nullptr, p);
+  push_region(F, sz, rz, bz, sal ? sal + 2 : nullptr, p, med ? med + 2 : nullptr, 3, mb ? mb + 2 : nullptr, 4);
 }
 
 }  // namespace glia

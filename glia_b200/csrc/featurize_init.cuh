@@ -21,7 +21,9 @@ struct GraphView {
 __device__ __forceinline__ void candidate_row_from_blocks(const FeatCfg& F, const GraphView& G, int xi,
                                                           const double* __restrict__ blk,
                                                           const unsigned char* __restrict__ orient, long long c,
-                                                          double* out, int parts) {
+                                                          double* out, int parts, const double* __restrict__ medC = nullptr) {
+  // medC (F.median): this candidate's medians [Z region per region image][boundary-of Z per boundary image][pair
+  // boundary per boundary image] (median.cu); those of X and Y are already inside their blocks.
   const int e = G.cand[c], rv = G.rev[e];
   const int a = G.ea[e], b = G.eb[e];
   const RecLayout LR = F.reg, LE = F.edge;
@@ -63,24 +65,30 @@ __device__ __forceinline__ void candidate_row_from_blocks(const FeatCfg& F, cons
     for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], bl, 0.0);
     for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], p1, 0.0);
     for (int t = 0; t < T; ++t) *p++ = sdivide(vbl[t], p2, 0.0);
-    const int off0 = 4 + F.D + 2 * T;  // first image feature inside a block
+    int off = 4 + F.D + 2 * T;  // first image feature inside a block
+    const int nreal = 1 + F.lenReal();  // entropy, [median], mean, stddev, min, max
     for (int i = 0; i < F.nR; ++i) {
       double l1, x2;
-      const double* g1 = A + off0 + 5 * i;
-      const double* g2 = B + off0 + 5 * i;
+      const double* g1 = A + off + (F.hist ? F.rBins[i] : 0);
+      const double* g2 = B + off + (F.hist ? F.rBins[i] : 0);
       hist_dists(rx, nX, ry, nY, F.rBins[i], F.rAdd[i], l1, x2);
       *p++ = l1; *p++ = x2;
-      for (int k = 0; k < 5; ++k) *p++ = fabs(g1[k] - g2[k]);  // entropy, mean, stddev, min, max
+      for (int k = 0; k < nreal; ++k) *p++ = fabs(g1[k] - g2[k]);
+      off += F.lenR(i);
     }
     for (int i = 0; i < F.nRL; ++i) {
       double l1, x2;
       hist_dists(rx, nX, ry, nY, F.rlBins[i], F.rlAdd[i], l1, x2);
-      *p++ = l1; *p++ = x2; *p++ = fabs(A[off0 + 5 * F.nR + i] - B[off0 + 5 * F.nR + i]);
+      const int eo = off + (F.hist ? F.rlBins[i] : 0);
+      *p++ = l1; *p++ = x2; *p++ = fabs(A[eo] - B[eo]);
+      off += F.lenRL(i);
     }
     ImgFeat g;
     for (int k = 0; k < F.nB; ++k) {
-      img_feat(F.log2tab, pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g);
-      *p++ = g.entropy; *p++ = g.mean; *p++ = g.stddev; *p++ = g.mn; *p++ = g.mx;
+      img_feat(F.log2tab, pb, nb, F.bBins[k], F.bAdd[k], F.bMax[k], F.bF64[k], g, F.hist ? p : nullptr);
+      if (F.hist) p += F.bBins[k];
+      if (F.median && medC) g.median = medC[F.nR + F.nB + k];
+      p = push_img(F, g, true, p);
     }
     for (int k = 0; k < xi; ++k) out[x0len + k] = B1[k];
   }
@@ -116,7 +124,7 @@ __device__ __forceinline__ void candidate_row_from_blocks(const FeatCfg& F, cons
     }
     ShapeFeat sz;
     shape_feat(F, rz, bz, sz);
-    push_region(F, sz, rz, bz, nullptr, out + x0len + 2 * xi);
+    push_region(F, sz, rz, bz, nullptr, out + x0len + 2 * xi, medC, 1, medC ? medC + F.nR : nullptr, 1);
   }
 }
 

@@ -34,8 +34,33 @@ struct FeatCfg {
   RecLayout reg, edge;
   double normArea, normLen;
   int useLog, simple;
+  int hist, median;  // GLIA_USE_HISTOGRAM_AS_FEATS / GLIA_USE_MEDIAN_AS_FEATS of the reference build, as run-time fields
   int dim;           // row length without saliency terms
   const double* log2tab;  // device table: log2 of the counts 0 .. 4095 (featurize.cuh)
+  // serialised lengths (type/feat.hxx:608-626, :677-700, :826-840): ImageLabelFeats = [bins] + entropy,
+  // ImageRealFeats = [median] + mean, stddev, min, max
+  __host__ __device__ int lenReal() const { return median ? 5 : 4; }
+  __host__ __device__ int lenLabel(int bins) const { return (hist ? bins : 0) + 1; }
+  __host__ __device__ int lenR(int i) const { return lenLabel(rBins[i]) + lenReal(); }
+  __host__ __device__ int lenRL(int i) const { return lenLabel(rlBins[i]); }
+  __host__ __device__ int lenB(int i) const { return lenLabel(bBins[i]) + lenReal(); }
+  __host__ __device__ int xiLen() const {  // one region block (x1 / x2 / x3) without its saliency
+    int n = D + 4 + 2 * nThr;
+    for (int i = 0; i < nR; ++i) n += lenR(i);
+    for (int i = 0; i < nRL; ++i) n += lenRL(i);
+    for (int i = 0; i < nB; ++i) n += lenB(i);
+    return n;
+  }
+  __host__ __device__ int x0Len() const {  // pair terms without saliency
+    int n = 11 + 4 * nThr + nR * (3 + lenReal()) + 3 * nRL;
+    for (int i = 0; i < nB; ++i) n += lenB(i);
+    return n;
+  }
+  __host__ __device__ int rowLen(int withSal) const {
+    if (simple) return 5 + nB * (median ? 2 : 1) + 4 * nR + 2 * nRL;
+    return x0Len() + 3 * xiLen() + (withSal ? 5 : 0);
+  }
+  __host__ __device__ int nMed() const { return median ? 3 * nR + 4 * nB : 0; }  // medians of one row (featurize.cuh)
 };
 
 }  // namespace glia

@@ -80,6 +80,14 @@ typedef struct glia_params {
    * planes supply neighbour labels/mask.  z_end == 0 means the whole volume (no slab). */
   int z_begin, z_end, halo_lo, halo_hi;
   void* stream; /* cudaStream_t to run on (NULL = a private stream) */
+  /* The reference's two compile-time feature layouts (CMakeLists.txt:53-64) as run-time fields:
+   * use_hist_feat   = GLIA_USE_HISTOGRAM_AS_FEATS: every ImageLabelFeats block is [histogram bins] + entropy
+   *                   (type/feat.hxx:608-626);
+   * use_median_feat = GLIA_USE_MEDIAN_AS_FEATS: every ImageRealFeats block is median, mean, stddev, min, max, the
+   *                   difference blocks gain |median difference| (type/feat.hxx:677-700, :772-810) and --simpf
+   *                   rows the pair boundary's median (hmt/bc_feat.hxx:252-268).  median = the n/2-th order
+   *                   statistic (util/stats.hxx:83-91).  Needs the whole volume in one handle (no z-slab). */
+  int use_hist_feat, use_median_feat;
 } glia_params;
 
 typedef struct glia_handle glia_handle;

@@ -46,10 +46,24 @@ struct go_state {
   int* row;                 /* CSR by a: [R+1] */
   /* incoming edge lists (for non-mutual lookups): in_row [R+1], in_e */
   double normArea, normLen;
+  /* GLIA_USE_MEDIAN_AS_FEATS: the values themselves, per base region / per directed base edge */
+  float** rvals[GO_MAX_IMG]; /* [R] -> cnt[r] values */
+  float** evals[GO_MAX_IMG]; /* [E] -> ecnt[e] values */
   /* scratch */
   int* mark; int stamp;
   int* mark2;
 };
+
+/* growing value list of a voxel set (median variant) */
+typedef struct { float* v; size_t n, cap; } vlist;
+static void vl_add(vlist* l, const float* src, size_t n) {
+  if (l->n + n > l->cap) { l->cap = 2 * (l->n + n) + 16; l->v = (float*)realloc(l->v, 4 * l->cap); }
+  memcpy(l->v + l->n, src, 4 * n); l->n += n;
+}
+static int cmp_f32(const void* a, const void* b) {
+  float x = *(const float*)a, y = *(const float*)b;
+  return x < y ? -1 : x > y;
+}
 
 static void stat_init(stat_t* s, int bins) {
   s->n = 0; s->s = s->s2 = 0; s->mn = DBL_MAX; s->mx = -DBL_MAX;
@@ -238,6 +252,30 @@ go_state* go_build(const go_cfg* cfg, const uint32_t* L, const uint32_t* M, cons
     for (int t = 0; t < T; ++t) if ((double)pb[p] >= cfg->thr[t]) s->ethr[(size_t)e * T + t]++; /* feat.hxx:498 */
     for (int i = 0; i < cfg->n_bimg; ++i) stat_add(&s->estat[i][e], &s->bs[i], s->bs[i].img[p]);
   }
+  if (cfg->use_median) { /* type/feat.hxx:711-724: the values of every point of the set */
+    size_t* cur = (size_t*)calloc((size_t)(R > E ? R : E) + 1, sizeof(size_t));
+    for (int i = 0; i < cfg->n_rimg; ++i) {
+      s->rvals[i] = (float**)calloc((size_t)R + 1, sizeof(float*));
+      for (int r = 0; r < R; ++r) s->rvals[i][r] = (float*)malloc(4 * (size_t)(s->cnt[r] ? s->cnt[r] : 1));
+      memset(cur, 0, sizeof(size_t) * ((size_t)R + 1));
+      for (p = 0; p < N; ++p) {
+        if (M && M[p] == 0) continue;
+        int a = find_u32(s->label, R, L[p]);
+        s->rvals[i][a][cur[a]++] = s->rs[i].img[p];
+      }
+    }
+    for (int i = 0; i < cfg->n_bimg; ++i) {
+      s->evals[i] = (float**)calloc((size_t)E + 1, sizeof(float*));
+      for (int e = 0; e < E; ++e) s->evals[i][e] = (float*)malloc(4 * (size_t)(s->ecnt[e] ? s->ecnt[e] : 1));
+      memset(cur, 0, sizeof(size_t) * ((size_t)E + 1));
+      for (p = 0; p < N; ++p) {
+        if (!cls[p]) continue;
+        int e = find_u64(keys, E, vkey[p]);
+        s->evals[i][e][cur[e]++] = s->bs[i].img[p];
+      }
+    }
+    free(cur);
+  }
   free(keys); free(vkey); free(cls);
   s->mark = (int*)calloc((size_t)R + 1, 4);
   s->mark2 = (int*)calloc((size_t)R + 1, 4);
@@ -253,6 +291,8 @@ static void stat_free_arr(stat_t* a, int n) {
 void go_free(go_state* s) {
   if (!s) return;
   for (int i = 0; i < GO_MAX_IMG; ++i) {
+    if (s->rvals[i]) { for (int r = 0; r < s->R; ++r) free(s->rvals[i][r]); free(s->rvals[i]); }
+    if (s->evals[i]) { for (int e = 0; e < s->E; ++e) free(s->evals[i][e]); free(s->evals[i]); }
     stat_free_arr(s->rstat[i], s->R); stat_free_arr(s->rlstat[i], s->R); stat_free_arr(s->estat[i], s->E);
     free(s->rs[i].bounds); free(s->rls[i].bounds); free(s->bs[i].bounds);
   }
@@ -307,9 +347,26 @@ void go_get_edge_stats(const go_state* s, int i, uint32_t* hist, double* sum, do
  * type/feat.hxx:71-90, :485-502, :632-638, :706-738; hmt/bc_feat.hxx:88-127).
  * ---------------------------------------------------------------------- */
 typedef struct {
-  double entropy, mean, stddev, mn, mx;
+  double entropy, mean, stddev, mn, mx, median;
   double hist[256];
 } imgfeat;
+
+/* ImageRealFeats::generate under GLIA_USE_MEDIAN_AS_FEATS (type/feat.hxx:711-724): amedian = the n/2-th order
+ * statistic (util/stats.hxx:83-91), mean = sum / n in double (:57-59), var = two-pass sum of squared deviations / n
+ * (:62-71).  Consumes (sorts) the list. */
+static void real_feats_from_values(imgfeat* f, vlist* l) {
+  f->median = 0.0;
+  if (l->n == 0) return; /* generate() returns before touching anything */
+  double sum = 0.0;
+  for (size_t i = 0; i < l->n; ++i) sum += l->v[i];
+  f->mean = sdivide(sum, (double)l->n, 0.0);
+  double var = 0.0;
+  for (size_t i = 0; i < l->n; ++i) { double dx = l->v[i] - f->mean; var += dx * dx; }
+  f->stddev = ssqrt(sdivide(var, (double)l->n, 0.0), 0.0);
+  qsort(l->v, l->n, 4, cmp_f32);
+  f->mn = l->v[0]; f->mx = l->v[l->n - 1];
+  f->median = l->v[l->n / 2];
+}
 
 typedef struct {
   double area, perim, compactness, bboxArea, bboxSize[3];
@@ -325,6 +382,7 @@ static void img_feats(imgfeat* f, const stat_t* st, int bins) {
   for (int i = 0; i < bins; ++i) f->hist[i] = n ? st->hist[i] / (double)n : 0.0;
   for (int i = 0; i < bins; ++i)
     if (!(fabs(f->hist[i] - 0.0) < FEPS)) f->entropy -= f->hist[i] * log2(f->hist[i]);
+  f->median = 0.0;
   if (n == 0) { f->mean = f->stddev = f->mn = f->mx = 0.0; return; }
   int ni = (int)n;
   f->mean = st->s / ni;
@@ -384,6 +442,12 @@ static void region_feats(go_state* s, const int* S, int n, regfeat* f, const dou
     stat_t* t = tmp_stat(s->rs[i].bins);
     for (int j = 0; j < n; ++j) stat_merge(t, &s->rstat[i][S[j]], s->rs[i].bins);
     img_feats(&f->region[i], t, s->rs[i].bins);
+    if (c->use_median) {
+      vlist l = {0, 0, 0};
+      for (int j = 0; j < n; ++j) vl_add(&l, s->rvals[i][S[j]], s->cnt[S[j]]);
+      real_feats_from_values(&f->region[i], &l);
+      free(l.v);
+    }
   }
   for (int i = 0; i < c->n_rlimg; ++i) {
     stat_t* t = tmp_stat(s->rls[i].bins);
@@ -396,6 +460,14 @@ static void region_feats(go_state* s, const int* S, int n, regfeat* f, const dou
       for (int e = s->row[S[j]]; e < s->row[S[j] + 1]; ++e)
         if (LIVE(s, e, s->mark, st)) stat_merge(t, &s->estat[i][e], s->bs[i].bins);
     img_feats(&f->boundary[i], t, s->bs[i].bins);
+    if (c->use_median) {
+      vlist l = {0, 0, 0};
+      for (int j = 0; j < n; ++j)
+        for (int e = s->row[S[j]]; e < s->row[S[j] + 1]; ++e)
+          if (LIVE(s, e, s->mark, st)) vl_add(&l, s->evals[i][e], s->ecnt[e]);
+      real_feats_from_values(&f->boundary[i], &l);
+      free(l.v);
+    }
   }
   f->has_sal = sal != NULL;
   f->sal = sal ? *sal : 0.0;
@@ -411,6 +483,17 @@ static double dist_x2(const double* a, const double* b, int n) {
   return r;
 }
 
+/* ImageFeats::serialize = ImageLabelFeats ([histogram] entropy, type/feat.hxx:616-623) then ImageRealFeats
+ * ([median] mean stddev min max, :684-694); real = 0: ImageLabelFeats alone. */
+static double* push_img(const go_cfg* c, const imgfeat* g, int bins, int real, double* p) {
+  if (c->use_hist) for (int b = 0; b < bins; ++b) *p++ = g->hist[b];
+  *p++ = g->entropy;
+  if (!real) return p;
+  if (c->use_median) *p++ = g->median;
+  *p++ = g->mean; *p++ = g->stddev; *p++ = g->mn; *p++ = g->mx;
+  return p;
+}
+
 static void push_region(const go_state* s, const regfeat* f, double** o) {
   const go_cfg* c = &s->cfg;
   int lg = c->use_log;
@@ -422,24 +505,22 @@ static void push_region(const go_state* s, const regfeat* f, double** o) {
   for (int d = 0; d < s->D; ++d) *p++ = lg ? slog(f->bboxSize[d], 0) : f->bboxSize[d];
   for (int t = 0; t < c->n_thr; ++t) *p++ = lg ? slog(f->validPerims[t], 0) : f->validPerims[t];
   for (int t = 0; t < c->n_thr; ++t) *p++ = f->rValidPerims[t];
-  for (int i = 0; i < c->n_rimg; ++i) {
-    const imgfeat* g = &f->region[i];
-    *p++ = g->entropy; *p++ = g->mean; *p++ = g->stddev; *p++ = g->mn; *p++ = g->mx;
-  }
-  for (int i = 0; i < c->n_rlimg; ++i) *p++ = f->labelRegion[i].entropy;
-  for (int i = 0; i < c->n_bimg; ++i) {
-    const imgfeat* g = &f->boundary[i];
-    *p++ = g->entropy; *p++ = g->mean; *p++ = g->stddev; *p++ = g->mn; *p++ = g->mx;
-  }
+  for (int i = 0; i < c->n_rimg; ++i) p = push_img(c, &f->region[i], s->rs[i].bins, 1, p);
+  for (int i = 0; i < c->n_rlimg; ++i) p = push_img(c, &f->labelRegion[i], s->rls[i].bins, 0, p);
+  for (int i = 0; i < c->n_bimg; ++i) p = push_img(c, &f->boundary[i], s->bs[i].bins, 1, p);
   if (f->has_sal) *p++ = f->sal;
   *o = p;
 }
 
 int go_row_dim(const go_state* s, int with_sal) {
   const go_cfg* c = &s->cfg;
-  if (c->simple) return 5 + c->n_bimg + 4 * c->n_rimg + 2 * c->n_rlimg;
-  int x0 = 11 + 4 * c->n_thr + 7 * c->n_rimg + 3 * c->n_rlimg + 5 * c->n_bimg + (with_sal ? 2 : 0);
-  int xi = s->D + 4 + 2 * c->n_thr + 5 * c->n_rimg + c->n_rlimg + 5 * c->n_bimg + (with_sal ? 1 : 0);
+  int real = c->use_median ? 5 : 4;
+  if (c->simple) return 5 + c->n_bimg * (c->use_median ? 2 : 1) + 4 * c->n_rimg + 2 * c->n_rlimg;
+  int x0 = 11 + 4 * c->n_thr + (3 + real) * c->n_rimg + 3 * c->n_rlimg + (with_sal ? 2 : 0);
+  int xi = s->D + 4 + 2 * c->n_thr + (with_sal ? 1 : 0);
+  for (int i = 0; i < c->n_rimg; ++i) xi += (c->use_hist ? s->rs[i].bins : 0) + 1 + real;
+  for (int i = 0; i < c->n_rlimg; ++i) xi += (c->use_hist ? s->rls[i].bins : 0) + 1;
+  for (int i = 0; i < c->n_bimg; ++i) { int l = (c->use_hist ? s->bs[i].bins : 0) + 1 + real; xi += l; x0 += l; }
   return x0 + 3 * xi;
 }
 
@@ -460,6 +541,8 @@ static void candidate_row(go_state* s, const int* X, int nx, const int* Y, int n
   /* (computed on the fly: small sets) */
   uint64_t nb = 0, vp[GO_MAX_THR] = {0};
   stat_t bst[GO_MAX_IMG];
+  vlist bvl[GO_MAX_IMG];
+  memset(bvl, 0, sizeof(bvl));
   for (int i = 0; i < c->n_bimg; ++i) stat_init(&bst[i], s->bs[i].bins);
   for (int side = 0; side < 2; ++side) {
     const int* A = side ? Y : X; int na = side ? ny : nx;
@@ -477,6 +560,7 @@ static void candidate_row(go_state* s, const int* X, int nx, const int* Y, int n
         nb += s->ecnt[e];
         for (int t = 0; t < T; ++t) vp[t] += s->ethr[(size_t)e * T + t];
         for (int k = 0; k < c->n_bimg; ++k) stat_merge(&bst[k], &s->estat[k][e], s->bs[k].bins);
+        if (c->use_median) for (int k = 0; k < c->n_bimg; ++k) vl_add(&bvl[k], s->evals[k][e], s->ecnt[e]);
       }
     }
   }
@@ -484,14 +568,17 @@ static void candidate_row(go_state* s, const int* X, int nx, const int* Y, int n
   double areaDiff = fabs(f1->area - f2->area), perimDiff = fabs(f1->perim - f2->perim);
   double bl = sdivide(ceil((uint32_t)nb / 2.0), s->normLen, 0.0);
   imgfeat bf[GO_MAX_IMG];
-  for (int k = 0; k < c->n_bimg; ++k) { img_feats(&bf[k], &bst[k], s->bs[k].bins); free(bst[k].hist); }
+  for (int k = 0; k < c->n_bimg; ++k) {
+    img_feats(&bf[k], &bst[k], s->bs[k].bins); free(bst[k].hist);
+    if (c->use_median) { real_feats_from_values(&bf[k], &bvl[k]); free(bvl[k].v); }
+  }
   if (c->simple) { /* bc_feat.hxx:247-279 (log applied before selection) */
     *p++ = lg ? slog(f1->area, 0) : f1->area;
     *p++ = lg ? slog(f2->area, 0) : f2->area;
     *p++ = lg ? slog(f1->perim, 0) : f1->perim;
     *p++ = lg ? slog(f2->perim, 0) : f2->perim;
     *p++ = lg ? slog(bl, 0) : bl;
-    for (int k = 0; k < c->n_bimg; ++k) *p++ = bf[k].mean;
+    for (int k = 0; k < c->n_bimg; ++k) { *p++ = bf[k].mean; if (c->use_median) *p++ = bf[k].median; } /* bc_feat.hxx:263-268 */
     for (int i = 0; i < c->n_rimg; ++i) {
       const imgfeat *a = &f1->region[i], *b = &f2->region[i];
       *p++ = fabs(a->mean - b->mean);
@@ -528,6 +615,7 @@ static void candidate_row(go_state* s, const int* X, int nx, const int* Y, int n
     *p++ = dist_l1(a->hist, b->hist, s->rs[i].bins);
     *p++ = dist_x2(a->hist, b->hist, s->rs[i].bins);
     *p++ = fabs(a->entropy - b->entropy);
+    if (c->use_median) *p++ = fabs(a->median - b->median); /* feat.hxx:803-805 */
     *p++ = fabs(a->mean - b->mean);
     *p++ = fabs(a->stddev - b->stddev);
     *p++ = fabs(a->mn - b->mn);
@@ -539,9 +627,7 @@ static void candidate_row(go_state* s, const int* X, int nx, const int* Y, int n
     *p++ = dist_x2(a->hist, b->hist, s->rls[i].bins);
     *p++ = fabs(a->entropy - b->entropy);
   }
-  for (int k = 0; k < c->n_bimg; ++k) {
-    *p++ = bf[k].entropy; *p++ = bf[k].mean; *p++ = bf[k].stddev; *p++ = bf[k].mn; *p++ = bf[k].mx;
-  }
+  for (int k = 0; k < c->n_bimg; ++k) p = push_img(c, &bf[k], s->bs[k].bins, 1, p);
   if (f1->has_sal && f2->has_sal && fZ->has_sal) { /* bc_feat.hxx:208-213 */
     double d02 = fabs(f1->sal - fZ->sal), d12 = fabs(f2->sal - fZ->sal);
     *p++ = d02 < d12 ? d02 : d12;

@@ -34,6 +34,8 @@ typedef struct go_cfg {
   int normalize;            /* --ns   (main_merge_order_bc.cxx:36-39) */
   int use_log;              /* --logs (main_merge_order_bc.cxx:86-91) */
   int simple;               /* --simpf (bc_feat.hxx:247-279) */
+  int use_hist;             /* GLIA_USE_HISTOGRAM_AS_FEATS build (CMakeLists.txt:58-60; type/feat.hxx:608-626) */
+  int use_median;           /* GLIA_USE_MEDIAN_AS_FEATS build (CMakeLists.txt:62-64; type/feat.hxx:677-810) */
 } go_cfg;
 
 typedef struct go_state go_state;

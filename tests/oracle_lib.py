@@ -29,6 +29,7 @@ class GoCfg(C.Structure):
         ("blo", C.c_double * MAX_IMG), ("bhi", C.c_double * MAX_IMG),
         ("thr", C.c_double * MAX_THR),
         ("normalize", C.c_int), ("use_log", C.c_int), ("simple", C.c_int),
+        ("use_hist", C.c_int), ("use_median", C.c_int),
     ]
 
 
@@ -98,11 +99,13 @@ class FeatureConfig:
     """Mirrors the CLI options of hmt/main_merge_order_bc.cxx:172-242."""
 
     def __init__(self, rimgs=(), rlimgs=(), bimgs=(), thr=(0.2, 0.5, 0.8), normalize=False,
-                 use_log=False, simple=False):
+                 use_log=False, simple=False, use_hist=False, use_median=False):
         # each image entry: (array float32, bins, lo, hi)
         self.rimgs, self.rlimgs, self.bimgs = list(rimgs), list(rlimgs), list(bimgs)
         self.thr = list(thr)
         self.normalize, self.use_log, self.simple = normalize, use_log, simple
+        # the reference's GLIA_USE_HISTOGRAM_AS_FEATS / GLIA_USE_MEDIAN_AS_FEATS builds (CMakeLists.txt:53-64)
+        self.use_hist, self.use_median = use_hist, use_median
 
 
 def default_config(pb, **kw):
@@ -136,6 +139,7 @@ class Oracle:
         for i, t in enumerate(cfg.thr):
             g.thr[i] = t
         g.normalize, g.use_log, g.simple = int(cfg.normalize), int(cfg.use_log), int(cfg.simple)
+        g.use_hist, g.use_median = int(getattr(cfg, "use_hist", False)), int(getattr(cfg, "use_median", False))
         self.g = g
         self.h = lib().go_build(C.byref(g), _ptr(self.labels), _ptr(self.mask), _ptr(self.pb))
         self.R = lib().go_num_regions(self.h)
@@ -275,16 +279,26 @@ class OracleRF:
 
 
 # ---------------------------------------------------------------- reference (oracle/_ref)
-def ref_available(ndim=2):
-    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libglia_ref%dd.so" % ndim))
+def _ref_variant(cfg):
+    """Suffix of the reference build that has cfg's feature layout compiled in."""
+    if cfg is None:
+        return ""
+    v = ("hist" if getattr(cfg, "use_hist", False) else "") + ("median" if getattr(cfg, "use_median", False) else "")
+    return "_" + v if v else ""
+
+
+def ref_available(ndim=2, cfg=None):
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libglia_ref%dd%s.so" % (ndim, _ref_variant(cfg))))
 
 
 _ref = {}
 
 
-def ref_lib(ndim):
+def ref_lib(ndim, cfg=None):
+    key = (ndim, _ref_variant(cfg))
+    ndim_, ndim = ndim, key
     if ndim not in _ref:
-        L = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libglia_ref%dd.so" % ndim))
+        L = C.CDLL(os.path.join(ORACLE_DIR, "_ref", "libglia_ref%dd%s.so" % key))
         L.glia_ref_time.restype = C.c_double
         L.glia_ref_time_leaf_feats.restype = C.c_double
         for n in ("reg_label", "reg_count", "reg_border", "edge_a", "edge_b", "edge_count",
@@ -316,7 +330,7 @@ def ref_run(mode, labels, pb, cfg, mask=None, pred=None, order=None, sal=None, i
     labels = np.ascontiguousarray(labels, np.uint32)
     pb = np.ascontiguousarray(pb, np.float32)
     ndim = labels.ndim
-    L = ref_lib(ndim)
+    L = ref_lib(ndim, cfg)
     dims = (C.c_int * 3)(*(list(labels.shape[::-1]) + [1] * (3 - ndim)))
     keep = []
 

@@ -123,6 +123,81 @@ def test_bc_feat_matches_reference(case):
         assert np.array_equal(rows, ref["merge_rows"])
 
 
+# ---- the reference's optional feature layouts: GLIA_USE_HISTOGRAM_AS_FEATS / GLIA_USE_MEDIAN_AS_FEATS builds
+VARIANTS = [
+    # (shape, nlabels, seed, mask?, normalize, logs, simple, hist, median)
+    ((24, 28), 30, 11, False, False, False, False, True, False),
+    ((27, 19), 16, 12, True, True, True, False, False, True),
+    ((22, 25), 22, 13, False, False, False, True, False, True),
+    ((23, 21), 18, 14, False, False, True, False, True, True),
+    ((9, 10, 11), 14, 15, True, True, False, False, True, True),
+]
+
+
+def _have_variant(nd, cfg):
+    if ol.ref_available(nd, cfg):
+        return True
+    try:
+        ol.build_ref()
+    except Exception:
+        return False
+    return ol.ref_available(nd, cfg)
+
+
+def _variant_cfg(pb, case, two_images=False):
+    shape, nl, seed, um, ns, lg, simp, uh, umed = case
+    kw = dict(normalize=ns, use_log=lg, simple=simp, use_hist=uh, use_median=umed)
+    if not two_images:
+        return ol.default_config(pb, **kw)
+    rng = np.random.default_rng(seed + 7)
+    img2 = (np.floor(rng.random(pb.shape) * 64) / 64).astype(np.float32)
+    return ol.FeatureConfig(rimgs=[(pb, 16, 0.0, 1.0), (img2, 8, 0.0, 1.0)], rlimgs=[(img2, 4, 0.0, 1.0)],
+                            bimgs=[(pb, 16, 0.0, 1.0), (img2, 5, 0.0, 1.0)], **kw)
+
+
+@pytest.mark.parametrize("two", [False, True])
+@pytest.mark.parametrize("case", VARIANTS)
+def test_variant_layouts_match_reference(case, two):
+    """Initial candidates, greedy order and the bc_feat stage under the hist / median builds.  Dyadic pb: every
+    column is bit-identical except the median builds' stddev, which the reference computes two-pass
+    (util/stats.hxx:62-71) from a pixel order the oracle does not keep."""
+    shape, nl, seed, um, ns, lg, simp, uh, umed = case
+    lab, pb, mask = _make(shape, nl, seed, um)
+    cfg = _variant_cfg(pb, case, two)
+    if not _have_variant(len(shape), cfg):
+        pytest.skip("oracle/_ref variant not available")
+    o = ol.Oracle(lab, pb, cfg, mask=mask)
+
+    def same(a, b):
+        assert a.shape == b.shape
+        if umed:
+            np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-14)
+        else:
+            assert np.array_equal(a, b)
+
+    ref = ol.ref_run(1, lab, pb, cfg, mask=mask, pred=quant_pred)
+    rk = ref["cand_keys"]
+    keys, rows = o.init_candidates(swap=(rk[:, 0] > rk[:, 1]).astype(np.uint8))
+    assert np.array_equal(np.sort(rk[:, :2], axis=1), keys)
+    assert rows.shape[1] == ref["dim"] == o.row_dim()
+    same(rows, ref["cand_rows"])
+
+    ref = ol.ref_run(2, lab, pb, cfg, mask=mask, pred=quant_pred)
+    n0 = o.Cn
+    rk = ref["cand_keys"][:n0]
+    ks = np.sort(rk[:, :2], axis=1)
+    perm = np.lexsort((ks[:, 1], ks[:, 0]))
+    res = o.greedy(fn=quant_pred, want_cands=True, init_swap=(rk[perm, 0] > rk[perm, 1]).astype(np.uint8))
+    assert np.array_equal(res["order"], ref["order"])
+    same(res["rows"], ref["merge_rows"])
+    if simp:
+        return
+    for sal in (None, res["sal"]):
+        rb = ol.ref_run(3, lab, pb, cfg, mask=mask, order=res["order"], sal=sal, init_sal=1.0, sal_bias=0.25)
+        rows = o.bc_feat(res["order"], sal=sal, init_sal=1.0, sal_bias=0.25)
+        same(rows, rb["merge_rows"])
+
+
 def test_nondyadic_within_tolerance():
     if not _have_ref(2):
         pytest.skip("oracle/_ref not available")
