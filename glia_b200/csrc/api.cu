@@ -67,6 +67,7 @@ extern "C" int glia_b200_create(const glia_params* p, glia_handle** out) {
   if (p->ndim == 2) { h->KX = p->dims[0]; h->KY = 1; h->KZ = p->dims[1]; }
   else { h->KX = p->dims[0]; h->KY = p->dims[1]; h->KZ = p->dims[2]; }
   int zb = 0, ze = h->KZ, hl = 0, hh = 0;
+  if (p->z_end > 0 && p->use_median_feat) { glia_b200_destroy(h); return GLIA_E_ARG; }  // medians need the whole volume (median.cu)
   if (p->z_end > 0) {
     if (p->ndim != 3 || p->z_begin < 0 || p->z_end > h->KZ || p->z_begin >= p->z_end ||
         p->halo_lo < 0 || p->halo_hi < 0 || (p->z_begin > 0 && p->halo_lo < 1) ||
@@ -151,9 +152,13 @@ extern "C" void glia_b200_destroy(glia_handle* h) {
                           &h->eb, &h->row, &h->rev, &h->cand, &h->bAggAdd, &h->bAggMax, &h->bAggF64,
                           &h->cubTmp, &h->scalars, &h->rows, &h->sal, &h->keysOut, &h->interest,
                           &h->exportBuf, &h->exportCursor, &h->regBlocks, &h->bAggMax2, &h->bAggOwn,
-                          &h->orient, &h->tieBuf, &h->firstVox, &h->log2tab};
+                          &h->orient, &h->tieBuf, &h->firstVox, &h->log2tab, &h->medRStart, &h->medEStart,
+                          &h->medTmpA, &h->medTmpB, &h->medReg, &h->medCand};
   for (auto b : bufs) b->release();
   for (auto& b : h->inImg) b.release();
+  for (auto& b : h->medRKeys) b.release();
+  for (auto& b : h->medEKeys) b.release();
+  for (auto& b : h->medQ) b.release();
   for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);
   if (h->copyStream) { for (int i = 0; i < 4; ++i) cudaEventDestroy(h->evCopy[i]); cudaStreamDestroy(h->copyStream); }
   if (h->ownStream) cudaStreamDestroy(h->stream);

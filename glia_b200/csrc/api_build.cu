@@ -14,6 +14,7 @@ cudaError_t launch_voxel_pass_generic(const VoxParams& P, const VoxChannels& C, 
 cudaError_t launch_label_max(const uint32_t* labels, size_t n, uint32_t* out, cudaStream_t st);
 }  // namespace glia
 int glia_finalize_graph(glia_handle* h);
+int glia_median_build(glia_handle* h);
 int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
 int glia_rf_label_index(const glia_rf* m, int label);
 int glia_rf_score_device(const glia_rf* m, const double* dX, size_t N, int D, int labelIdx,
@@ -316,6 +317,7 @@ extern "C" int glia_b200_build(glia_handle* h, const uint32_t* labels, const uin
   // glia_b200_build_partial + the exchange of shard.cu instead)
   s = glia_finalize_graph(h);
   if (s != GLIA_OK) return s;
+  if (h->prm.use_median_feat && (s = glia_median_build(h)) != GLIA_OK) return s;
   CK(cudaEventRecord(h->ev[2], st));
   CK(cudaStreamSynchronize(st));
   float ms = 0;

@@ -7,12 +7,14 @@
 // and the two directed boundaries a->b, b->a.
 #include "featurize.cuh"
 #include "featurize_init.cuh"
+#include "median.cuh"
 
 namespace glia {
 
 __global__ void __launch_bounds__(128)
 init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G,
-                       const unsigned char* __restrict__ orient, uint32_t* __restrict__ keys, double* __restrict__ rows) {
+                       const unsigned char* __restrict__ orient, uint32_t* __restrict__ keys, double* __restrict__ rows,
+                       const double* __restrict__ medReg, const double* __restrict__ medCand) {
   long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (c >= G.C) return;
   const int e = G.cand[c], rv = G.rev[e];
@@ -41,7 +43,19 @@ init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant_
       for (int i = 0; i < LE.nF64; ++i) bz.f[i] += G.sF64[(size_t)k * LE.nF64 + i];
     }
   }
-  featurize_row(F, rx, ry, rz, bx, by, bz, pb, nullptr, rows + (size_t)c * F.dim, -1, orient && orient[c]);
+  double med[7 * GLIA_MAX_IMG];  // featurize_row's layout, from the per-region and per-candidate medians (median.cu)
+  if (F.median && medReg && medCand) {
+    const double* ma = medReg + (size_t)a * (F.nR + F.nB);
+    const double* mb = medReg + (size_t)b * (F.nR + F.nB);
+    const double* mc = medCand + (size_t)c * (F.nR + 2 * F.nB);
+    for (int i = 0; i < F.nR; ++i) { med[3 * i] = ma[i]; med[3 * i + 1] = mb[i]; med[3 * i + 2] = mc[i]; }
+    for (int j = 0; j < F.nB; ++j) {
+      double* m = med + 3 * F.nR + 4 * j;
+      m[0] = ma[F.nR + j]; m[1] = mb[F.nR + j]; m[2] = mc[F.nR + j]; m[3] = mc[F.nR + F.nB + j];
+    }
+  }
+  featurize_row(F, rx, ry, rz, bx, by, bz, pb, nullptr, rows + (size_t)c * F.dim, -1, orient && orient[c],
+                (F.median && medReg && medCand) ? med : nullptr);
 }
 
 // ---- v2: the x1 / x2 blocks of a row depend on ONE base region only, and each region takes part in
@@ -53,7 +67,7 @@ init_candidates_kernel(const __grid_constant__ FeatCfg F, const __grid_constant_
 // block layout: [0, xi) = push_region output, [xi] = area, [xi+1] = perim (normalised, before --logs)
 __global__ void __launch_bounds__(128)
 region_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G, int xi,
-                     double* __restrict__ blk) {
+                     double* __restrict__ blk, const double* __restrict__ medReg) {
   long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (r >= G.R) return;
   const RecLayout LR = F.reg, LE = F.edge;
@@ -62,7 +76,8 @@ region_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ 
   ShapeFeat s;
   shape_feat(F, rx, bx, s);
   double* o = blk + (size_t)r * (xi + 2);
-  push_region(F, s, rx, bx, nullptr, o);
+  const double* m = medReg ? medReg + (size_t)r * (F.nR + F.nB) : nullptr;
+  push_region(F, s, rx, bx, nullptr, o, m, 1, m ? m + F.nR : nullptr, 1);
   o[xi] = s.area; o[xi + 1] = s.perim;
 }
 
@@ -72,12 +87,13 @@ region_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ 
 __global__ void __launch_bounds__(128)
 init_candidates_blocks_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ GraphView G, int xi,
                               const double* __restrict__ blk, const unsigned char* __restrict__ orient,
-                              uint32_t* __restrict__ keys, double* __restrict__ rows) {
+                              uint32_t* __restrict__ keys, double* __restrict__ rows, const double* __restrict__ medCand) {
   long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (c >= G.C) return;
   if (keys) { const int e = G.cand[c]; keys[2 * c] = G.regLabel[G.ea[e]]; keys[2 * c + 1] = G.regLabel[G.eb[e]]; }
   if (!rows) return;
-  candidate_row_from_blocks(F, G, xi, blk, orient, c, rows + (size_t)c * F.dim, 3);
+  candidate_row_from_blocks(F, G, xi, blk, orient, c, rows + (size_t)c * F.dim, 3,
+                            medCand ? medCand + (size_t)c * (F.nR + 2 * F.nB) : nullptr);
 }
 
 }  // namespace glia
@@ -105,7 +121,8 @@ int glia_region_blocks_device(glia_handle* h, int* xiOut) {
   if (h->R == 0) return GLIA_OK;
   GraphView G = glia_graph_view(h);
   GLIA_CUDA_CHECK(h, h->regBlocks.ensure(8 * (size_t)(h->R + 1) * (xi + 2)));
-  region_blocks_kernel<<<(unsigned)((h->R + 127) / 128), 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>());
+  region_blocks_kernel<<<(unsigned)((h->R + 127) / 128), 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>(),
+                                                                              h->fc.median ? h->medReg.as<double>() : nullptr);
   h->launches++;
   GLIA_CUDA_CHECK(h, cudaGetLastError());
   return GLIA_OK;
@@ -120,12 +137,16 @@ int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows) {
   // orientation bits of equal-area pairs are only valid for the build they were installed after
   const unsigned char* orient = (h->hasOrient && h->orientC == h->C) ? h->orient.as<unsigned char>() : nullptr;
   const int xi = h->fc.xiLen();
+  const bool med = h->fc.median && dRows;
+  if (med) { int st = glia_median_init_candidates(h); if (st != GLIA_OK) return st; }
   if (h->fc.simple || !dRows) {
-    init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, orient, dKeys, dRows);
+    init_candidates_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, orient, dKeys, dRows,
+                                                          med ? h->medReg.as<double>() : nullptr, med ? h->medCand.as<double>() : nullptr);
   } else {
     int st = glia_region_blocks_device(h, nullptr);
     if (st != GLIA_OK) return st;
-    init_candidates_blocks_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>(), orient, dKeys, dRows);
+    init_candidates_blocks_kernel<<<blocks, 128, 0, h->stream>>>(h->fc, G, xi, h->regBlocks.as<double>(), orient, dKeys, dRows,
+                                                                 med ? h->medCand.as<double>() : nullptr);
   }
   h->launches++;
   GLIA_CUDA_CHECK(h, cudaGetLastError());

@@ -147,4 +147,8 @@ struct glia_handle {
   bool hasOrient = false;
   long long orientC = 0;
   glia::DevBuf interest, exportBuf, exportCursor;         // multi-GPU exchange (shard.cu)
+  // median features (median.cu): sorted value keys per base region / directed boundary, per image
+  glia::DevBuf medRKeys[GLIA_MAX_IMG], medEKeys[GLIA_MAX_IMG], medRStart, medEStart, medTmpA, medTmpB;
+  glia::DevBuf medReg, medCand, medQ[6];
+  bool hasMedian = false;
 };

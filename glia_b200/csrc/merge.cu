@@ -19,6 +19,7 @@
 #include <unordered_map>
 #include <vector>
 #include "featurize.cuh"
+#include "median.cuh"
 
 namespace glia {
 
@@ -137,6 +138,7 @@ struct BcFeatView {
   const uint32_t* bAdd; const uint32_t* bMax; const double* bF64;
   const uint32_t* cAdd; const uint32_t* cMax; const double* cF64;
   const uint32_t* nAdd; const uint32_t* nMax; const double* nF64;
+  const double* med; int nMed;         // [n][nMed] medians of the rows' voxel sets (featurize.cuh), or null
 };
 
 __global__ void __launch_bounds__(128)
@@ -153,7 +155,7 @@ bc_feat_rows_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ B
   double sal[3];
   if (V.withSal) { sal[0] = V.nodeSal[x]; sal[1] = V.nodeSal[y]; sal[2] = V.nodeSal[z]; }
   featurize_row(F, R(x), R(y), R(z), B(x), B(y), B(z), pb, V.withSal ? sal : nullptr,
-                rows + (size_t)i * V.dim);
+                rows + (size_t)i * V.dim, -1, false, V.med ? V.med + (size_t)i * V.nMed : nullptr);
 }
 
 }  // namespace glia
@@ -284,7 +286,100 @@ extern "C" int glia_b200_bc_feat(glia_handle* h, const uint32_t* order, int64_t 
         dLevelNodes + levelOff[l], cnt, dC0, dC1, LR, LE, rAdd, rMax, rF64, bAdd, bF64, cAdd, cF64);
     h->launches++;
   }
-  BcFeatView V{n, R, withSal, dim, dX, dY, dSal, rAdd, rMax, rF64, bAdd, bMax, bF64, cAdd, cMax, cF64, nAdd, nMax, nF64};
+  // ---- medians (GLIA_USE_MEDIAN_AS_FEATS): every set of a row is a union of base segments named by the tree
+  double* dMed = nullptr;
+  const int nMed = h->fc.nMed();
+  if (nMed) {
+    const int nR = h->prm.n_rimg, nB = h->prm.n_bimg;
+    std::vector<int> ea(E), eb(E), rev(E), row(R + 1);
+    if (E) { CK(cudaMemcpyAsync(ea.data(), h->ea.p, 4 * (size_t)E, cudaMemcpyDeviceToHost, st));
+             CK(cudaMemcpyAsync(eb.data(), h->eb.p, 4 * (size_t)E, cudaMemcpyDeviceToHost, st));
+             CK(cudaMemcpyAsync(rev.data(), h->rev.p, 4 * (size_t)E, cudaMemcpyDeviceToHost, st)); }
+    CK(cudaMemcpyAsync(row.data(), h->row.p, 4 * (size_t)(R + 1), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    // leaves in depth-first order: the base regions of a node are one range [lo, hi) of `leaf`
+    std::vector<int> leaf, pos(R, -1), lo(N, 0), hi(N, 0);
+    leaf.reserve(R);
+    {
+      std::vector<std::pair<int, int>> stack;  // (node, state)
+      for (int root = 0; root < N; ++root) {
+        if (parent[root] != root) continue;
+        stack.push_back({root, 0});
+        while (!stack.empty()) {
+          auto [v, state] = stack.back();
+          if (v < R) { lo[v] = (int)leaf.size(); pos[v] = lo[v]; leaf.push_back(v); hi[v] = lo[v] + 1; stack.pop_back(); continue; }
+          if (state == 0) { lo[v] = (int)leaf.size(); stack.back().second = 1; stack.push_back({c0[v], 0}); }
+          else if (state == 1) { stack.back().second = 2; stack.push_back({c1[v], 0}); }
+          else { hi[v] = (int)leaf.size(); stack.pop_back(); }
+        }
+      }
+    }
+    auto inside = [&](int b, int v) { return pos[b] >= lo[v] && pos[b] < hi[v]; };
+    auto live = [&](int e, int v) { return rev[e] < 0 || !inside(eb[e], v); };  // entry of node v (type/region.hxx:66-75)
+    std::vector<double> nodeMed((size_t)N * (nR + nB), 0.0), pairMed((size_t)n * (nB ? nB : 1), 0.0);
+    std::vector<int> qKind, qLen, seg; std::vector<long long> qOff; std::vector<double*> qDst;
+    auto flush = [&]() -> int {
+      if (qKind.empty()) return GLIA_OK;
+      std::vector<double> res(qKind.size());
+      int s = glia_median_queries(h, qKind, qOff, qLen, seg, res.data(), nullptr);
+      if (s != GLIA_OK) return s;
+      for (size_t q = 0; q < res.size(); ++q) *qDst[q] = res[q];
+      qKind.clear(); qLen.clear(); qOff.clear(); qDst.clear(); seg.clear();
+      return GLIA_OK;
+    };
+    auto add_queries = [&](int store, int nImg, long long off, int len, double* dst) {
+      for (int i = 0; i < nImg; ++i) { qKind.push_back(store * GLIA_MAX_IMG + i); qOff.push_back(off); qLen.push_back(len); qDst.push_back(dst + i); }
+    };
+    std::vector<char> used(N, 0);
+    for (int i = 0; i < n; ++i) used[nodeX[i]] = used[nodeY[i]] = used[R + i] = 1;
+    for (int v = 0; v < N; ++v) {
+      if (!used[v]) continue;
+      long long off = (long long)seg.size();
+      for (int k = lo[v]; k < hi[v]; ++k) seg.push_back(leaf[k]);
+      add_queries(0, nR, off, hi[v] - lo[v], &nodeMed[(size_t)v * (nR + nB)]);
+      if (nB) {
+        off = (long long)seg.size();
+        for (int k = lo[v]; k < hi[v]; ++k)
+          for (int e = row[leaf[k]]; e < row[leaf[k] + 1]; ++e) if (live(e, v)) seg.push_back(e);
+        add_queries(1, nB, off, (int)((long long)seg.size() - off), &nodeMed[(size_t)v * (nR + nB) + nR]);
+      }
+      if (v >= R && nB) {  // pair boundary of the merge (util/struct.hxx:10-16, type/region.hxx:42-51)
+        off = (long long)seg.size();
+        const int sides[2][2] = {{c0[v], c1[v]}, {c1[v], c0[v]}};
+        for (auto& sd : sides) {
+          const int A = sd[0], B = sd[1];
+          for (int k = lo[A]; k < hi[A]; ++k)
+            for (int e = row[leaf[k]]; e < row[leaf[k] + 1]; ++e) {
+              if (!live(e, A) || !inside(eb[e], B)) continue;
+              bool act = false;  // the target must still own an entry inside its side
+              for (int e2 = row[eb[e]]; e2 < row[eb[e] + 1] && !act; ++e2) act = live(e2, B);
+              if (act) seg.push_back(e);
+            }
+        }
+        add_queries(1, nB, off, (int)((long long)seg.size() - off), &pairMed[(size_t)(v - R) * nB]);
+      }
+      if (seg.size() > (32u << 20)) { int s = flush(); if (s != GLIA_OK) return s; }
+    }
+    { int s = flush(); if (s != GLIA_OK) return s; }
+    std::vector<double> med((size_t)n * nMed);
+    for (int i = 0; i < n; ++i) {
+      const int x = nodeX[i], y = nodeY[i], z = R + i;
+      double* m = &med[(size_t)i * nMed];
+      for (int k = 0; k < nR; ++k) {
+        m[3 * k] = nodeMed[(size_t)x * (nR + nB) + k]; m[3 * k + 1] = nodeMed[(size_t)y * (nR + nB) + k];
+        m[3 * k + 2] = nodeMed[(size_t)z * (nR + nB) + k];
+      }
+      for (int k = 0; k < nB; ++k) {
+        double* q = m + 3 * nR + 4 * k;
+        q[0] = nodeMed[(size_t)x * (nR + nB) + nR + k]; q[1] = nodeMed[(size_t)y * (nR + nB) + nR + k];
+        q[2] = nodeMed[(size_t)z * (nR + nB) + nR + k]; q[3] = pairMed[(size_t)i * nB + k];
+      }
+    }
+    CK(S.get(&dMed, med.size(), false, st));
+    CK(cudaMemcpyAsync(dMed, med.data(), 8 * med.size(), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));  // med is a local
+  }
+  BcFeatView V{n, R, withSal, dim, dX, dY, dSal, rAdd, rMax, rF64, bAdd, bMax, bF64, cAdd, cMax, cF64, nAdd, nMax, nF64, dMed, nMed};
   bc_feat_rows_kernel<<<nblk(n, 128), 128, 0, st>>>(h->fc, V, dRows);
   h->launches++;
   CK(cudaGetLastError());

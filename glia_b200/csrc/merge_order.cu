@@ -20,6 +20,7 @@
 #include <vector>
 #include <chrono>
 #include "featurize.cuh"
+#include "median.cuh"
 
 int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows);
 int glia_rf_label_index(const glia_rf* m, int label);
@@ -39,7 +40,7 @@ __global__ void __launch_bounds__(MERGE_TPB)
 merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __restrict__ stage,
                    int stageWords, const RfNode16* __restrict__ nodes,
                    const int* __restrict__ treeOff, const RfDist dist, int labelIdx,
-                   double* __restrict__ rows, double* __restrict__ sal) {
+                   double* __restrict__ rows, double* __restrict__ sal, const double* __restrict__ med, int nMed) {
   extern __shared__ __align__(16) double srow[];
   __shared__ int shits;
   const int w = blockIdx.x;
@@ -62,7 +63,8 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
     RecSingle rx = regRec(0), ry = regRec(1);
     RecSum2 rz{rx, ry};
     featurize_row(F, rx, ry, rz, edgeRec(0), edgeRec(1), edgeRec(2), edgeRec(3), nullptr, row,
-                  F.simple ? (threadIdx.x == 0 ? -1 : 4) : (int)(threadIdx.x >> 5));
+                  F.simple ? (threadIdx.x == 0 ? -1 : 4) : (int)(threadIdx.x >> 5), false,
+                  med ? med + (size_t)w * nMed : nullptr);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < F.dim; i += MERGE_TPB) srow[i] = row[i];
@@ -116,6 +118,10 @@ struct Greedy {
   std::vector<Rec> btot;                                         // boundary-of totals (add, f64 only)
   std::vector<std::vector<int>> nmOut;                           // non-mutual boundaries by source region
   std::vector<std::map<int, Rec>> dm;                            // dm[x][w] = mutual boundaries x -> w
+  // median features only (median.cu): the base sets behind the records
+  std::vector<std::map<int, std::vector<int>>> de;               // de[x][w] = base directed boundaries of dm[x][w]
+  std::vector<std::vector<int>> mem;                             // base regions of a region id
+  std::vector<double> medOf;                                     // [id][nR + nB]: region / boundary-of medians
   std::vector<int> ufParent, idOfRoot, repBase;  // union-find over base regions
 
   void ufUnion(int r0, int r1, int r2) {
@@ -219,6 +225,23 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       else G.dm[a].emplace(G.eb[e], G.edgeRec(e));
     }
   }
+  const int nMed = h->fc.nMed(), nRi = h->prm.n_rimg, nBi = h->prm.n_bimg, nMedReg = nRi + nBi;
+  if (nMed) {  // GLIA_USE_MEDIAN_AS_FEATS: keep the base sets behind every record (median.cu)
+    G.de.resize(maxIds); G.mem.resize(maxIds); G.medOf.assign((size_t)maxIds * nMedReg, 0.0);
+    if (C) {  // medians of the base regions were computed for the initial candidates
+      CK(dl(G.medOf.data(), h->medReg.p, 8 * (size_t)R * nMedReg));
+      CK(cudaStreamSynchronize(st));
+    } else {
+      int s = glia_median_init_candidates(h);
+      if (s) return s;
+      CK(dl(G.medOf.data(), h->medReg.p, 8 * (size_t)R * nMedReg));
+      CK(cudaStreamSynchronize(st));
+    }
+    for (int a = 0; a < R; ++a) {
+      G.mem[a].assign(1, a);
+      for (int e = G.row[a]; e < G.row[a + 1]; ++e) if (G.rev[e] >= 0) G.de[a][G.eb[e]].assign(1, e);
+    }
+  }
   std::map<Key, Item> table;
   typedef std::tuple<double, unsigned long long, Key> QKey;
   std::set<QKey> queue;
@@ -241,11 +264,11 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
   const int stageWords = 2 * regW + 4 * edgeW;
   size_t capBatch = 0;
   uint32_t* hStage = nullptr; double* hSal = nullptr; double* hRows = nullptr;
-  uint32_t* dStage = nullptr; double* dSal = nullptr; double* dRows = nullptr;
+  uint32_t* dStage = nullptr; double* dSal = nullptr; double* dRows = nullptr; double* dMed = nullptr;
   auto release = [&]() {
     if (hStage) cudaFreeHost(hStage); if (hSal) cudaFreeHost(hSal); if (hRows) cudaFreeHost(hRows);
-    if (dStage) cudaFree(dStage); if (dSal) cudaFree(dSal); if (dRows) cudaFree(dRows);
-    hStage = nullptr; hSal = nullptr; hRows = nullptr; dStage = nullptr; dSal = nullptr; dRows = nullptr;
+    if (dStage) cudaFree(dStage); if (dSal) cudaFree(dSal); if (dRows) cudaFree(dRows); if (dMed) cudaFree(dMed);
+    hStage = nullptr; hSal = nullptr; hRows = nullptr; dStage = nullptr; dSal = nullptr; dRows = nullptr; dMed = nullptr;
   };
   auto ensure_batch = [&](size_t m) -> cudaError_t {
     if (m <= capBatch) return cudaSuccess;
@@ -257,6 +280,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     if ((e = cudaMallocHost((void**)&hRows, 8 * capBatch * dim)) != cudaSuccess) return e;
     if ((e = cudaMalloc((void**)&dStage, 4 * capBatch * stageWords)) != cudaSuccess) return e;
     if ((e = cudaMalloc((void**)&dSal, 8 * capBatch)) != cudaSuccess) return e;
+    if (nMed && (e = cudaMalloc((void**)&dMed, 8 * capBatch * nMed)) != cudaSuccess) return e;
     return cudaMalloc((void**)&dRows, 8 * capBatch * dim);
   };
   struct Guard { decltype(release)& r; ~Guard() { r(); } } guard{release};
@@ -329,8 +353,25 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       }
       G.dm[r2].emplace(W, std::move(out));
       G.dm[W].emplace(r2, std::move(in));
+      if (nMed) {
+        std::vector<int> lo, li;
+        for (int r : {r0, r1}) {
+          auto f = G.de[r].find(W);
+          if (f != G.de[r].end()) lo.insert(lo.end(), f->second.begin(), f->second.end());
+          auto g = G.de[W].find(r);
+          if (g != G.de[W].end()) { li.insert(li.end(), g->second.begin(), g->second.end()); G.de[W].erase(g); }
+        }
+        G.de[r2].emplace(W, std::move(lo));
+        G.de[W].emplace(r2, std::move(li));
+      }
     }
     G.dm[r0].clear(); G.dm[r1].clear();
+    if (nMed) {
+      G.de[r0].clear(); G.de[r1].clear();
+      G.mem[r2] = std::move(G.mem[r0]);
+      G.mem[r2].insert(G.mem[r2].end(), G.mem[r1].begin(), G.mem[r1].end());
+      G.mem[r1].clear(); G.mem[r1].shrink_to_fit();
+    }
     G.ufUnion(r0, r1, r2);
     // erase the stale table items
     for (auto& kw : keys) {
@@ -361,6 +402,21 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     };
     Rec bzz, pb;
     bzz.init(LE); pb.init(LE);
+    // median queries of this batch: r2's own sets once, then per candidate the merged region, its entries and the
+    // pair boundary; each set is a list of base segments (median.cu)
+    std::vector<int> qKind, qLen, qSeg; std::vector<long long> qOff;
+    auto add_q = [&](int store, int nImg, long long off) {
+      for (int i = 0; i < nImg; ++i) { qKind.push_back(store * GLIA_MAX_IMG + i); qOff.push_back(off); qLen.push_back((int)((long long)qSeg.size() - off)); }
+    };
+    if (nMed) {
+      long long off = 0;
+      qSeg.insert(qSeg.end(), G.mem[r2].begin(), G.mem[r2].end());
+      add_q(0, nRi, off);
+      off = (long long)qSeg.size();
+      for (auto& kv : G.de[r2]) qSeg.insert(qSeg.end(), kv.second.begin(), kv.second.end());
+      qSeg.insert(qSeg.end(), G.nmOut[r2].begin(), G.nmOut[r2].end());
+      add_q(1, nBi, off);
+    }
     for (int W : Ws) {
       const Rec& dWY = G.dm[W][r2]; const Rec& dYW = G.dm[r2][W];
       put_rec(p, G.reg[W]);
@@ -382,17 +438,56 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
         for (int i = 0; i < LE.nMax; ++i) pb.mx[i] = std::max(pb.mx[i], m[i]);
         for (int i = 0; i < LE.nF64; ++i) pb.f[i] += f[i];
       };
-      for (int e : G.nmOut[W]) if (G.cur(G.eb[e]) == r2 && G.active(G.eb[e], r2)) merge_base(e);
+      std::vector<int> pairNM;  // non-mutual boundaries counted into the pair boundary
+      for (int e : G.nmOut[W]) if (G.cur(G.eb[e]) == r2 && G.active(G.eb[e], r2)) { merge_base(e); if (nMed) pairNM.push_back(e); }
       auto nt = nmByTarget.find(W);
-      if (nt != nmByTarget.end()) for (int e : nt->second) if (G.active(G.eb[e], W)) merge_base(e);
+      if (nt != nmByTarget.end()) for (int e : nt->second) if (G.active(G.eb[e], W)) { merge_base(e); if (nMed) pairNM.push_back(e); }
+      if (nMed) {
+        long long off = (long long)qSeg.size();  // region of Z = W u r2
+        qSeg.insert(qSeg.end(), G.mem[W].begin(), G.mem[W].end());
+        qSeg.insert(qSeg.end(), G.mem[r2].begin(), G.mem[r2].end());
+        add_q(0, nRi, off);
+        off = (long long)qSeg.size();            // entries of Z: those of W and r2 except the mutual pair (region.hxx:66-75)
+        for (auto& kv : G.de[W]) if (kv.first != r2) qSeg.insert(qSeg.end(), kv.second.begin(), kv.second.end());
+        for (auto& kv : G.de[r2]) if (kv.first != W) qSeg.insert(qSeg.end(), kv.second.begin(), kv.second.end());
+        qSeg.insert(qSeg.end(), G.nmOut[W].begin(), G.nmOut[W].end());
+        qSeg.insert(qSeg.end(), G.nmOut[r2].begin(), G.nmOut[r2].end());
+        add_q(1, nBi, off);
+        off = (long long)qSeg.size();            // pair boundary
+        { auto f = G.de[W].find(r2); if (f != G.de[W].end()) qSeg.insert(qSeg.end(), f->second.begin(), f->second.end()); }
+        { auto f = G.de[r2].find(W); if (f != G.de[r2].end()) qSeg.insert(qSeg.end(), f->second.begin(), f->second.end()); }
+        qSeg.insert(qSeg.end(), pairNM.begin(), pairNM.end());
+        add_q(1, nBi, off);
+      }
       put_parts(bx.add.data(), bx.add.size(), best1.data(), best1.size(), bx.f.data(), bx.f.size());
       put_parts(by.add.data(), by.add.size(), yb1.data(), yb1.size(), by.f.data(), by.f.size());
       put_rec(p, bzz); put_rec(p, pb);
     }
+    if (nMed) {
+      std::vector<double> res(qKind.size());
+      int s = glia_median_queries(h, qKind, qOff, qLen, qSeg, res.data(), nullptr);
+      if (s) return s;
+      double* my = &G.medOf[(size_t)r2 * nMedReg];
+      for (int i = 0; i < nMedReg; ++i) my[i] = res[i];
+      std::vector<double> med(m * nMed);
+      for (size_t j = 0; j < m; ++j) {
+        const double* mw = &G.medOf[(size_t)Ws[j] * nMedReg];
+        const double* rz = &res[nMedReg + j * (nRi + 2 * nBi)];
+        double* o = &med[j * nMed];
+        for (int i = 0; i < nRi; ++i) { o[3 * i] = mw[i]; o[3 * i + 1] = my[i]; o[3 * i + 2] = rz[i]; }
+        for (int i = 0; i < nBi; ++i) {
+          double* q = o + 3 * nRi + 4 * i;
+          q[0] = mw[nRi + i]; q[1] = my[nRi + i]; q[2] = rz[nRi + i]; q[3] = rz[nRi + nBi + i];
+        }
+      }
+      CK(cudaMemcpyAsync(dMed, med.data(), 8 * med.size(), cudaMemcpyHostToDevice, st));
+      CK(cudaStreamSynchronize(st));  // med is a local
+    }
     const double tC = trace ? now() : 0.0;
     CK(cudaMemcpyAsync(dStage, hStage, 4 * m * stageWords, cudaMemcpyHostToDevice, st));
     merge_batch_kernel<<<(unsigned)m, MERGE_TPB, 8 * (size_t)dim, st>>>(
-        h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, dSal);
+        h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, dSal,
+        nMed ? dMed : nullptr, nMed);
     h->launches++;
     CK(cudaMemcpyAsync(hSal, dSal, 8 * m, cudaMemcpyDeviceToHost, st));
     if (rows) CK(cudaMemcpyAsync(hRows, dRows, 8 * m * dim, cudaMemcpyDeviceToHost, st));
