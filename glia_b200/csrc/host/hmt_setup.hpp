@@ -67,6 +67,8 @@ inline void setup_inputs(const Args& a, HmtInputs& in) {
   p.n_thr = (int)bt.size();
   for (size_t i = 0; i < bt.size(); ++i) p.thr[i] = bt[i];
   p.normalize = a.flag("ns"); p.use_log = a.flag("logs"); p.simple = a.flag("simpf");
+  // the reference's CMake options GLIA_HMT_HIST_FEAT / GLIA_HMT_MEDIAN_FEAT (CMakeLists.txt:53-64) as run-time flags
+  p.use_hist_feat = a.flag("histf"); p.use_median_feat = a.flag("medf");
   p.device = a.has("device") ? atoi(a.str("device").c_str()) : 0;
 }
 

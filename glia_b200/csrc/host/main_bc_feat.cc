@@ -9,7 +9,7 @@ int main(int argc, char** argv) {
   gh::add_alias_common(a);
   if (!a.parse(argc, argv) || a.has("help")) {
     std::cerr << "Usage: bc_feat -s SEG -o ORDER [-y SAL --s0 INIT --sb BIAS] --pb PB [--rbi/--rbb/--rbl/--rbu]...\n"
-                 "       [--bt T...] [-m MASK] [-n 0|1] [-l 0|1] [--simpf 0|1] -b BCFEAT [--device N]\n";
+                 "       [--bt T...] [-m MASK] [-n 0|1] [-l 0|1] [--simpf 0|1] [--histf 0|1] [--medf 0|1] -b BCFEAT [--device N]\n";
     return a.has("help") ? EXIT_SUCCESS : EXIT_FAILURE;
   }
   a.require("mergeOrder"); a.require("bfeat");

@@ -10,7 +10,7 @@ int main(int argc, char** argv) {
   if (!a.parse(argc, argv) || a.has("help")) {
     std::cerr << "Usage: merge_order_bc --bct 1 --bcm MODEL -s SEG --pb PB [--rbi IMG --rbb BINS --rbl LO --rbu HI]...\n"
                  "       [--rli/--rlb/--rll/--rlu] [--ri/--rb/--rl/--ru] [--bi/--bb/--bl/--bu] [--bt T...] [-m MASK]\n"
-                 "       [--bcm M1 --bcm M2 --bcmd DIM0 DIM1 THR] [-n 0|1] [-l 0|1] [--simpf 0|1] -o ORDER [--sal SAL] [-b BCFEAT] [--device N]\n"
+                 "       [--bcm M1 --bcm M2 --bcmd DIM0 DIM1 THR] [-n 0|1] [-l 0|1] [--simpf 0|1] [--histf 0|1] [--medf 0|1] -o ORDER [--sal SAL] [-b BCFEAT] [--device N]\n"
                  "       [--ref-order N]  equal-area pairs follow the unordered_map call order of the reference (N = its rmap.reserve, 0 = none)\n"
                  "Images: .npy, .mha, .mhd (raw).\n";
     return a.has("help") ? EXIT_SUCCESS : EXIT_FAILURE;

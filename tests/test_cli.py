@@ -83,3 +83,27 @@ def test_cli_pipeline_matches_api_and_oracle(tmp_path):
     r = subprocess.run([os.path.join(BIN, "pred_rf"), "--m", "/nonexistent", "--f", feat_f, "--l", "-1", "--p", pred_f],
                        capture_output=True, text=True)
     assert r.returncode == 1 and "Error" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cli_hist_and_median_flags(tmp_path):
+    """--histf / --medf select the layouts the reference builds with GLIA_HMT_HIST_FEAT / GLIA_HMT_MEDIAN_FEAT."""
+    shape = (30, 44)
+    lab, pb = synth.speckle_volume(shape, 40, seed=41)
+    spec = [(pb, 16, 0.0, 1.0)]
+    kw = dict(use_hist=True, use_median=True)
+    o = ol.Oracle(lab, pb, ol.FeatureConfig(rimgs=spec, bimgs=spec, **kw))
+    res = o.greedy(fn=lambda row: np.floor((np.sum(np.abs(row[:12])) * 3.7 % 1.0) * 8) / 8.0)
+    seg_f, pb_f = str(tmp_path / "seg.npy"), str(tmp_path / "pb.mha")
+    np.save(seg_f, lab)
+    _write_mha(pb_f, pb, "MET_FLOAT")
+    order_f, feat_f = str(tmp_path / "order.txt"), str(tmp_path / "bcfeat.txt")
+    np.savetxt(order_f, res["order"], fmt="%d")
+    cmd = [os.path.join(BIN, "bc_feat"), "-s", seg_f, "-o", order_f, "--pb", pb_f, "--rbi", pb_f, "--rbb", "16",
+           "--rbl", "0", "--rbu", "1", "--bt", "0.2", "0.5", "0.8", "--histf", "1", "--medf", "1", "-b", feat_f]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rows = np.loadtxt(feat_f).reshape(len(res["order"]), -1)
+    want = o.bc_feat(res["order"])
+    assert rows.shape == want.shape
+    np.testing.assert_allclose(rows, want, rtol=1e-6, atol=1e-9)

@@ -139,3 +139,86 @@ def test_cuda_greedy_with_reference_call_order(path):
     rg = g.merge_order_bc(grf)
     assert np.array_equal(rg["order"], ro["order"])
     assert np.array_equal(rg["sal"], ro["sal"])
+
+
+# ---------------------------------------------------------------- optional feature layouts (hist / median builds)
+VGOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "variants", "*.npz")))
+
+
+def _vload(path, mod):
+    z = np.load(path)
+    mask = z["mask"] if z["mask"].size else None
+    ns, lg, simp, uh, um = (bool(v) for v in z["flags"])
+    kw = dict(normalize=ns, use_log=lg, simple=simp, use_hist=uh, use_median=um)
+    pb = z["pb"]
+    if z["img2"].size:
+        img2 = z["img2"]
+        cfg = mod.FeatureConfig(rimgs=[(pb, 16, 0.0, 1.0), (img2, 8, 0.0, 1.0)], rlimgs=[(img2, 4, 0.0, 1.0)],
+                                bimgs=[(pb, 16, 0.0, 1.0), (img2, 5, 0.0, 1.0)], **kw)
+    else:
+        cfg = mod.default_config(pb, **kw)
+    return z, z["labels"], pb, mask, cfg, kw
+
+
+def _init_swap(z):
+    rk = z["init_keys"]
+    ks = np.sort(rk[:, :2], axis=1)
+    assert np.array_equal(ks, ks[np.lexsort((ks[:, 1], ks[:, 0]))])  # mode 1 emits in table (key) order
+    return ks, (rk[:, 0] > rk[:, 1]).astype(np.uint8)
+
+
+def test_variant_fixtures_present():
+    assert len(VGOLD) >= 5
+
+
+@pytest.mark.parametrize("path", VGOLD, ids=[os.path.basename(p)[:-4] for p in VGOLD])
+def test_oracle_reproduces_variant_golden(path):
+    """Fixtures from reference builds with GLIA_USE_HISTOGRAM_AS_FEATS / GLIA_USE_MEDIAN_AS_FEATS.  Median builds compute
+    stddev two-pass over a pixel order the oracle does not keep (util/stats.hxx:62-71): 1e-12 there, bit-exact elsewhere."""
+    z, lab, pb, mask, cfg, kw = _vload(path, ol)
+    o = ol.Oracle(lab, pb, cfg, mask=mask)
+    ks, swap = _init_swap(z)
+
+    def same(a, b):
+        assert a.shape == b.shape
+        if kw["use_median"]:
+            np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-14)
+        else:
+            assert np.array_equal(a, b)
+
+    keys, rows = o.init_candidates(swap=swap)
+    assert np.array_equal(keys, ks)
+    same(rows, z["init_rows"])
+    n0 = int(z["n_init"])
+    rk = z["cand_keys"][:n0]
+    k2 = np.sort(rk[:, :2], axis=1)
+    perm = np.lexsort((k2[:, 1], k2[:, 0]))
+    res = o.greedy(fn=quant_pred, init_swap=(rk[perm, 0] > rk[perm, 1]).astype(np.uint8))
+    assert np.array_equal(res["order"], z["order"]) and np.array_equal(res["sal"], z["sal"])
+    same(res["rows"], z["merge_rows"])
+    if not kw["simple"]:
+        same(o.bc_feat(z["order"]), z["bcfeat_rows"])
+        same(o.bc_feat(z["order"], sal=z["sal"], init_sal=1.0, sal_bias=0.25), z["bcfeat_rows_sal"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", VGOLD, ids=[os.path.basename(p)[:-4] for p in VGOLD])
+def test_cuda_reproduces_variant_golden(path):
+    """The CUDA path against the variant reference builds: initial rows with the reference's call order replayed
+    (orient.cu), and the bc_feat stage.  Rows within 1e-5 relative."""
+    from glia_b200 import api
+    z, lab, pb, mask, cfg, kw = _vload(path, api)
+    g = api.MergeTreeBuilder(lab.shape, cfg).build(lab, pb, mask)
+    ks, swap = _init_swap(z)
+    assert g.row_dim() == z["init_rows"].shape[1]
+    emu = g.reference_orientation(4 * g.R + 16)
+    assert np.array_equal(emu, swap)
+    g.set_tie_orientation(emu)
+    keys, rows = g.init_candidates()
+    assert np.array_equal(keys, ks)
+    np.testing.assert_allclose(rows, z["init_rows"], rtol=RTOL, atol=1e-9)
+    g.set_tie_orientation(None)
+    if not kw["simple"]:
+        np.testing.assert_allclose(g.bc_feat(z["order"]), z["bcfeat_rows"], rtol=RTOL, atol=1e-9)
+        np.testing.assert_allclose(g.bc_feat(z["order"], sal=z["sal"], init_sal=1.0, sal_bias=0.25),
+                                   z["bcfeat_rows_sal"], rtol=RTOL, atol=1e-9)
