@@ -120,3 +120,38 @@ def test_median_needs_whole_volume():
     cfg = api.FeatureConfig(rimgs=[(pb, 16, 0.0, 1.0)], bimgs=[(pb, 16, 0.0, 1.0)], use_median=True)
     with pytest.raises(api.GliaError):
         api.MergeTreeBuilder((8, 8, 8), cfg, slab=(0, 4, 0, 1))
+
+
+def test_median_variant_at_slice_size(record_property):
+    """One C3-size slice (2048^2, ~25 k superpixels) and a 96^3 volume with hist + median features on: every row of the
+    initial candidates against the oracle, the median columns bit for bit."""
+    import ctypes as C
+    import time
+    import torch
+    for shape, cell in (((2048, 2048), 13), ((96, 96, 96), 10)):
+        L = api.lib()
+        nd = len(shape)
+        n = int(np.prod(shape))
+        lab_d = torch.empty(n, dtype=torch.int32, device="cuda")
+        pb_d = torch.empty(n, dtype=torch.float32, device="cuda")
+        dims = (C.c_int * 3)(*(list(shape[::-1]) + [1] * (3 - nd)))
+        nc = C.c_uint64(0)
+        assert L.glia_b200_synth_voronoi(nd, dims, cell, 77, lab_d.data_ptr(), pb_d.data_ptr(), None, C.byref(nc)) == 0
+        torch.cuda.synchronize()
+        lab, pb = lab_d.cpu().numpy().view(np.uint32).reshape(shape), pb_d.cpu().numpy().reshape(shape)
+        co, cg = _cfgs(pb, None, use_hist=True, use_median=True)
+        o = ol.Oracle(lab, pb, co)
+        g = api.MergeTreeBuilder(shape, cg, label_bound=int(nc.value) + 1)
+        g.build(lab, pb)
+        t0 = time.perf_counter()
+        g.build(lab, pb)
+        kg, rowg = g.init_candidates()
+        dt = time.perf_counter() - t0
+        ko, rowo = o.init_candidates()
+        assert np.array_equal(ko, kg)
+        np.testing.assert_allclose(rowg, rowo, rtol=RTOL, atol=1e-9)
+        mc = _median_columns(o, co)
+        assert np.array_equal(rowg[:, mc], rowo[:, mc])
+        record_property("median_build_plus_rows_s_%dd" % nd, dt)
+        print("median variant %s: R=%d C=%d dim=%d, build + rows (host buffers) %.3f s" % (shape, g.R, g.Cn, g.row_dim(), dt))
+        g.close()
