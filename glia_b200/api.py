@@ -62,7 +62,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_region_presence", "glia_b200_index_regions", "glia_b200_gather_regions",
            "glia_b200_tune", "glia_b200_candidate_ties", "glia_b200_set_tie_orientation",
            "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
-           "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms"]
+           "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms",
+           "glia_b200_bc_feat_sharded"]
 
 
 def lib():
@@ -101,6 +102,8 @@ def lib():
         L.glia_b200_merge_order_bc.argtypes = [vp, vp, vp, vp, vp, C.POINTER(C.c_int64),
                                                C.POINTER(C.c_int64)]
         L.glia_b200_bc_feat.argtypes = [vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp]
+        L.glia_b200_bc_feat_sharded.argtypes = [vp, vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp,
+                                                C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.glia_b200_rf_load.argtypes = [C.c_char_p, C.c_int, C.POINTER(vp)]
         L.glia_b200_rf_from_arrays.argtypes = [C.c_int] * 4 + [vp] * 7 + [C.c_int, C.POINTER(vp)]
         L.glia_b200_rf_destroy.argtypes = [vp]
@@ -464,6 +467,18 @@ class MergeTreeBuilder:
         self._check(lib().glia_b200_build_sharded(self.h, comm.h, _addr(labels), _addr(mask), _addr(pb)))
         self._counts()
         return self
+
+    def bc_feat_sharded(self, comm, order, sal=None, init_sal=1.0, sal_bias=0.0):
+        """bc_feat stage on a sharded build (collective): returns (first, rows) - this rank's share of the merges."""
+        order = np.ascontiguousarray(order, np.uint32)
+        n = len(order)
+        s = None if sal is None else np.ascontiguousarray(sal, np.float64)
+        share = (n + comm.world - 1) // comm.world
+        rows = np.zeros((max(share, 1), self.row_dim(sal is not None)))
+        first, count = C.c_int64(), C.c_int64()
+        self._check(lib().glia_b200_bc_feat_sharded(self.h, comm.h, _addr(order), n, _addr(s), C.c_double(init_sal),
+                                                    C.c_double(sal_bias), _addr(rows), C.byref(first), C.byref(count)))
+        return first.value, rows[:count.value]
 
     def build_partial(self, labels, pb, mask=None):
         if not self.device_pointers:

@@ -271,6 +271,7 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
   const VoxParams& P = h->vp;
   const uint32_t LB = P.labelBound;
   const long long R = h->R;
+  h->ownLo = ownLo; h->ownHi = ownHi;
   size_t tmpBytes = 0;
   PhaseTrace tr(st);
   CK(cudaMemsetAsync(h->scalars.p, 0, 64, st));

@@ -63,6 +63,15 @@ struct FeatCfg {
   __host__ __device__ int nMed() const { return median ? 3 * nR + 4 * nB : 0; }  // medians of one row (featurize.cuh)
 };
 
+// Completes per-node tables that every rank of a sharded build holds a partial copy of (merge.cu asks, shard.cu
+// answers with ncclAllReduce); in place, on the given stream.
+struct TableReducer {
+  enum Type { U32, I32, F64 };
+  enum Op { SUM, MAX, MIN };
+  virtual int all_reduce(void* buf, size_t count, Type t, Op op, cudaStream_t st) = 0;
+  virtual ~TableReducer() {}
+};
+
 }  // namespace glia
 
 // alg::EnsembleRandomForest + opt::ThresholdModelDistributor (alg/rf.hxx:63-98, type/function.hxx:71-85):
@@ -135,6 +144,7 @@ struct glia_handle {
   glia::DevBuf regAdd, regMax, regF64, edgeKeys, edgeAdd, edgeMax, edgeF64, flags;
   // finalised graph
   long long R = 0, E = 0, C = 0;
+  long long ownLo = 0, ownHi = 0;                          // region indices owned by this handle (all of them unless sharded)
   glia::DevBuf rank, regLabel, cAdd, cMax, cF64;          // regions ascending by label
   glia::DevBuf eSlot, eKey, eSlotSorted, eKeySorted;      // compaction + sort
   glia::DevBuf sAdd, sMax, sF64, ea, eb, row, rev, cand;  // directed boundaries, CSR by a

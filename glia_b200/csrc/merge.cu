@@ -55,12 +55,15 @@ __device__ __forceinline__ int lca_of(const TreeView& T, int a, int b) {
 
 // per directed boundary: LCA of its end points; per base region: depth of the highest LCA
 // among its mutual boundaries (topd) and whether it owns a non-mutual boundary (hasNM)
+// A sharded build holds the boundaries of its owned regions AND of their neighbours; a boundary is handled by the
+// rank that owns its source region, [ownLo, ownHi) (every directed boundary exactly once across the ranks).
 __global__ void edge_lca_kernel(TreeView T, const int* __restrict__ ea, const int* __restrict__ eb,
                                 const int* __restrict__ rev, int E, int* __restrict__ lca,
-                                int* __restrict__ topd, int* __restrict__ hasNM) {
+                                int* __restrict__ topd, int* __restrict__ hasNM, int ownLo, int ownHi) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= E) return;
   int a = ea[e], b = eb[e];
+  if (a < ownLo || a >= ownHi) { lca[e] = -1; return; }
   int l = lca_of(T, a, b);
   lca[e] = l;
   if (rev[e] >= 0) atomicMin(topd + a, l >= 0 ? T.depth[l] : -1);  // never cancelled: always live
@@ -75,11 +78,12 @@ __global__ void edge_scatter_kernel(TreeView T, const int* __restrict__ ea, cons
                                     RecLayout L, const uint32_t* __restrict__ sAdd,
                                     const uint32_t* __restrict__ sMax, const double* __restrict__ sF64,
                                     uint32_t* cAdd, uint32_t* cMax, double* cF64, uint32_t* nAdd,
-                                    uint32_t* nMax, double* nF64, uint32_t* bMax) {
+                                    uint32_t* nMax, double* nF64, uint32_t* bMax, int ownLo, int ownHi) {
   long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (w >= E) return;
   int e = (int)w, a = ea[e], b = eb[e], l = lca[e];
+  if (a < ownLo || a >= ownHi) return;
   bool mutual = rev[e] >= 0;
   if (l >= 0) {
     uint32_t* dA; uint32_t* dM; double* dF; bool go = true;
@@ -132,6 +136,7 @@ __global__ void level_combine_kernel(const int* __restrict__ nodes, int count,
 
 struct BcFeatView {
   int n, R, withSal, dim;
+  int first, count;                    // rows [first, first + count) are written (a rank's share, shard.cu)
   const int* nodeX; const int* nodeY;  // [n] nodes merged at step i (node of the step = R + i)
   const double* nodeSal;               // [N] or null
   const uint32_t* rAdd; const uint32_t* rMax; const double* rF64;
@@ -145,7 +150,9 @@ __global__ void __launch_bounds__(128)
 bc_feat_rows_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ BcFeatView V,
                     double* __restrict__ rows) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= V.n) return;
+  if (i >= V.count) return;
+  rows += (size_t)i * V.dim;
+  i += V.first;
   size_t x = V.nodeX[i], y = V.nodeY[i], z = (size_t)V.R + i;
   const RecLayout LR = F.reg, LE = F.edge;
   auto R = [&](size_t v) { return RecSingle{V.rAdd + v * LR.nAdd, V.rMax + v * LR.nMax, V.rF64 + v * LR.nF64}; };
@@ -155,7 +162,7 @@ bc_feat_rows_kernel(const __grid_constant__ FeatCfg F, const __grid_constant__ B
   double sal[3];
   if (V.withSal) { sal[0] = V.nodeSal[x]; sal[1] = V.nodeSal[y]; sal[2] = V.nodeSal[z]; }
   featurize_row(F, R(x), R(y), R(z), B(x), B(y), B(z), pb, V.withSal ? sal : nullptr,
-                rows + (size_t)i * V.dim, -1, false, V.med ? V.med + (size_t)i * V.nMed : nullptr);
+                rows, -1, false, V.med ? V.med + (size_t)i * V.nMed : nullptr);
 }
 
 }  // namespace glia
@@ -180,11 +187,18 @@ struct Scratch {  // freed on scope exit
 };
 }  // namespace
 
-extern "C" int glia_b200_bc_feat(glia_handle* h, const uint32_t* order, int64_t n64,
-                                 const double* sal_in, double init_sal, double sal_bias,
-                                 double* rows) {
+// K5 for one handle, or - with a reducer - for one rank of a z-slab sharded build (shard.cu): every directed boundary
+// lives on exactly one rank, so the per-node sums / maxima scattered from the local boundaries are partial and one
+// all-reduce per array completes them; the tree, the level-wise combination (cheap) and the region records (already
+// global) are replicated, and each rank featurises its contiguous share of the merges.
+int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const double* sal_in, double init_sal,
+                      double sal_bias, double* rows, glia::TableReducer* red, int world, int rank, int64_t* firstOut,
+                      int64_t* countOut) {
   if (!h || (n64 > 0 && (!order || !rows)) || n64 < 0 || n64 > 0x3fffffff) return GLIA_E_ARG;
   if (!h->built) return GLIA_E_STATE;
+  if (firstOut) *firstOut = 0;
+  if (countOut) *countOut = 0;
+  if (red && h->fc.nMed()) { h->err = "median features need the whole volume in one handle"; return GLIA_E_STATE; }
   if (n64 == 0) return GLIA_OK;
   CK(cudaSetDevice(h->prm.device));
   cudaStream_t st = h->stream;
@@ -245,7 +259,11 @@ extern "C" int glia_b200_bc_feat(glia_handle* h, const uint32_t* order, int64_t 
   CK(S.get(&nAdd, (size_t)N * LE.nAdd, true, st)); CK(S.get(&nMax, (size_t)N * LE.nMax, true, st));
   CK(S.get(&nF64, (size_t)N * LE.nF64, true, st));
   const int dim = glia_b200_row_dim(h, withSal);
-  if (h->prm.device_pointers) dRows = rows; else CK(S.get(&dRows, (size_t)n * dim, false, st));
+  const int share = (n + world - 1) / world;
+  const int first = std::min(n, rank * share), count = std::min(n, first + share) - first;
+  if (firstOut) *firstOut = first;
+  if (countOut) *countOut = count;
+  if (h->prm.device_pointers) dRows = rows; else CK(S.get(&dRows, (size_t)std::max(count, 1) * dim, false, st));
   if (withSal) { CK(S.get(&dSal, N, false, st)); CK(cudaMemcpyAsync(dSal, nodeSal.data(), 8 * (size_t)N, cudaMemcpyHostToDevice, st)); }
   std::vector<int> cnt0(N);
   for (int v = 0; v < N; ++v) cnt0[v] = parent[v] != v;
@@ -272,11 +290,36 @@ extern "C" int glia_b200_bc_feat(glia_handle* h, const uint32_t* order, int64_t 
   }
   TreeView T{N, R, K, dUp, cntPrev};
   if (E > 0) {
-    edge_lca_kernel<<<nblk(E, 256), 256, 0, st>>>(T, h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>(), E, dLca, dTopd, dHasNM);
+    edge_lca_kernel<<<nblk(E, 256), 256, 0, st>>>(T, h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>(), E, dLca, dTopd, dHasNM,
+                                                  (int)h->ownLo, (int)h->ownHi);
+  }
+  if (red) {  // which base regions still own live entries is a property of ALL boundaries
+    int s;
+    if ((s = red->all_reduce(dTopd, (size_t)R, glia::TableReducer::I32, glia::TableReducer::MIN, st))) return s;
+    if ((s = red->all_reduce(dHasNM, (size_t)R, glia::TableReducer::I32, glia::TableReducer::MAX, st))) return s;
+  }
+  if (E > 0) {
     edge_scatter_kernel<<<nblk((long long)E * 32, 256), 256, 0, st>>>(
         T, h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>(), dLca, dTopd, dHasNM, E, LE, h->sAdd.as<uint32_t>(),
-        h->sMax.as<uint32_t>(), h->sF64.as<double>(), cAdd, cMax, cF64, nAdd, nMax, nF64, bMax);
+        h->sMax.as<uint32_t>(), h->sF64.as<double>(), cAdd, cMax, cF64, nAdd, nMax, nF64, bMax, (int)h->ownLo, (int)h->ownHi);
     h->launches += 2;
+  }
+  if (red) {
+    typedef glia::TableReducer TR;
+    int s;
+    // leaves: boundary-of aggregates, each taken from the rank that owns the region
+    if (h->ownLo > 0) { CK(cudaMemsetAsync(bAdd, 0, 4 * (size_t)h->ownLo * LE.nAdd, st)); CK(cudaMemsetAsync(bF64, 0, 8 * (size_t)h->ownLo * LE.nF64, st)); }
+    if (h->ownHi < R) { CK(cudaMemsetAsync(bAdd + (size_t)h->ownHi * LE.nAdd, 0, 4 * (size_t)(R - h->ownHi) * LE.nAdd, st));
+                        CK(cudaMemsetAsync(bF64 + (size_t)h->ownHi * LE.nF64, 0, 8 * (size_t)(R - h->ownHi) * LE.nF64, st)); }
+    if ((s = red->all_reduce(bAdd, (size_t)R * LE.nAdd, TR::U32, TR::SUM, st))) return s;
+    if ((s = red->all_reduce(bF64, (size_t)R * LE.nF64, TR::F64, TR::SUM, st))) return s;
+    if ((s = red->all_reduce(bMax, (size_t)N * LE.nMax, TR::U32, TR::MAX, st))) return s;
+    if ((s = red->all_reduce(cAdd, (size_t)N * LE.nAdd, TR::U32, TR::SUM, st))) return s;
+    if ((s = red->all_reduce(cMax, (size_t)N * LE.nMax, TR::U32, TR::MAX, st))) return s;
+    if ((s = red->all_reduce(cF64, (size_t)N * LE.nF64, TR::F64, TR::SUM, st))) return s;
+    if ((s = red->all_reduce(nAdd, (size_t)N * LE.nAdd, TR::U32, TR::SUM, st))) return s;
+    if ((s = red->all_reduce(nMax, (size_t)N * LE.nMax, TR::U32, TR::MAX, st))) return s;
+    if ((s = red->all_reduce(nF64, (size_t)N * LE.nF64, TR::F64, TR::SUM, st))) return s;
   }
   // ---- per-level update of merged-region records
   for (int l = 1; l <= maxLevel; ++l) {
@@ -379,11 +422,17 @@ extern "C" int glia_b200_bc_feat(glia_handle* h, const uint32_t* order, int64_t 
     CK(cudaMemcpyAsync(dMed, med.data(), 8 * med.size(), cudaMemcpyHostToDevice, st));
     CK(cudaStreamSynchronize(st));  // med is a local
   }
-  BcFeatView V{n, R, withSal, dim, dX, dY, dSal, rAdd, rMax, rF64, bAdd, bMax, bF64, cAdd, cMax, cF64, nAdd, nMax, nF64, dMed, nMed};
-  bc_feat_rows_kernel<<<nblk(n, 128), 128, 0, st>>>(h->fc, V, dRows);
+  BcFeatView V{n, R, withSal, dim, first, count, dX, dY, dSal, rAdd, rMax, rF64, bAdd, bMax, bF64, cAdd, cMax, cF64, nAdd, nMax, nF64, dMed, nMed};
+  if (count) bc_feat_rows_kernel<<<nblk(count, 128), 128, 0, st>>>(h->fc, V, dRows);
   h->launches++;
   CK(cudaGetLastError());
-  if (!h->prm.device_pointers) CK(cudaMemcpyAsync(rows, dRows, 8 * (size_t)n * dim, cudaMemcpyDeviceToHost, st));
+  if (!h->prm.device_pointers && count) CK(cudaMemcpyAsync(rows, dRows, 8 * (size_t)count * dim, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return GLIA_OK;
+}
+
+extern "C" int glia_b200_bc_feat(glia_handle* h, const uint32_t* order, int64_t n64,
+                                 const double* sal_in, double init_sal, double sal_bias,
+                                 double* rows) {
+  return glia_bc_feat_impl(h, order, n64, sal_in, init_sal, sal_bias, rows, nullptr, 1, 0, nullptr, nullptr);
 }

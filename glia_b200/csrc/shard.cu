@@ -531,3 +531,34 @@ extern "C" int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint3
   cudaEventElapsedTime(&ms, c->evB, c->evC); h->ms[1] = ms;  // graph: import + CSR + candidates + region gather
   return GLIA_OK;
 }
+
+// ---- K5 on a sharded build: the bc_feat stage for a given merge order, every rank featurising its share of the
+// merges (hmt/main_bc_feat.cxx:76-95 is the reference's parfor over merges).  The directed boundaries of a sharded
+// build are spread over the ranks, so the per-node tables merge.cu scatters them into are completed by all-reduces.
+int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const double* sal_in, double init_sal,
+                      double sal_bias, double* rows, glia::TableReducer* red, int world, int rank, int64_t* firstOut,
+                      int64_t* countOut);
+
+namespace {
+struct NcclReducer : glia::TableReducer {
+  NcclApi* N; glia_comm* c; glia_handle* h;
+  int all_reduce(void* buf, size_t count, Type t, Op op, cudaStream_t st) override {
+    if (!count) return GLIA_OK;
+    const ncclDataType_t dt = t == U32 ? ncclUint32 : (t == I32 ? ncclInt32 : ncclFloat64);
+    const ncclRedOp_t ro = op == SUM ? ncclSum : (op == MAX ? ncclMax : ncclMin);
+    NK(h, N->AllReduce(buf, buf, count, dt, ro, c->main, st));
+    return GLIA_OK;
+  }
+};
+}  // namespace
+
+extern "C" int glia_b200_bc_feat_sharded(glia_handle* h, glia_comm* c, const uint32_t* order, int64_t n,
+                                         const double* sal_in, double init_sal, double sal_bias, double* rows,
+                                         int64_t* first, int64_t* count) {
+  NcclApi* N = nccl_api();
+  if (!h || !c || !N) return GLIA_E_ARG;
+  if (c->device != h->prm.device) { h->err = "communicator lives on another device"; return GLIA_E_ARG; }
+  NcclReducer red;
+  red.N = N; red.c = c; red.h = h;
+  return glia_bc_feat_impl(h, order, n, sal_in, init_sal, sal_bias, rows, &red, c->world, c->rank, first, count);
+}

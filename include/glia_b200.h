@@ -210,6 +210,14 @@ GLIA_API int glia_b200_comm_create(const void* id256, int world, int rank, int d
 GLIA_API void glia_b200_comm_destroy(glia_comm* c);
 GLIA_API int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint32_t* labels, const uint32_t* mask,
                                      const float* pb);
+/* The bc_feat stage (glia_b200_bc_feat) on a handle built by glia_b200_build_sharded: collective over the communicator.
+ * Every rank passes the same order / saliencies; rank r featurises merges [*first, *first + *count) - contiguous
+ * shares of ceil(n / world) - and writes them to rows[0 .. *count) (reference: the parfor over merges of
+ * hmt/main_bc_feat.cxx:76-95).  The per-node boundary tables are completed by all-reduces, the merge tree is
+ * replicated.  Not available with use_median_feat. */
+GLIA_API int glia_b200_bc_feat_sharded(glia_handle* h, glia_comm* c, const uint32_t* order, int64_t n,
+                                       const double* sal_in, double init_sal, double sal_bias, double* rows,
+                                       int64_t* first, int64_t* count);
 GLIA_API double glia_b200_comm_last_exchange_ms(const glia_comm* c);
 
 /* ---- random forest ---- */

@@ -46,6 +46,23 @@ def main():
             good = (all(x[3] == g.R for x in parts) and np.array_equal(K, k0) and np.array_equal(Rw, rows0) and np.array_equal(S, sal0))
             print("shape", shape, "shuffle", shuffle, "R", g.R, "C", g.Cn, "native == single:", good, flush=True)
             ok = ok and good
+        # the bc_feat stage on the sharded build (K5): a greedy order from the single handle, every rank featurises its
+        # share of the merges, gathered rows == the single-handle stage (with and without saliency columns)
+        res = g.merge_order_bc(forest)
+        for sal_in in (None, res["sal"]):
+            want = g.bc_feat(res["order"], sal=sal_in, init_sal=1.0, sal_bias=0.25)
+            first, mine = b.bc_feat_sharded(native, res["order"], sal=sal_in, init_sal=1.0, sal_bias=0.25)
+            parts = [None] * world
+            dist.all_gather_object(parts, (first, mine))
+            if rank == 0:
+                parts.sort(key=lambda x: x[0])
+                got = np.concatenate([x[1] for x in parts])
+                good = got.shape == want.shape and np.array_equal(got, want)
+                if not good and got.shape == want.shape:
+                    bad = np.argwhere(got != want)
+                    print("  first mismatches (row, col):", bad[:5].tolist(), "max abs diff", float(np.abs(got - want).max()), flush=True)
+                print("  bc_feat sharded (%d merges, sal=%s) == single: %s" % (len(want), sal_in is not None, good), flush=True)
+                ok = ok and good
         b.close(); g.close()
     native.close()
     flag = torch.tensor([1 if ok else 0], device=torch.device("cuda", lr))
