@@ -177,17 +177,6 @@ using namespace glia;
 #include <stdio.h>
 #include <stdlib.h>
 // GLIA_B200_TRACE=1: host-side wall clock of each finalisation phase (stream synchronised) on stderr
-struct PhaseTrace {
-  bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
-  PhaseTrace(cudaStream_t s) : on(getenv("GLIA_B200_TRACE") != nullptr), st(s) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
-  void mark(const char* what) {
-    if (!on) return;
-    cudaStreamSynchronize(st);
-    auto t1 = std::chrono::steady_clock::now();
-    fprintf(stderr, "[glia trace] %-28s %8.1f us\n", what, std::chrono::duration<double, std::micro>(t1 - t0).count());
-    t0 = t1;
-  }
-};
 static inline unsigned nblk(long long n, int per) { return (unsigned)((n + per - 1) / per); }
 
 int glia_finalize_regions(glia_handle* h);

@@ -1,5 +1,8 @@
 // glia_b200 — the handle behind the C ABI (include/glia_b200.h).
 #pragma once
+#include <chrono>
+#include <stdio.h>
+#include <stdlib.h>
 #include <vector>
 #include "common.cuh"
 
@@ -61,6 +64,19 @@ struct FeatCfg {
     return x0Len() + 3 * xiLen() + (withSal ? 5 : 0);
   }
   __host__ __device__ int nMed() const { return median ? 3 * nR + 4 * nB : 0; }  // medians of one row (featurize.cuh)
+};
+
+// GLIA_B200_TRACE=1: per-phase wall times on stderr (each mark synchronises the stream; diagnostics only).
+struct PhaseTrace {
+  bool on; cudaStream_t st; std::chrono::steady_clock::time_point t0;
+  PhaseTrace(cudaStream_t s) : on(getenv("GLIA_B200_TRACE") != nullptr), st(s) { if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); } }
+  void mark(const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[glia trace] %-28s %8.1f us\n", what, std::chrono::duration<double, std::micro>(t1 - t0).count());
+    t0 = t1;
+  }
 };
 
 // Completes per-node tables that every rank of a sharded build holds a partial copy of (merge.cu asks, shard.cu

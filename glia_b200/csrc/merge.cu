@@ -205,6 +205,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   const int n = (int)n64, R = (int)h->R, E = (int)h->E, N = R + n;
   const int withSal = sal_in != nullptr;
   const RecLayout LR = h->vp.reg, LE = h->vp.edge;
+  PhaseTrace tr(st);
   // ---- host: labels -> nodes, tree, levels
   std::vector<uint32_t> lab(R);
   if (R) CK(cudaMemcpyAsync(lab.data(), h->regLabel.p, 4 * (size_t)R, cudaMemcpyDeviceToHost, st));
@@ -240,6 +241,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
     for (int i = 0; i < n; ++i) levelNodes[pos[level[R + i]]++] = R + i; }
   int K = 1; while ((1ll << K) < N) ++K;
   ++K;
+  tr.mark("k5: host tree");
   // ---- device buffers
   Scratch S;
   int *dUp, *dCntA, *dCntB, *dC0, *dC1, *dX, *dY, *dLevelNodes, *dLca, *dTopd, *dHasNM;
@@ -281,6 +283,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   CK(cudaMemcpyAsync(rF64, h->cF64.p, 8 * (size_t)R * LR.nF64, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(bAdd, h->bAggAdd.p, 4 * (size_t)R * LE.nAdd, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(bF64, h->bAggF64.p, 8 * (size_t)R * LE.nF64, cudaMemcpyDeviceToDevice, st));
+  tr.mark("k5: alloc + upload");
   // ---- binary lifting + depth
   int* cntPrev = dCntA; int* cntNext = dCntB;
   for (int k = 0; k + 1 < K; ++k) {
@@ -289,6 +292,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
     h->launches++;
   }
   TreeView T{N, R, K, dUp, cntPrev};
+  tr.mark("k5: lifting");
   if (E > 0) {
     edge_lca_kernel<<<nblk(E, 256), 256, 0, st>>>(T, h->ea.as<int>(), h->eb.as<int>(), h->rev.as<int>(), E, dLca, dTopd, dHasNM,
                                                   (int)h->ownLo, (int)h->ownHi);
@@ -321,6 +325,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
     if ((s = red->all_reduce(nMax, (size_t)N * LE.nMax, TR::U32, TR::MAX, st))) return s;
     if ((s = red->all_reduce(nF64, (size_t)N * LE.nF64, TR::F64, TR::SUM, st))) return s;
   }
+  tr.mark("k5: boundary lca + scatter");
   // ---- per-level update of merged-region records
   for (int l = 1; l <= maxLevel; ++l) {
     int cnt = levelOff[l + 1] - levelOff[l];
@@ -329,6 +334,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
         dLevelNodes + levelOff[l], cnt, dC0, dC1, LR, LE, rAdd, rMax, rF64, bAdd, bF64, cAdd, cF64);
     h->launches++;
   }
+  tr.mark("k5: level combine");
   // ---- medians (GLIA_USE_MEDIAN_AS_FEATS): every set of a row is a union of base segments named by the tree
   double* dMed = nullptr;
   const int nMed = h->fc.nMed();
@@ -426,8 +432,11 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   if (count) bc_feat_rows_kernel<<<nblk(count, 128), 128, 0, st>>>(h->fc, V, dRows);
   h->launches++;
   CK(cudaGetLastError());
+  tr.mark("k5: rows kernel");
   if (!h->prm.device_pointers && count) CK(cudaMemcpyAsync(rows, dRows, 8 * (size_t)count * dim, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  tr.mark("k5: rows to host");
+  if (tr.on) fprintf(stderr, "[glia trace] k5: %d merges, %d levels\n", n, maxLevel);
   return GLIA_OK;
 }
 
