@@ -159,10 +159,41 @@ extern "C" void glia_b200_destroy(glia_handle* h) {
   for (auto& b : h->medRKeys) b.release();
   for (auto& b : h->medEKeys) b.release();
   for (auto& b : h->medQ) b.release();
+  for (auto& b : h->k5) b.release();
   for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);
   if (h->copyStream) { for (int i = 0; i < 4; ++i) cudaEventDestroy(h->evCopy[i]); cudaStreamDestroy(h->copyStream); }
+  for (int i = 0; i < 2; ++i) { if (h->pin[i]) cudaFreeHost(h->pin[i]); if (h->evPin[i]) cudaEventDestroy(h->evPin[i]); }
   if (h->ownStream) cudaStreamDestroy(h->stream);
   delete h;
+}
+
+// A cudaMemcpy into pageable memory goes through the driver's small staging buffer (~3 GB/s measured for 81 MB of
+// bc_feat rows); two pinned 8 MB buffers filled asynchronously while the host drains the other one reach PCIe speed.
+int glia_copy_to_host(glia_handle* h, void* dst, const void* dsrc, size_t bytes) {
+  const size_t CH = 8u << 20;
+  cudaStream_t st = h->stream;
+  if (bytes <= CH) {
+    GLIA_CUDA_CHECK(h, cudaMemcpyAsync(dst, dsrc, bytes, cudaMemcpyDeviceToHost, st));
+    GLIA_CUDA_CHECK(h, cudaStreamSynchronize(st));
+    return GLIA_OK;
+  }
+  for (int i = 0; i < 2; ++i) {
+    if (!h->pin[i]) GLIA_CUDA_CHECK(h, cudaMallocHost(&h->pin[i], CH));
+    if (!h->evPin[i]) GLIA_CUDA_CHECK(h, cudaEventCreateWithFlags(&h->evPin[i], cudaEventDisableTiming));
+  }
+  const size_t nch = (bytes + CH - 1) / CH;
+  auto len = [&](size_t k) { return std::min(CH, bytes - k * CH); };
+  GLIA_CUDA_CHECK(h, cudaMemcpyAsync(h->pin[0], dsrc, len(0), cudaMemcpyDeviceToHost, st));
+  GLIA_CUDA_CHECK(h, cudaEventRecord(h->evPin[0], st));
+  for (size_t k = 0; k < nch; ++k) {
+    if (k + 1 < nch) {
+      GLIA_CUDA_CHECK(h, cudaMemcpyAsync(h->pin[(k + 1) & 1], (const char*)dsrc + (k + 1) * CH, len(k + 1), cudaMemcpyDeviceToHost, st));
+      GLIA_CUDA_CHECK(h, cudaEventRecord(h->evPin[(k + 1) & 1], st));
+    }
+    GLIA_CUDA_CHECK(h, cudaEventSynchronize(h->evPin[k & 1]));
+    memcpy((char*)dst + k * CH, h->pin[k & 1], len(k));
+  }
+  return GLIA_OK;
 }
 
 // Re-points one configured image at a new buffer of the same extent (a handle is reused for a

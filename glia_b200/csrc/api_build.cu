@@ -448,7 +448,7 @@ extern "C" int glia_b200_init_candidates(glia_handle* h, uint32_t* keys, double*
   CK(cudaEventRecord(h->ev[4], h->stream));
   if (!h->prm.device_pointers) {
     if (keys) CK(cudaMemcpyAsync(keys, dKeys, 8 * C, cudaMemcpyDeviceToHost, h->stream));
-    if (rows) CK(cudaMemcpyAsync(rows, dRows, 8 * C * dim, cudaMemcpyDeviceToHost, h->stream));
+    if (rows) { int s2 = glia_copy_to_host(h, rows, dRows, 8 * C * dim); if (s2 != GLIA_OK) return s2; }
   }
   CK(cudaStreamSynchronize(h->stream));
   float ms = 0; cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]); h->ms[2] = ms;

@@ -176,5 +176,12 @@ struct glia_handle {
   // median features (median.cu): sorted value keys per base region / directed boundary, per image
   glia::DevBuf medRKeys[GLIA_MAX_IMG], medEKeys[GLIA_MAX_IMG], medRStart, medEStart, medTmpA, medTmpB;
   glia::DevBuf medReg, medCand, medQ[6];
+  glia::DevBuf k5[40];                                    // scratch of the bc_feat stage (merge.cu), kept between calls
   bool hasMedian = false;
+  // large results to pageable host memory: two pinned staging buffers, D2H of chunk k+1 overlaps the host copy of chunk k
+  void* pin[2] = {nullptr, nullptr};
+  cudaEvent_t evPin[2] = {nullptr, nullptr};
 };
+
+// device -> (pageable) host copy of a large result on the handle's stream; returns when dst is complete (api.cu)
+int glia_copy_to_host(glia_handle* h, void* dst, const void* dsrc, size_t bytes);

@@ -134,6 +134,29 @@ __global__ void level_combine_kernel(const int* __restrict__ nodes, int count,
   for (int i = lane; i < LE.nF64; i += 32) bF64[z * LE.nF64 + i] = bF64[x * LE.nF64 + i] + bF64[y * LE.nF64 + i] - cF64[z * LE.nF64 + i];
 }
 
+// The narrow top of a deep tree (every remaining level holds <= 256 nodes; a greedy or random merge order on 10^5
+// regions has ~10^4 such levels): ONE CTA walks those levels in order, a warp per node, a barrier per level, instead of
+// one launch per level.  trip[i] = (node, child0, child1) in level order.
+__global__ void __launch_bounds__(1024)
+level_tail_kernel(const int4* __restrict__ trip, const int* __restrict__ levelOff, int l0, int l1,
+                  RecLayout LR, RecLayout LE, uint32_t* rAdd, uint32_t* rMax, double* rF64, uint32_t* bAdd, double* bF64,
+                  const uint32_t* __restrict__ cAdd, const double* __restrict__ cF64) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int l = l0; l <= l1; ++l) {
+    const int beg = levelOff[l], cnt = levelOff[l + 1] - beg;
+    for (int w = warp; w < cnt; w += 32) {
+      const int4 t = trip[beg + w];
+      const size_t z = t.x, x = t.y, y = t.z;
+      for (int i = lane; i < LR.nAdd; i += 32) rAdd[z * LR.nAdd + i] = rAdd[x * LR.nAdd + i] + rAdd[y * LR.nAdd + i];
+      for (int i = lane; i < LR.nMax; i += 32) rMax[z * LR.nMax + i] = max(rMax[x * LR.nMax + i], rMax[y * LR.nMax + i]);
+      for (int i = lane; i < LR.nF64; i += 32) rF64[z * LR.nF64 + i] = rF64[x * LR.nF64 + i] + rF64[y * LR.nF64 + i];
+      for (int i = lane; i < LE.nAdd; i += 32) bAdd[z * LE.nAdd + i] = bAdd[x * LE.nAdd + i] + bAdd[y * LE.nAdd + i] - cAdd[z * LE.nAdd + i];
+      for (int i = lane; i < LE.nF64; i += 32) bF64[z * LE.nF64 + i] = bF64[x * LE.nF64 + i] + bF64[y * LE.nF64 + i] - cF64[z * LE.nF64 + i];
+    }
+    __syncthreads();  // the next level reads what this one wrote (same CTA: the barrier orders global memory too)
+  }
+}
+
 struct BcFeatView {
   int n, R, withSal, dim;
   int first, count;                    // rows [first, first + count) are written (a rank's share, shard.cu)
@@ -172,16 +195,17 @@ using namespace glia;
 static inline unsigned nblk(long long n, int per) { return (unsigned)((n + per - 1) / per); }
 
 namespace {
-struct Scratch {  // freed on scope exit
-  std::vector<void*> p;
-  ~Scratch() { for (void* q : p) cudaFree(q); }
+struct Scratch {  // the i-th request of a call reuses the handle's i-th grow-only buffer: no cudaMalloc / cudaFree after the first call
+  glia_handle* h; int next = 0;
+  explicit Scratch(glia_handle* hh) : h(hh) {}
   template <class T> cudaError_t get(T** out, size_t count, bool zero, cudaStream_t st) {
-    void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, sizeof(T) * (count ? count : 1));
+    if (next >= (int)(sizeof(h->k5) / sizeof(h->k5[0]))) return cudaErrorMemoryAllocation;
+    glia::DevBuf& b = h->k5[next++];
+    const size_t bytes = sizeof(T) * (count ? count : 1);
+    cudaError_t e = b.ensure(bytes);
     if (e != cudaSuccess) return e;
-    p.push_back(q);
-    *out = (T*)q;
-    if (zero) e = cudaMemsetAsync(q, 0, sizeof(T) * (count ? count : 1), st);
+    *out = (T*)b.p;
+    if (zero) e = cudaMemsetAsync(b.p, 0, bytes, st);
     return e;
   }
 };
@@ -213,11 +237,18 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   std::vector<int> parent(N), c0(N, -1), c1(N, -1), level(N, 0), nodeX(n), nodeY(n);
   std::vector<double> nodeSal(N, init_sal);
   for (int v = 0; v < N; ++v) parent[v] = v;
+  // keys of merged regions -> nodes: a direct table when they are dense (the reference numbers them upwards from the
+  // largest label + 1, util/struct_merge.hxx:18-21), a hash map otherwise
+  uint32_t kMin = 0xFFFFFFFFu, kMax = 0;
+  for (int i = 0; i < n; ++i) { kMin = std::min(kMin, order[3 * i + 2]); kMax = std::max(kMax, order[3 * i + 2]); }
+  const bool dense = (uint64_t)kMax - kMin < 8ull * (uint64_t)n + 1024;
+  std::vector<int> direct;
   std::unordered_map<uint32_t, int> merged;
-  merged.reserve((size_t)n * 2);
+  if (dense) direct.assign((size_t)(kMax - kMin) + 1, -1); else merged.reserve((size_t)n * 2);
+  auto set_merged = [&](uint32_t key, int node) { if (dense) direct[key - kMin] = node; else merged[key] = node; };
   auto resolve = [&](uint32_t key) -> int {
-    auto it = merged.find(key);
-    if (it != merged.end()) return it->second;
+    if (dense) { if (key >= kMin && key <= kMax && direct[key - kMin] >= 0) return direct[key - kMin]; }
+    else { auto it = merged.find(key); if (it != merged.end()) return it->second; }
     auto lb = std::lower_bound(lab.begin(), lab.end(), key);
     return (lb != lab.end() && *lb == key) ? (int)(lb - lab.begin()) : -1;
   };
@@ -231,7 +262,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
     parent[x] = parent[y] = z; c0[z] = x; c1[z] = y; nodeX[i] = x; nodeY[i] = y;
     level[z] = 1 + std::max(level[x], level[y]);
     maxLevel = std::max(maxLevel, level[z]);
-    merged[order[3 * i + 2]] = z;
+    set_merged(order[3 * i + 2], z);
     nodeSal[z] = withSal ? sal_in[i] + sal_bias : 0.0;  // hmt/bc_feat.hxx:12-26
   }
   std::vector<int> levelOff(maxLevel + 2, 0), levelNodes(n);
@@ -243,7 +274,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   ++K;
   tr.mark("k5: host tree");
   // ---- device buffers
-  Scratch S;
+  Scratch S(h);
   int *dUp, *dCntA, *dCntB, *dC0, *dC1, *dX, *dY, *dLevelNodes, *dLca, *dTopd, *dHasNM;
   double* dSal = nullptr; double* dRows;
   uint32_t *rAdd, *rMax, *bAdd, *bMax, *cAdd, *cMax, *nAdd, *nMax;
@@ -327,12 +358,25 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   }
   tr.mark("k5: boundary lca + scatter");
   // ---- per-level update of merged-region records
-  for (int l = 1; l <= maxLevel; ++l) {
+  int tail0 = maxLevel + 1;  // first level of the narrow top: every level from here on holds <= 256 nodes
+  while (tail0 > 1 && levelOff[tail0] - levelOff[tail0 - 1] <= 256) --tail0;
+  for (int l = 1; l < tail0; ++l) {
     int cnt = levelOff[l + 1] - levelOff[l];
     if (!cnt) continue;
     level_combine_kernel<<<nblk((long long)cnt * 32, 256), 256, 0, st>>>(
         dLevelNodes + levelOff[l], cnt, dC0, dC1, LR, LE, rAdd, rMax, rF64, bAdd, bF64, cAdd, cF64);
     h->launches++;
+  }
+  if (tail0 <= maxLevel) {
+    std::vector<int4> trip(n);
+    for (int i = 0; i < n; ++i) { const int z = levelNodes[i]; trip[i] = make_int4(z, c0[z], c1[z], 0); }
+    int4* dTrip; int* dLevelOff;
+    CK(S.get(&dTrip, (size_t)n, false, st)); CK(S.get(&dLevelOff, levelOff.size(), false, st));
+    CK(cudaMemcpyAsync(dTrip, trip.data(), sizeof(int4) * (size_t)n, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(dLevelOff, levelOff.data(), 4 * levelOff.size(), cudaMemcpyHostToDevice, st));
+    level_tail_kernel<<<1, 1024, 0, st>>>(dTrip, dLevelOff, tail0, maxLevel, LR, LE, rAdd, rMax, rF64, bAdd, bF64, cAdd, cF64);
+    h->launches++;
+    CK(cudaStreamSynchronize(st));  // trip is a local
   }
   tr.mark("k5: level combine");
   // ---- medians (GLIA_USE_MEDIAN_AS_FEATS): every set of a row is a union of base segments named by the tree
@@ -433,7 +477,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   h->launches++;
   CK(cudaGetLastError());
   tr.mark("k5: rows kernel");
-  if (!h->prm.device_pointers && count) CK(cudaMemcpyAsync(rows, dRows, 8 * (size_t)count * dim, cudaMemcpyDeviceToHost, st));
+  if (!h->prm.device_pointers && count) { int s = glia_copy_to_host(h, rows, dRows, 8 * (size_t)count * dim); if (s != GLIA_OK) return s; }
   CK(cudaStreamSynchronize(st));
   tr.mark("k5: rows to host");
   if (tr.on) fprintf(stderr, "[glia trace] k5: %d merges, %d levels\n", n, maxLevel);

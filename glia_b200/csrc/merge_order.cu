@@ -40,7 +40,11 @@ __global__ void __launch_bounds__(MERGE_TPB)
 merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __restrict__ stage,
                    int stageWords, const RfNode16* __restrict__ nodes,
                    const int* __restrict__ treeOff, const RfDist dist, int labelIdx,
-                   double* __restrict__ rows, double* __restrict__ sal, const double* __restrict__ med, int nMed) {
+                   double* __restrict__ rows, double* __restrict__ sal, const double* __restrict__ med, int nMed,
+                   double* __restrict__ rowsHost) {
+  // stage / sal / med / rowsHost are pinned HOST buffers read and written in place (unified addressing): a merge is
+  // one launch and one synchronisation, no separate copies (58 -> ~25 us per merge on the chain's critical path);
+  // rows is device scratch (the row is re-read for the forest walk).
   extern __shared__ __align__(16) double srow[];
   __shared__ int shits;
   const int w = blockIdx.x;
@@ -67,7 +71,7 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
                   med ? med + (size_t)w * nMed : nullptr);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < F.dim; i += MERGE_TPB) srow[i] = row[i];
+  for (int i = threadIdx.x; i < F.dim; i += MERGE_TPB) { const double v = row[i]; srow[i] = v; if (rowsHost) rowsHost[(size_t)w * F.dim + i] = v; }
   __syncthreads();
   int hits = 0;
   const int mdl = dist.pick(srow), tb = dist.begin(mdl), ntree = dist.end(mdl) - tb;  // alg/rf.hxx:97-98
@@ -264,11 +268,11 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
   const int stageWords = 2 * regW + 4 * edgeW;
   size_t capBatch = 0;
   uint32_t* hStage = nullptr; double* hSal = nullptr; double* hRows = nullptr;
-  uint32_t* dStage = nullptr; double* dSal = nullptr; double* dRows = nullptr; double* dMed = nullptr;
+  double* dRows = nullptr; double* hMed = nullptr;
   auto release = [&]() {
-    if (hStage) cudaFreeHost(hStage); if (hSal) cudaFreeHost(hSal); if (hRows) cudaFreeHost(hRows);
-    if (dStage) cudaFree(dStage); if (dSal) cudaFree(dSal); if (dRows) cudaFree(dRows); if (dMed) cudaFree(dMed);
-    hStage = nullptr; hSal = nullptr; hRows = nullptr; dStage = nullptr; dSal = nullptr; dRows = nullptr; dMed = nullptr;
+    if (hStage) cudaFreeHost(hStage); if (hSal) cudaFreeHost(hSal); if (hRows) cudaFreeHost(hRows); if (hMed) cudaFreeHost(hMed);
+    if (dRows) cudaFree(dRows);
+    hStage = nullptr; hSal = nullptr; hRows = nullptr; hMed = nullptr; dRows = nullptr;
   };
   auto ensure_batch = [&](size_t m) -> cudaError_t {
     if (m <= capBatch) return cudaSuccess;
@@ -278,9 +282,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     if ((e = cudaMallocHost((void**)&hStage, 4 * capBatch * stageWords)) != cudaSuccess) return e;
     if ((e = cudaMallocHost((void**)&hSal, 8 * capBatch)) != cudaSuccess) return e;
     if ((e = cudaMallocHost((void**)&hRows, 8 * capBatch * dim)) != cudaSuccess) return e;
-    if ((e = cudaMalloc((void**)&dStage, 4 * capBatch * stageWords)) != cudaSuccess) return e;
-    if ((e = cudaMalloc((void**)&dSal, 8 * capBatch)) != cudaSuccess) return e;
-    if (nMed && (e = cudaMalloc((void**)&dMed, 8 * capBatch * nMed)) != cudaSuccess) return e;
+    if (nMed && (e = cudaMallocHost((void**)&hMed, 8 * capBatch * nMed)) != cudaSuccess) return e;
     return cudaMalloc((void**)&dRows, 8 * capBatch * dim);
   };
   struct Guard { decltype(release)& r; ~Guard() { r(); } } guard{release};
@@ -480,17 +482,13 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
           q[0] = mw[nRi + i]; q[1] = my[nRi + i]; q[2] = rz[nRi + i]; q[3] = rz[nRi + nBi + i];
         }
       }
-      CK(cudaMemcpyAsync(dMed, med.data(), 8 * med.size(), cudaMemcpyHostToDevice, st));
-      CK(cudaStreamSynchronize(st));  // med is a local
+      memcpy(hMed, med.data(), 8 * med.size());
     }
     const double tC = trace ? now() : 0.0;
-    CK(cudaMemcpyAsync(dStage, hStage, 4 * m * stageWords, cudaMemcpyHostToDevice, st));
     merge_batch_kernel<<<(unsigned)m, MERGE_TPB, 8 * (size_t)dim, st>>>(
-        h->fc, (int)m, dStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, dSal,
-        nMed ? dMed : nullptr, nMed);
+        h->fc, (int)m, hStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, hSal,
+        nMed ? hMed : nullptr, nMed, rows ? hRows : nullptr);
     h->launches++;
-    CK(cudaMemcpyAsync(hSal, dSal, 8 * m, cudaMemcpyDeviceToHost, st));
-    if (rows) CK(cudaMemcpyAsync(hRows, dRows, 8 * m * dim, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     const double tD = trace ? now() : 0.0;
     nfeat += (long long)m;
