@@ -36,7 +36,7 @@ class Params(C.Structure):
         ("label_bound", C.c_uint32), ("edge_capacity", C.c_uint64),
         ("z_begin", C.c_int), ("z_end", C.c_int), ("halo_lo", C.c_int), ("halo_hi", C.c_int),
         ("stream", C.c_void_p),
-        ("use_hist_feat", C.c_int), ("use_median_feat", C.c_int),
+        ("use_hist_feat", C.c_int), ("use_median_feat", C.c_int), ("contour_only", C.c_int),
     ]
 
 
@@ -151,7 +151,8 @@ class FeatureConfig:
     --ns, --logs, --simpf).  Each image entry: (array-or-device-address, bins, lo, hi)."""
 
     def __init__(self, rimgs=(), rlimgs=(), bimgs=(), thr=(0.2, 0.5, 0.8), normalize=False,
-                 use_log=False, simple=False, use_hist=False, use_median=False):
+                 use_log=False, simple=False, use_hist=False, use_median=False, contour_only=False):
+        self.contour_only = contour_only  # TRegionMap(..., onlyContour=true): masked-out voxels are classified too
         self.rimgs, self.rlimgs, self.bimgs = list(rimgs), list(rlimgs), list(bimgs)
         self.thr = list(thr)
         self.normalize, self.use_log, self.simple = normalize, use_log, simple
@@ -303,6 +304,7 @@ class MergeTreeBuilder:
             p.thr[i] = t
         p.normalize, p.use_log, p.simple = int(cfg.normalize), int(cfg.use_log), int(cfg.simple)
         p.use_hist_feat, p.use_median_feat = int(getattr(cfg, "use_hist", False)), int(getattr(cfg, "use_median", False))
+        p.contour_only = int(getattr(cfg, "contour_only", False))
         p.device_pointers, p.device = int(device_pointers), device
         p.label_bound, p.edge_capacity = label_bound, edge_capacity
         if slab is not None:

@@ -80,6 +80,7 @@ extern "C" int glia_b200_create(const glia_params* p, glia_handle** out) {
   VoxParams& P = h->vp;
   memset(&P, 0, sizeof(P));
   memset(&h->vc, 0, sizeof(h->vc));
+  P.contourOnly = p->contour_only != 0;
   P.ndim = p->ndim; P.X = h->KX; P.Y = h->KY; P.Z = h->KZ;
   P.zBegin = zb; P.zEnd = ze; P.zBuf0 = zb - hl; P.zBufN = (ze + hh) - (zb - hl);
   h->nvoxBuf = (size_t)P.X * P.Y * P.zBufN;

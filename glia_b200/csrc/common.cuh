@@ -40,6 +40,7 @@ struct VoxParams {
   const uint32_t* mask;  // may be null
   const float* pb;
   int ndim;
+  int contourOnly;  // glia_params.contour_only: masked-out voxels are still source voxels (the mask hides neighbours only)
   int X, Y, Z;      // full (global) extent; Z == 1 and Y == rows when ndim == 2 (see voxel_pass.cu)
   int zBegin, zEnd; // owned planes (global z)
   int zBuf0;        // global z of buffer plane 0

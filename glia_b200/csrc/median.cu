@@ -20,10 +20,10 @@ namespace glia {
 // One 64-bit key per voxel: (region index << 32 | value key); masked voxels sort behind the last region.
 __global__ void med_region_keys_kernel(const uint32_t* __restrict__ labels, const uint32_t* __restrict__ mask,
                                        const float* __restrict__ img, const uint32_t* __restrict__ rank, size_t n,
-                                       uint32_t R, unsigned long long* __restrict__ keys) {
+                                       uint32_t R, unsigned long long* __restrict__ keys, int contourOnly) {
   size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (p >= n) return;
-  if (mask && mask[p] == 0) { keys[p] = (unsigned long long)R << 32; return; }
+  if (mask && mask[p] == 0 && !contourOnly) { keys[p] = (unsigned long long)R << 32; return; }
   keys[p] = ((unsigned long long)rank[labels[p]] << 32) | f2ord(img[p]);
 }
 
@@ -33,12 +33,12 @@ __global__ void med_region_keys_kernel(const uint32_t* __restrict__ labels, cons
 __global__ void med_edge_keys_kernel(const uint32_t* __restrict__ labels, const uint32_t* __restrict__ mask,
                                      const float* __restrict__ img, const uint32_t* __restrict__ rank,
                                      const int* __restrict__ row, const int* __restrict__ eb, int D, int X, int Y, int Z,
-                                     uint32_t E, unsigned long long* __restrict__ keys) {
+                                     uint32_t E, unsigned long long* __restrict__ keys, int contourOnly) {
   const size_t n = (size_t)X * Y * Z;
   size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (p >= n) return;
   unsigned long long key = (unsigned long long)E << 32;
-  if (!mask || mask[p] != 0) {
+  if (!mask || mask[p] != 0 || contourOnly) {
     const int x = (int)(p % X), y = (int)((p / X) % Y), z = (int)(p / ((size_t)X * Y));
     const int c[3] = {x, y, z}, ext[3] = {X, Y, Z};
     const size_t stride[3] = {1, (size_t)X, (size_t)X * Y};
@@ -220,13 +220,13 @@ int glia_median_build(glia_handle* h) {
   };
   int s;
   for (int i = 0; i < prm.n_rimg; ++i) {
-    med_region_keys_kernel<<<nblk((long long)n, 256), 256, 0, st>>>(P.labels, P.mask, h->vc.reg[i].data, h->rank.as<uint32_t>(), n, (uint32_t)R, ka);
+    med_region_keys_kernel<<<nblk((long long)n, 256), 256, 0, st>>>(P.labels, P.mask, h->vc.reg[i].data, h->rank.as<uint32_t>(), n, (uint32_t)R, ka, P.contourOnly);
     h->launches++;
     if ((s = sort_into(R, h->medRKeys[i], h->medRStart.as<long long>(), i == 0))) return s;
   }
   for (int j = 0; j < prm.n_bimg && E > 0; ++j) {
     med_edge_keys_kernel<<<nblk((long long)n, 256), 256, 0, st>>>(P.labels, P.mask, h->vc.edge[j].data, h->rank.as<uint32_t>(),
-                                                                   h->row.as<int>(), h->eb.as<int>(), D, X, Y, Z, (uint32_t)E, ka);
+                                                                   h->row.as<int>(), h->eb.as<int>(), D, X, Y, Z, (uint32_t)E, ka, P.contourOnly);
     h->launches++;
     if ((s = sort_into(E, h->medEKeys[j], h->medEStart.as<long long>(), j == 0))) return s;
   }

@@ -162,8 +162,8 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
       int gx = x0 - GLIA_TILE_XOFF + cx, gy = y0 - hy + cy, gz = z0 - 1 + cz;
       int bz = gz - P.zBuf0;
       bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 && bz < P.zBufN;
-      if (ok && P.mask && msk[i] == 0) ok = false;
-      valid[i] = ok ? 1 : 0;
+      // 1 = in the volume and unmasked, 2 = in the volume but masked out (a source voxel only in contour-only mode)
+      valid[i] = !ok ? 0 : ((P.mask && msk[i] == 0) ? 2 : 1);
     }
   } else {
     // ---- stage label + validity tile (halo 1)
@@ -175,13 +175,14 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
       bool ok = gx >= 0 && gx < P.X && gy >= 0 && gy < P.Y && gz >= 0 && gz < P.Z && bz >= 0 &&
                 bz < P.zBufN;
       uint32_t l = 0;
+      unsigned char v = 0;
       if (ok) {
         size_t q = (size_t)bz * strideZ + (size_t)gy * strideY + gx;
-        if (P.mask && __ldg(P.mask + q) == 0) ok = false;
-        else l = __ldg(P.labels + q);
+        v = (P.mask && __ldg(P.mask + q) == 0) ? 2 : 1;
+        if (v == 1 || P.contourOnly) l = __ldg(P.labels + q);
       }
       lab[i] = l;
-      valid[i] = ok ? 1 : 0;
+      valid[i] = v;
     }
   }
   __syncthreads();
@@ -199,13 +200,14 @@ voxel_pass_generic(const __grid_constant__ VoxParams P, const __grid_constant__ 
       int gz = z0 + zz;
       if (gz >= P.zEnd) break;
       int c = ((zz + 1) * SY + (ty + hy)) * SX + tx + GLIA_TILE_XOFF;
-      if (!valid[c]) continue;
+      // contour-only region maps classify masked-out voxels too (genContourMap over the image, util/struct.hxx:129-146)
+      if (!(valid[c] == 1 || (valid[c] == 2 && P.contourOnly))) continue;
       uint32_t me = lab[c];
       if (me == 0xFFFFFFFFu) { atomicOr(P.overflow, 2); continue; }  // reserved: the empty-slot marker of the tables
       // type/neighbor.hxx:78-88 order: d0-, d0+, d1-, d1+, d2-, d2+
       int nvalid = 0; bool found = false; uint32_t nb = 0;
 #define GLIA_VISIT(off)                                                   \
-  { int q_ = c + (off); if (valid[q_]) { ++nvalid; uint32_t l_ = lab[q_]; \
+  { int q_ = c + (off); if (valid[q_] == 1) { ++nvalid; uint32_t l_ = lab[q_]; \
       if (!found && l_ != me) { found = true; nb = l_; } } }
       GLIA_VISIT(-1) GLIA_VISIT(+1)
       if (hy) { GLIA_VISIT(-SX) GLIA_VISIT(+SX) }

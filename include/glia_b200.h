@@ -88,6 +88,11 @@ typedef struct glia_params {
    *                   rows the pair boundary's median (hmt/bc_feat.hxx:252-268).  median = the n/2-th order
    *                   statistic (util/stats.hxx:83-91).  Needs the whole volume in one handle (no z-slab). */
   int use_hist_feat, use_median_feat;
+  /* TRegionMap(image, mask, onlyContour = true) (type/region_map.hxx:54-58), as hmt/main_merge_order_pb.cxx:23 builds
+   * it: the image-driven genContourMap (util/struct.hxx:129-146) classifies EVERY voxel, masked-out ones included -
+   * the mask then only hides neighbours.  Region records count those voxels too; only boundary records are
+   * meaningful in this mode (which is all glia_b200_merge_order_pb reads). */
+  int contour_only;
 } glia_params;
 
 typedef struct glia_handle glia_handle;

@@ -167,7 +167,7 @@ go_state* go_build(const go_cfg* cfg, const uint32_t* L, const uint32_t* M, cons
   /* labels present (unmasked voxels only): util/struct.hxx:61-92 */
   uint32_t* tmp = (uint32_t*)malloc(4 * (N ? N : 1));
   size_t nu = 0;
-  for (size_t p = 0; p < N; ++p) if (!M || M[p] != 0) tmp[nu++] = L[p];
+  for (size_t p = 0; p < N; ++p) if (!M || M[p] != 0 || cfg->contour_only) tmp[nu++] = L[p];
   qsort(tmp, nu, 4, cmp_u32);
   int R = 0;
   for (size_t i = 0; i < nu; ++i) if (i == 0 || tmp[i] != tmp[i - 1]) tmp[R++] = tmp[i];
@@ -198,7 +198,7 @@ go_state* go_build(const go_cfg* cfg, const uint32_t* L, const uint32_t* M, cons
     for (xyz[1] = 0; xyz[1] < dims[1]; ++xyz[1])
       for (xyz[0] = 0; xyz[0] < dims[0]; ++xyz[0], ++p) {
         cls[p] = 0;
-        if (M && M[p] == 0) continue;
+        if (M && M[p] == 0 && !cfg->contour_only) continue;
         int a = find_u32(s->label, R, L[p]);
         s->cnt[a]++;
         for (int d = 0; d < s->D; ++d) { /* alg/geometry.hxx:21-39 */
@@ -259,7 +259,7 @@ go_state* go_build(const go_cfg* cfg, const uint32_t* L, const uint32_t* M, cons
       for (int r = 0; r < R; ++r) s->rvals[i][r] = (float*)malloc(4 * (size_t)(s->cnt[r] ? s->cnt[r] : 1));
       memset(cur, 0, sizeof(size_t) * ((size_t)R + 1));
       for (p = 0; p < N; ++p) {
-        if (M && M[p] == 0) continue;
+        if (M && M[p] == 0 && !cfg->contour_only) continue;
         int a = find_u32(s->label, R, L[p]);
         s->rvals[i][a][cur[a]++] = s->rs[i].img[p];
       }
@@ -836,4 +836,206 @@ int go_bc_feat(go_state* s, const uint32_t* order, int n, const double* sal_in, 
   for (int i = 0; i < n; ++i) free(msets[i].base);
   free(mkeys); free(msets); free(msal);
   return status;
+}
+
+/* ------------------------------------------------------------------------
+ * merge order from the boundary probability alone
+ * (hmt/main_merge_order_pb.cxx:14-40; util/struct_merge.hxx:36-136) and
+ * pre_merge (gadget/main_pre_merge.cxx:7-87).  Needs bimg[0] == pb (pair
+ * boundary sums / values) and, for pre_merge, rimg[0] == pb (region means).
+ * Item data = (mean, n) of the pair boundary (struct_merge.hxx:44-56), or the
+ * values themselves for the median variant (:100-112); a merge combines the
+ * data of the two items it replaces without touching the image again
+ * (:62-76, :119-126).  Table / queue semantics as in go_greedy.
+ * ---------------------------------------------------------------------- */
+typedef struct { uint32_t r0, r1; double sal; uint64_t seq; double mean; long n; float* v; size_t nv; } pitem;
+typedef struct { pitem* it; int n, cap; } ptable;
+static int p_lower(const ptable* t, uint32_t r0, uint32_t r1) {
+  int lo = 0, hi = t->n;
+  while (lo < hi) {
+    int m = (lo + hi) >> 1;
+    const pitem* x = &t->it[m];
+    if (x->r0 < r0 || (x->r0 == r0 && x->r1 < r1)) lo = m + 1; else hi = m;
+  }
+  return lo;
+}
+static int p_find(const ptable* t, uint32_t r0, uint32_t r1) {
+  int i = p_lower(t, r0, r1);
+  return (i < t->n && t->it[i].r0 == r0 && t->it[i].r1 == r1) ? i : -1;
+}
+static void p_insert(ptable* t, pitem v) {
+  if (t->n == t->cap) { t->cap = t->cap ? 2 * t->cap : 64; t->it = (pitem*)realloc(t->it, sizeof(pitem) * t->cap); }
+  int i = p_lower(t, v.r0, v.r1);
+  memmove(&t->it[i + 1], &t->it[i], sizeof(pitem) * (size_t)(t->n - i));
+  t->it[i] = v; t->n++;
+}
+static void p_erase(ptable* t, int i) {
+  free(t->it[i].v);
+  memmove(&t->it[i], &t->it[i + 1], sizeof(pitem) * (size_t)(t->n - i - 1));
+  t->n--;
+}
+static double values_amedian(const float* v, size_t n) { /* util/stats.hxx:83-91 (n > 0) */
+  float* c = (float*)malloc(4 * n);
+  memcpy(c, v, 4 * n);
+  qsort(c, n, 4, cmp_f32);
+  double r = c[n / 2];
+  free(c);
+  return r;
+}
+typedef struct {
+  const go_state* s; uint32_t maxKey; int nthr; const int* thr; double rpbThr;
+  uint64_t* size; double* sum; /* per region id (base index, then R + merge index) */
+  double* rpb; uint8_t* has_rpb;
+} premerge_ctx;
+static int key_id(const go_state* s, uint32_t maxKey, uint32_t key) {
+  return key <= maxKey ? find_u32(s->label, s->R, key) : s->R + (int)(key - maxKey - 1);
+}
+/* gadget/main_pre_merge.cxx:26-76 */
+static int premerge_cond(premerge_ctx* c, uint32_t k0, uint32_t k1) {
+  int id[2] = {key_id(c->s, c->maxKey, k0), key_id(c->s, c->maxKey, k1)};
+  if (c->size[id[0]] > c->size[id[1]]) { int t = id[0]; id[0] = id[1]; id[1] = t; }
+  if ((long long)c->size[id[0]] < c->thr[0]) return 1;
+  if (c->nthr > 1) {
+    for (int k = 0; k < 2; ++k) {
+      if ((long long)c->size[id[k]] < c->thr[1]) {
+        if (!c->has_rpb[id[k]]) { c->rpb[id[k]] = sdivide(c->sum[id[k]], (double)c->size[id[k]], 0.0); c->has_rpb[id[k]] = 1; }
+        if (c->rpb[id[k]] > c->rpbThr) return 1;
+      }
+    }
+  }
+  return 0;
+}
+typedef struct { double sal; uint64_t seq; int idx; } prio;
+static int cmp_prio_desc(const void* a, const void* b) {
+  const prio* x = (const prio*)a; const prio* y = (const prio*)b;
+  if (x->sal != y->sal) return x->sal > y->sal ? -1 : 1;
+  return x->seq > y->seq ? -1 : (x->seq < y->seq);
+}
+
+static int pb_greedy(go_state* s, int type, premerge_ctx* pc, uint32_t* order, double* sal) {
+  int R = s->R;
+  if (R == 0 || s->cfg.n_bimg < 1) return 0;
+  if (type == 1 && !s->cfg.use_median) return -1;
+  uint32_t maxKey = s->label[R - 1];
+  ptable tb = {0, 0, 0};
+  uint64_t seq = 0;
+  /* init: mutual base pairs; pair boundary = (a->b) then (b->a) (util/struct.hxx:10-16) */
+  for (int e = 0; e < s->E; ++e) {
+    int a = s->ea[e], b = s->eb[e], rv = s->rev[e];
+    if (!(a < b && rv >= 0)) continue;
+    pitem v; memset(&v, 0, sizeof(v));
+    v.r0 = s->label[a]; v.r1 = s->label[b];
+    v.n = (long)s->ecnt[e] + (long)s->ecnt[rv];
+    v.mean = sdivide(s->estat[0][e].s + s->estat[0][rv].s, (double)v.n, 0.0);
+    if (type == 1) {
+      v.nv = (size_t)v.n; v.v = (float*)malloc(4 * (v.nv ? v.nv : 1));
+      memcpy(v.v, s->evals[0][e], 4 * (size_t)s->ecnt[e]);
+      memcpy(v.v + s->ecnt[e], s->evals[0][rv], 4 * (size_t)s->ecnt[rv]);
+      v.sal = -values_amedian(v.v, v.nv);
+    } else v.sal = -v.mean;
+    p_insert(&tb, v);
+  }
+  for (int i = 0; i < tb.n; ++i) tb.it[i].seq = seq++; /* queue insertion in table order (boundary_table.hxx:108-112) */
+  int M = 0;
+  uint32_t keyToAssign = maxKey + 1;
+  while (tb.n > 0) {
+    int top = -1;
+    if (!pc) {
+      top = 0;
+      for (int i = 1; i < tb.n; ++i)
+        if (tb.it[i].sal > tb.it[top].sal || (tb.it[i].sal == tb.it[top].sal && tb.it[i].seq > tb.it[top].seq)) top = i;
+    } else { /* first item in queue order that passes the condition (boundary_table.hxx:47-52) */
+      prio* q = (prio*)malloc(sizeof(prio) * (size_t)tb.n);
+      for (int i = 0; i < tb.n; ++i) { q[i].sal = tb.it[i].sal; q[i].seq = tb.it[i].seq; q[i].idx = i; }
+      qsort(q, (size_t)tb.n, sizeof(prio), cmp_prio_desc);
+      for (int i = 0; i < tb.n && top < 0; ++i) if (premerge_cond(pc, tb.it[q[i].idx].r0, tb.it[q[i].idx].r1)) top = q[i].idx;
+      free(q);
+      if (top < 0) break;
+    }
+    uint32_t r0 = tb.it[top].r0, r1 = tb.it[top].r1, r2 = keyToAssign++;
+    order[3 * M] = r0; order[3 * M + 1] = r1; order[3 * M + 2] = r2;
+    sal[M] = tb.it[top].sal;
+    ++M;
+    if (pc) { /* rmap.merge(r0, r1, r2): sizes and sums of the merged region */
+      int i0 = key_id(s, maxKey, r0), i1 = key_id(s, maxKey, r1), i2 = R + (int)(r2 - maxKey - 1);
+      pc->size[i2] = pc->size[i0] + pc->size[i1];
+      pc->sum[i2] = pc->sum[i0] + pc->sum[i1];
+    }
+    p_erase(&tb, top);
+    int i = 0;
+    while (i < tb.n && tb.it[i].r0 <= r1) { /* boundary_table.hxx:127-166 */
+      uint32_t k0 = tb.it[i].r0, k1 = tb.it[i].r1, rs;
+      if (k0 == r0 || k0 == r1) rs = k1;
+      else if (k1 == r0 || k1 == r1) rs = k0;
+      else { ++i; continue; }
+      int j0 = p_find(&tb, rs < r0 ? rs : r0, rs < r0 ? r0 : rs);
+      int j1 = p_find(&tb, rs < r1 ? rs : r1, rs < r1 ? r1 : rs);
+      pitem v; memset(&v, 0, sizeof(v));
+      v.r0 = rs; v.r1 = r2;
+      double acc = 0.0; long n = 0; /* struct_merge.hxx:62-76: 0s then 1s */
+      if (j0 >= 0) { acc += tb.it[j0].mean * tb.it[j0].n; n += tb.it[j0].n; }
+      if (j1 >= 0) { acc += tb.it[j1].mean * tb.it[j1].n; n += tb.it[j1].n; }
+      v.n = n; v.mean = sdivide(acc, (double)n, 0.0);
+      if (type == 1) {
+        v.nv = (j0 >= 0 ? tb.it[j0].nv : 0) + (j1 >= 0 ? tb.it[j1].nv : 0);
+        v.v = (float*)malloc(4 * (v.nv ? v.nv : 1));
+        size_t o = 0;
+        if (j0 >= 0) { memcpy(v.v, tb.it[j0].v, 4 * tb.it[j0].nv); o = tb.it[j0].nv; }
+        if (j1 >= 0) memcpy(v.v + o, tb.it[j1].v, 4 * tb.it[j1].nv);
+        v.sal = -values_amedian(v.v, v.nv);
+      } else v.sal = -v.mean;
+      v.seq = seq++;
+      p_insert(&tb, v);
+      int j;
+      j = p_find(&tb, rs < r0 ? rs : r0, rs < r0 ? r0 : rs); if (j >= 0) p_erase(&tb, j);
+      j = p_find(&tb, rs < r1 ? rs : r1, rs < r1 ? r1 : rs); if (j >= 0) p_erase(&tb, j);
+      i = p_lower(&tb, k0, k1);
+    }
+  }
+  for (int i = 0; i < tb.n; ++i) free(tb.it[i].v);
+  free(tb.it);
+  return M;
+}
+
+int go_merge_order_pb(go_state* s, int type, uint32_t* order, double* sal) {
+  return pb_greedy(s, type, NULL, order, sal);
+}
+
+/* labels_out: the input labels with every merged base region renamed to its final key
+ * (transformKeys, util/struct_merge.hxx:188-209; transformImage, util/image.hxx:246-259). */
+int go_pre_merge(go_state* s, const int* size_thr, int n_thr, double rpb_thr, uint32_t* order, double* sal,
+                 const uint32_t* labels_in, const uint32_t* mask, uint32_t* labels_out) {
+  int R = s->R;
+  if (R <= 0) return 0;
+  if (n_thr < 1 || s->cfg.n_rimg < 1) return -1;
+  premerge_ctx c;
+  c.s = s; c.maxKey = s->label[R - 1]; c.nthr = n_thr; c.thr = size_thr; c.rpbThr = rpb_thr;
+  c.size = (uint64_t*)calloc(2 * (size_t)R, 8); c.sum = (double*)calloc(2 * (size_t)R, 8);
+  c.rpb = (double*)calloc(2 * (size_t)R, 8); c.has_rpb = (uint8_t*)calloc(2 * (size_t)R, 1);
+  for (int r = 0; r < R; ++r) { c.size[r] = s->cnt[r]; c.sum[r] = s->rstat[0][r].s; }
+  int M = pb_greedy(s, 2, &c, order, sal);
+  if (labels_out && M >= 0) {
+    /* final key of every id: follow the merges */
+    uint32_t* fin = (uint32_t*)malloc(4 * 2 * (size_t)R);
+    for (int r = 0; r < R; ++r) fin[r] = s->label[r];
+    for (int m = 0; m < M; ++m) fin[R + m] = order[3 * m + 2];
+    int* up = (int*)malloc(4 * 2 * (size_t)R);
+    for (int i = 0; i < 2 * R; ++i) up[i] = i;
+    for (int m = 0; m < M; ++m) {
+      up[key_id(s, c.maxKey, order[3 * m])] = R + m;
+      up[key_id(s, c.maxKey, order[3 * m + 1])] = R + m;
+    }
+    for (size_t p = 0; p < s->nvox; ++p) {
+      labels_out[p] = labels_in[p];
+      if (mask && mask[p] == 0) continue;
+      int a = find_u32(s->label, R, labels_in[p]);
+      if (a < 0) continue;
+      int v = a;
+      while (up[v] != v) v = up[v];
+      labels_out[p] = fin[v];
+    }
+    free(fin); free(up);
+  }
+  free(c.size); free(c.sum); free(c.rpb); free(c.has_rpb);
+  return M;
 }

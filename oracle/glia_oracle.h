@@ -36,6 +36,8 @@ typedef struct go_cfg {
   int simple;               /* --simpf (bc_feat.hxx:247-279) */
   int use_hist;             /* GLIA_USE_HISTOGRAM_AS_FEATS build (CMakeLists.txt:58-60; type/feat.hxx:608-626) */
   int use_median;           /* GLIA_USE_MEDIAN_AS_FEATS build (CMakeLists.txt:62-64; type/feat.hxx:677-810) */
+  int contour_only;         /* TRegionMap(image, mask, true): genContourMap over the image classifies masked-out
+                               voxels too (util/struct.hxx:129-146); the mask then hides neighbours only */
 } go_cfg;
 
 typedef struct go_state go_state;
@@ -77,6 +79,14 @@ int go_greedy(go_state* s, const rf_oracle* rf, go_pred_fn fn, void* ctx, uint32
 /* bc_feat stage (main_bc_feat.cxx:27-112) for a given order; sal_in may be NULL. */
 int go_bc_feat(go_state* s, const uint32_t* order, int n, const double* sal_in, double init_sal,
                double sal_bias, double* rows);
+
+/* SURVEY §8f rank 1.  merge order from the boundary probability alone (hmt/main_merge_order_pb.cxx:14-40):
+ * type 1 = approximate median (needs cfg.use_median), 2 = mean; needs bimg[0] == pb.  Returns M. */
+int go_merge_order_pb(go_state* s, int type, uint32_t* order, double* sal);
+/* pre_merge (gadget/main_pre_merge.cxx:7-87) without the final ITK relabel: order / sal of the conditional greedy run
+ * and the label image with merged regions renamed; needs rimg[0] == bimg[0] == pb.  Returns M. */
+int go_pre_merge(go_state* s, const int* size_thr, int n_thr, double rpb_thr, uint32_t* order, double* sal,
+                 const uint32_t* labels_in, const uint32_t* mask, uint32_t* labels_out);
 
 /* ---- random forest (rf_oracle.c) ---- */
 rf_oracle* rf_oracle_load(const char* path);  /* rf_old binary model file */

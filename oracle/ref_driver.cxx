@@ -20,6 +20,7 @@
 #include "hmt/bc_feat.hxx"
 #include "type/region_map.hxx"
 #include "util/struct_merge_bc.hxx"
+#include "util/struct_merge.hxx"
 #include "util/mp.hxx"
 
 using namespace glia;
@@ -44,6 +45,7 @@ struct Results {
   std::vector<uint32_t> order;       // 3 per merge
   std::vector<double> sal;
   std::vector<double> merge_rows;    // -b output: one row per merge
+  std::vector<uint32_t> out_labels;  // pre_merge: the label image after transformImage
   double t_rmap = 0, t_feat = 0, t_pred = 0, t_total = 0;
   int nthreads = 1;
 };
@@ -319,6 +321,87 @@ int glia_ref_run(
   return 0;
 }
 
+// ---- hmt/main_merge_order_pb.cxx:14-40 and gadget/main_pre_merge.cxx:7-87 ----
+// mode 4: merge_order_pb (type 1 = approximate median, 2 = mean; rmap with contours only, regions not updated).
+// mode 5: pre_merge: genMergeOrderGreedyUsingPbMean with the size / region-pb condition of main_pre_merge.cxx:26-76
+//         (restated here because it lives in a main file), transformKeys + transformImage (util/image.hxx:246-259 is
+//         behind the ITK filter includes: its 8-line loop is restated), no relabel (an ITK filter).
+int glia_ref_run_pb(int mode, const int* dims, const uint32_t* labels, const uint32_t* maskBuf, const float* pb,
+                    int type, const int* sizeThr, int nSizeThr, double rpbThreshold)
+{
+  G = Results();
+  double tStart = now();
+  auto segImage = wrap<LImage>(labels, dims);
+  LImage::Pointer mask = maskBuf ? wrap<LImage>(maskBuf, dims) : LImage::Pointer(nullptr);
+  auto pbImage = wrap<RImage>(pb, dims);
+  std::vector<TTriple<Label>> order;
+  std::vector<double> saliencies;
+  if (mode == 4) {
+    RegionMap rmap(segImage, mask, true);  // Only use contours
+    if (type == 1) {
+      genMergeOrderGreedyUsingPbApproxMedian(
+          order, saliencies, rmap, false, pbImage,
+          f_true<TBoundaryTable<std::vector<double>, RegionMap>&, TBoundaryTable<std::vector<double>, RegionMap>::iterator>,
+          f_null<std::vector<double>&, Label, Label>);
+    } else {
+      genMergeOrderGreedyUsingPbMean(
+          order, saliencies, rmap, false, pbImage,
+          f_true<TBoundaryTable<std::pair<double, int>, RegionMap>&, TBoundaryTable<std::pair<double, int>, RegionMap>::iterator>);
+    }
+  } else {
+    std::vector<int> sizeThresholds(sizeThr, sizeThr + nSizeThr);
+    RegionMap rmap(segImage, mask, false);
+    std::unordered_map<Label, double> rpbs;
+    genMergeOrderGreedyUsingPbMean(
+        order, saliencies, rmap, true, pbImage,
+        [&pbImage, &sizeThresholds, &rmap, rpbThreshold, &rpbs](
+            TBoundaryTable<std::pair<double, int>, RegionMap> const& bt,
+            TBoundaryTable<std::pair<double, int>, RegionMap>::iterator btit) {
+          Label key0 = btit->first.first;
+          Label key1 = btit->first.second;
+          auto const* pr0 = &rmap.find(key0)->second;
+          auto const* pr1 = &rmap.find(key1)->second;
+          auto sz0 = pr0->size();
+          auto sz1 = pr1->size();
+          if (sz0 > sz1) { std::swap(key0, key1); std::swap(pr0, pr1); std::swap(sz0, sz1); }
+          if (sz0 < sizeThresholds[0]) { return true; }
+          if (sizeThresholds.size() > 1) {
+            const RegionMap::Region* prs[2] = {pr0, pr1};
+            Label keys[2] = {key0, key1};
+            decltype(sz0) szs[2] = {sz0, sz1};
+            for (int k = 0; k < 2; ++k) {
+              if (szs[k] < sizeThresholds[1]) {
+                auto rpit = rpbs.find(keys[k]);
+                if (rpit != rpbs.end()) { if (rpit->second > rpbThreshold) { return true; } }
+                else {
+                  double rpb = 0.0;
+                  prs[k]->traverse([&pbImage, &rpb](RegionMap::Region::Point const& p) { rpb += pbImage->GetPixel(p); });
+                  rpb = sdivide(rpb, szs[k], 0.0);
+                  rpbs[keys[k]] = rpb;
+                  if (rpb > rpbThreshold) { return true; }
+                }
+              }
+            }
+          }
+          return false;
+        });
+    std::unordered_map<Label, Label> lmap;
+    transformKeys(lmap, order);
+    for (auto const& lp : lmap) {  // transformImage(segImage, rmap, lmap)
+      auto rit = rmap.find(lp.first);
+      if (rit != rmap.end()) {
+        rit->second.traverse([&segImage, &lp](RegionMap::Region::Point const& p) { segImage->SetPixel(p, lp.second); });
+      }
+    }
+    size_t n = segImage->GetBufferSize();
+    G.out_labels.assign(segImage->GetBufferPointer(), segImage->GetBufferPointer() + n);
+  }
+  for (auto const& m : order) { G.order.push_back(m.x0); G.order.push_back(m.x1); G.order.push_back(m.x2); }
+  G.sal = saliencies;
+  G.t_total = now() - tStart;
+  return 0;
+}
+
 // Leaf RegionFeats under the reference's own parfor (the GLIA_MT path,
 // hmt/main_bc_feat.cxx:59-69) — timing only, for the CPU baseline.
 double glia_ref_time_leaf_feats(
@@ -362,6 +445,7 @@ GETTER(cand_scores, double, cand_scores)
 GETTER(order, uint32_t, order)
 GETTER(sal, double, sal)
 GETTER(merge_rows, double, merge_rows)
+GETTER(out_labels, uint32_t, out_labels)
 int glia_ref_dim() { return G.dim; }
 int glia_ref_nthreads() { return G.nthreads; }
 double glia_ref_time(int which) {

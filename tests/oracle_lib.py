@@ -29,7 +29,7 @@ class GoCfg(C.Structure):
         ("blo", C.c_double * MAX_IMG), ("bhi", C.c_double * MAX_IMG),
         ("thr", C.c_double * MAX_THR),
         ("normalize", C.c_int), ("use_log", C.c_int), ("simple", C.c_int),
-        ("use_hist", C.c_int), ("use_median", C.c_int),
+        ("use_hist", C.c_int), ("use_median", C.c_int), ("contour_only", C.c_int),
     ]
 
 
@@ -74,6 +74,9 @@ def lib():
                                 C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p]
         L.go_bc_feat.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_double,
                                  C.c_double, C.c_void_p]
+        L.go_merge_order_pb.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.go_pre_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p]
         L.rf_oracle_load.restype = C.c_void_p
         L.rf_oracle_load.argtypes = [C.c_char_p]
         L.rf_oracle_from_arrays.restype = C.c_void_p
@@ -99,7 +102,8 @@ class FeatureConfig:
     """Mirrors the CLI options of hmt/main_merge_order_bc.cxx:172-242."""
 
     def __init__(self, rimgs=(), rlimgs=(), bimgs=(), thr=(0.2, 0.5, 0.8), normalize=False,
-                 use_log=False, simple=False, use_hist=False, use_median=False):
+                 use_log=False, simple=False, use_hist=False, use_median=False, contour_only=False):
+        self.contour_only = contour_only  # TRegionMap(..., onlyContour=true)
         # each image entry: (array float32, bins, lo, hi)
         self.rimgs, self.rlimgs, self.bimgs = list(rimgs), list(rlimgs), list(bimgs)
         self.thr = list(thr)
@@ -140,6 +144,7 @@ class Oracle:
             g.thr[i] = t
         g.normalize, g.use_log, g.simple = int(cfg.normalize), int(cfg.use_log), int(cfg.simple)
         g.use_hist, g.use_median = int(getattr(cfg, "use_hist", False)), int(getattr(cfg, "use_median", False))
+        g.contour_only = int(getattr(cfg, "contour_only", False))
         self.g = g
         self.h = lib().go_build(C.byref(g), _ptr(self.labels), _ptr(self.mask), _ptr(self.pb))
         self.R = lib().go_num_regions(self.h)
@@ -211,6 +216,25 @@ class Oracle:
             n = min(nc.value, maxc)
             res.update(cand_keys=ck[:n], cand_rows=cr[:n], cand_scores=cs[:n])
         return res
+
+    def merge_order_pb(self, type=1):
+        """hmt/main_merge_order_pb.cxx: type 1 = approximate median (cfg.use_median), 2 = mean."""
+        order = np.zeros((max(self.R, 1), 3), np.uint32)
+        sal = np.zeros(max(self.R, 1))
+        m = lib().go_merge_order_pb(self.h, type, _ptr(order), _ptr(sal))
+        assert m >= 0
+        return dict(order=order[:m], sal=sal[:m])
+
+    def pre_merge(self, size_thr, rpb_thr=0.0):
+        """gadget/main_pre_merge.cxx without the final ITK relabel."""
+        order = np.zeros((max(self.R, 1), 3), np.uint32)
+        sal = np.zeros(max(self.R, 1))
+        thr = np.ascontiguousarray(size_thr, np.int32)
+        out = np.zeros(self.labels.shape, np.uint32)
+        m = lib().go_pre_merge(self.h, _ptr(thr), len(thr), rpb_thr, _ptr(order), _ptr(sal), _ptr(self.labels),
+                               _ptr(self.mask), _ptr(out))
+        assert m >= 0
+        return dict(order=order[:m], sal=sal[:m], labels=out)
 
     def bc_feat(self, order, sal=None, init_sal=1.0, sal_bias=0.0):
         order = np.ascontiguousarray(order, np.uint32)
@@ -302,7 +326,7 @@ def ref_lib(ndim, cfg=None):
         L.glia_ref_time.restype = C.c_double
         L.glia_ref_time_leaf_feats.restype = C.c_double
         for n in ("reg_label", "reg_count", "reg_border", "edge_a", "edge_b", "edge_count",
-                  "cand_keys", "cand_rows", "cand_scores", "order", "sal", "merge_rows"):
+                  "cand_keys", "cand_rows", "cand_scores", "order", "sal", "merge_rows", "out_labels"):
             getattr(L, "glia_ref_n_" + n).restype = C.c_size_t
             getattr(L, "glia_ref_" + n).restype = C.c_void_p
         _ref[ndim] = L
@@ -321,6 +345,24 @@ def rf_pred_callback(orf):
     """(function pointer, ctx) pair scoring a row with an OracleRF without going through Python."""
     fn = C.cast(lib().rf_oracle_pred_cb, C.c_void_p)
     return fn, C.c_void_p(orf.h)
+
+
+def ref_run_pb(mode, labels, pb, mask=None, type=1, size_thr=(), rpb_thr=0.0):
+    """The compiled reference's merge_order_pb (mode 4) / pre_merge (mode 5) call sequences (oracle/ref_driver.cxx)."""
+    labels = np.ascontiguousarray(labels, np.uint32)
+    pb = np.ascontiguousarray(pb, np.float32)
+    ndim = labels.ndim
+    L = ref_lib(ndim)
+    dims = (C.c_int * 3)(*(list(labels.shape[::-1]) + [1] * (3 - ndim)))
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint32)
+    thr = (C.c_int * max(len(size_thr), 1))(*size_thr)
+    st = L.glia_ref_run_pb(C.c_int(mode), dims, _ptr(labels), _ptr(m), _ptr(pb), C.c_int(type), thr, C.c_int(len(size_thr)),
+                           C.c_double(rpb_thr))
+    assert st == 0
+    out = dict(order=_ref_get(L, "order", np.uint32).reshape(-1, 3), sal=_ref_get(L, "sal", np.float64))
+    if mode == 5:
+        out["labels"] = _ref_get(L, "out_labels", np.uint32).reshape(labels.shape)
+    return out
 
 
 def ref_run(mode, labels, pb, cfg, mask=None, pred=None, order=None, sal=None, init_sal=1.0,

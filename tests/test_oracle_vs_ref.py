@@ -287,3 +287,40 @@ def test_rf_oracle_agrees_with_sklearn_rule():
         c = e.predict(Xt).astype(int)  # class index 0/1
         sk_votes[np.arange(len(Xt)), c] += 1
     assert np.array_equal(votes, sk_votes)
+
+
+# ---- merge_order_pb and pre_merge
+PB_CASES = [((24, 28), 40, 41, False), ((31, 22), 25, 42, True), ((9, 10, 11), 20, 43, False), ((8, 12, 10), 14, 44, True)]
+
+
+@pytest.mark.parametrize("type_", [1, 2])
+@pytest.mark.parametrize("case", PB_CASES)
+def test_merge_order_pb_matches_reference(case, type_):
+    """hmt/main_merge_order_pb.cxx:14-40 (type 1 = approximate median, 2 = mean): order and saliencies bit for bit
+    (dyadic pb; tie-heavy: pb takes 256 levels, medians collide all the time)."""
+    shape, nl, seed, um = case
+    if not _have_ref(len(shape)):
+        pytest.skip("oracle/_ref not available")
+    lab, pb, mask = _make(shape, nl, seed, um)
+    ref = ol.ref_run_pb(4, lab, pb, mask=mask, type=type_)
+    o = ol.Oracle(lab, pb, ol.default_config(pb, use_median=(type_ == 1), contour_only=True), mask=mask)
+    res = o.merge_order_pb(type_)
+    assert len(ref["order"]) > 3
+    assert np.array_equal(res["order"], ref["order"])
+    assert np.array_equal(res["sal"], ref["sal"])
+
+
+@pytest.mark.parametrize("thr", [(30,), (25, 60)])
+@pytest.mark.parametrize("case", PB_CASES)
+def test_pre_merge_matches_reference(case, thr):
+    """gadget/main_pre_merge.cxx:7-87 (no relabel): the conditional greedy run and the renamed label image."""
+    shape, nl, seed, um = case
+    if not _have_ref(len(shape)):
+        pytest.skip("oracle/_ref not available")
+    lab, pb, mask = _make(shape, nl, seed, um)
+    ref = ol.ref_run_pb(5, lab, pb, mask=mask, size_thr=thr, rpb_thr=0.4)
+    o = ol.Oracle(lab, pb, ol.default_config(pb), mask=mask)
+    res = o.pre_merge(thr, 0.4)
+    assert np.array_equal(res["order"], ref["order"])
+    assert np.array_equal(res["sal"], ref["sal"])
+    assert np.array_equal(res["labels"], ref["labels"])
