@@ -63,7 +63,7 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_tune", "glia_b200_candidate_ties", "glia_b200_set_tie_orientation",
            "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
            "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms",
-           "glia_b200_bc_feat_sharded"]
+           "glia_b200_bc_feat_sharded", "glia_b200_merge_order_pb", "glia_b200_pre_merge"]
 
 
 def lib():
@@ -102,6 +102,8 @@ def lib():
         L.glia_b200_merge_order_bc.argtypes = [vp, vp, vp, vp, vp, C.POINTER(C.c_int64),
                                                C.POINTER(C.c_int64)]
         L.glia_b200_bc_feat.argtypes = [vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp]
+        L.glia_b200_merge_order_pb.argtypes = [vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
+        L.glia_b200_pre_merge.argtypes = [vp, vp, C.c_int, C.c_double, vp, vp, C.POINTER(C.c_int64), vp]
         L.glia_b200_bc_feat_sharded.argtypes = [vp, vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp,
                                                 C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.glia_b200_rf_load.argtypes = [C.c_char_p, C.c_int, C.POINTER(vp)]
@@ -444,6 +446,27 @@ class MergeTreeBuilder:
         m = nm.value
         return dict(order=order[:m], sal=sal[:m], rows=None if rows is None else rows[:m],
                     n_featurized=nf.value)
+
+    def merge_order_pb(self, type=1):
+        """hmt/main_merge_order_pb.cxx: type 1 = approximate median (cfg.use_median), 2 = mean."""
+        M = max(self.R - 1, 1)
+        order = np.zeros((M, 3), np.uint32)
+        sal = np.zeros(M)
+        nm = C.c_int64()
+        self._check(lib().glia_b200_merge_order_pb(self.h, type, _addr(order), _addr(sal), C.byref(nm)))
+        return dict(order=order[:nm.value], sal=sal[:nm.value])
+
+    def pre_merge(self, size_thr, rpb_thr=0.0, want_labels=True):
+        """gadget/main_pre_merge.cxx (without the ITK relabel): order, saliencies and the renamed label volume."""
+        M = max(self.R - 1, 1)
+        order = np.zeros((M, 3), np.uint32)
+        sal = np.zeros(M)
+        thr = np.ascontiguousarray(size_thr, np.int32)
+        out = np.zeros(self.shape, np.uint32) if want_labels else None
+        nm = C.c_int64()
+        self._check(lib().glia_b200_pre_merge(self.h, _addr(thr), len(thr), C.c_double(rpb_thr), _addr(order), _addr(sal),
+                                              C.byref(nm), _addr(out)))
+        return dict(order=order[:nm.value], sal=sal[:nm.value], labels=out)
 
     def bc_feat(self, order, sal=None, init_sal=1.0, sal_bias=0.0):
         order = np.ascontiguousarray(order, np.uint32)

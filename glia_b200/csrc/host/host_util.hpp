@@ -160,6 +160,31 @@ inline Image read_real_image(const std::string& file) {
   return im;
 }
 
+// label image out: .npy (u4 / u2) or uncompressed .mha (MET_UINT / MET_USHORT), same axis conventions as the readers
+inline void write_label_image(const std::string& file, const Image& like, const uint32_t* data, bool as16) {
+  const size_t n = like.size();
+  std::vector<uint16_t> v16;
+  if (as16) { v16.resize(n); for (size_t i = 0; i < n; ++i) v16[i] = (uint16_t)data[i]; }
+  const void* raw = as16 ? (const void*)v16.data() : (const void*)data;
+  const size_t bytes = n * (as16 ? 2 : 4);
+  std::ofstream os(file, std::ios::binary);
+  if (!os) perr("Error: cannot write file " + file);
+  if (ends_with(file, ".npy")) {
+    std::stringstream shape;
+    for (int i = like.ndim - 1; i >= 0; --i) shape << like.dims[i] << (i ? ", " : "");
+    std::string hdr = std::string("{'descr': '") + (as16 ? "<u2" : "<u4") + "', 'fortran_order': False, 'shape': (" + shape.str() + "), }";
+    while ((10 + hdr.size() + 1) % 64) hdr += ' ';
+    hdr += '\n';
+    const unsigned char pre[10] = {0x93, 'N', 'U', 'M', 'P', 'Y', 1, 0, (unsigned char)(hdr.size() & 255), (unsigned char)(hdr.size() >> 8)};
+    os.write((const char*)pre, 10); os.write(hdr.data(), (std::streamsize)hdr.size());
+  } else if (ends_with(file, ".mha")) {
+    os << "ObjectType = Image\nNDims = " << like.ndim << "\nBinaryData = True\nBinaryDataByteOrderMSB = False\nCompressedData = False\nDimSize =";
+    for (int i = 0; i < like.ndim; ++i) os << " " << like.dims[i];
+    os << "\nElementType = " << (as16 ? "MET_USHORT" : "MET_UINT") << "\nElementDataFile = LOCAL\n";
+  } else perr("Error: unsupported output image format (use .npy or .mha): " + file);
+  os.write((const char*)raw, (std::streamsize)bytes);
+}
+
 // ---- text files
 // order: one "r0 r1 r2" per line (TTriple operator<<, type/tuple.hxx:24-28)
 inline std::vector<uint32_t> read_order(const std::string& file) {

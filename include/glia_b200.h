@@ -106,6 +106,22 @@ GLIA_API const char* glia_b200_last_error(const glia_handle* h);
  * reference's per-image process loop does (gadget/python/script_util.py:6-23). */
 GLIA_API int glia_b200_set_image(glia_handle* h, int kind, int i, const float* data);
 
+/* SURVEY section 8f rank 1.  Merge order from the boundary probability alone (hmt/main_merge_order_pb.cxx:14-40,
+ * util/struct_merge.hxx:36-136): saliency of a pair = -(mean | approximate median) of pb over its pair boundary, a merge
+ * combines the data of the items it replaces (weighted mean, or concatenated values) and never re-reads the image.
+ * type: 1 = median (the handle must have use_median_feat), 2 = mean.  Boundary image 0 must be the pb map.  The
+ * reference builds its region map with onlyContour = true: create the handle with contour_only = 1 to reproduce it
+ * when a mask is given.  order [R-1][3] / sal [R-1] are host buffers; *n_merges receives the number of merges. */
+GLIA_API int glia_b200_merge_order_pb(glia_handle* h, int type, uint32_t* order, double* sal, int64_t* n_merges);
+/* pre_merge (gadget/main_pre_merge.cxx:7-87): the mean-pb greedy chain restricted to pairs whose smaller region is
+ * below size_thresholds[0] voxels, or - with a second threshold - where a region below size_thresholds[1] has a mean
+ * pb above rpb_threshold; regions are updated as they merge.  Region image 0 and boundary image 0 must be the pb map.
+ * labels_out (optional; host or device as the handle's inputs, same extent as the label volume) receives the label
+ * volume with every merged region renamed to its final key (transformKeys + transformImage); the reference's
+ * optional ITK relabel step is not part of this call. */
+GLIA_API int glia_b200_pre_merge(glia_handle* h, const int* size_thresholds, int n_thresholds, double rpb_threshold,
+                                 uint32_t* order, double* sal, int64_t* n_merges, uint32_t* labels_out);
+
 /* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
  * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
  * kernel, "slots": its shared-memory table slots (0 = default); "notma": value != 0 makes the generic voxel kernel

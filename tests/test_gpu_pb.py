@@ -1,0 +1,115 @@
+"""GPU parity for SURVEY §8f rank 1: merge_order_pb (hmt/main_merge_order_pb.cxx) and pre_merge
+(gadget/main_pre_merge.cxx) through the C ABI against the oracle, which is pinned to the compiled reference
+(tests/test_oracle_vs_ref.py::test_merge_order_pb_matches_reference, ::test_pre_merge_matches_reference)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from glia_b200 import api, synth
+
+pytestmark = pytest.mark.gpu
+BIN = os.path.join(os.path.dirname(api.HERE), "glia_b200", "bin")
+
+CASES = [((24, 28), 40, 41, False), ((31, 22), 25, 42, True), ((9, 10, 11), 20, 43, False), ((8, 12, 10), 14, 44, True),
+         ((64, 80), 300, 45, False), ((20, 24, 28), 250, 46, True)]
+
+
+def _make(shape, nl, seed, um):
+    lab, pb = synth.speckle_volume(shape, nl, seed=seed)
+    mask = (np.random.default_rng(seed + 100).random(shape) > 0.04).astype(np.uint32) if um else None
+    return lab, pb, mask
+
+
+@pytest.mark.parametrize("type_", [1, 2])
+@pytest.mark.parametrize("case", CASES)
+def test_merge_order_pb_matches_oracle(case, type_):
+    """Order and saliencies bit for bit: dyadic pb makes the sums exact, medians are order statistics; pb has 256
+    levels, so saliency ties (and with them the queue's tie-break rule) occur all the time."""
+    shape, nl, seed, um = case
+    lab, pb, mask = _make(shape, nl, seed, um)
+    kw = dict(use_median=(type_ == 1), contour_only=True)
+    spec = [(pb, 1, 0.0, 1.0)]
+    o = ol.Oracle(lab, pb, ol.FeatureConfig(bimgs=spec, thr=(), **kw), mask=mask)
+    g = api.MergeTreeBuilder(shape, api.FeatureConfig(bimgs=spec, thr=(), **kw)).build(lab, pb, mask)
+    ro, rg = o.merge_order_pb(type_), g.merge_order_pb(type_)
+    assert len(ro["order"]) > 3
+    assert np.array_equal(rg["order"], ro["order"])
+    assert np.array_equal(rg["sal"], ro["sal"])
+
+
+@pytest.mark.parametrize("thr", [(30,), (25, 60)])
+@pytest.mark.parametrize("case", CASES)
+def test_pre_merge_matches_oracle(case, thr):
+    shape, nl, seed, um = case
+    lab, pb, mask = _make(shape, nl, seed, um)
+    spec = [(pb, 1, 0.0, 1.0)]
+    o = ol.Oracle(lab, pb, ol.FeatureConfig(rimgs=spec, bimgs=spec, thr=()), mask=mask)
+    g = api.MergeTreeBuilder(shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=())).build(lab, pb, mask)
+    ro, rg = o.pre_merge(thr, 0.4), g.pre_merge(thr, 0.4)
+    assert np.array_equal(rg["order"], ro["order"])
+    assert np.array_equal(rg["sal"], ro["sal"])
+    assert np.array_equal(rg["labels"], ro["labels"])
+    # every merged region got one key; untouched regions keep theirs
+    merged = set(ro["order"][:, :2].ravel().tolist())
+    keep = ~np.isin(lab, list(merged))
+    assert np.array_equal(rg["labels"][keep], lab[keep])
+
+
+def test_merge_order_pb_nondyadic_saliencies_within_tolerance():
+    """Non-dyadic pb: the mean saliencies agree to 1e-12 (the reference sums floats into a double pixel by pixel, the
+    voxel pass sums exactly); the median run stays bit-identical."""
+    lab, pb = synth.speckle_volume((40, 50), 60, seed=11, dyadic=False)
+    spec = [(pb, 1, 0.0, 1.0)]
+    o = ol.Oracle(lab, pb, ol.FeatureConfig(bimgs=spec, thr=(), use_median=True, contour_only=True))
+    g = api.MergeTreeBuilder((40, 50), api.FeatureConfig(bimgs=spec, thr=(), use_median=True, contour_only=True)).build(lab, pb)
+    ro, rg = o.merge_order_pb(1), g.merge_order_pb(1)
+    assert np.array_equal(rg["order"], ro["order"]) and np.array_equal(rg["sal"], ro["sal"])
+    ro, rg = o.merge_order_pb(2), g.merge_order_pb(2)
+    n = min(len(ro["sal"]), len(rg["sal"]))
+    same = np.all(ro["order"][:n] == rg["order"][:n], axis=1)
+    k = n if same.all() else int(np.argmin(same))  # a 1-ulp difference may reorder a near-tie: compare up to there
+    assert k >= 1
+    np.testing.assert_allclose(rg["sal"][:k], ro["sal"][:k], rtol=1e-12)
+
+
+def _write_mha(path, arr, met_type):
+    dims = " ".join(str(s) for s in arr.shape[::-1])
+    hdr = ("ObjectType = Image\nNDims = %d\nBinaryData = True\nBinaryDataByteOrderMSB = False\n"
+           "CompressedData = False\nDimSize = %s\nElementType = %s\nElementDataFile = LOCAL\n" % (arr.ndim, dims, met_type))
+    with open(path, "wb") as f:
+        f.write(hdr.encode())
+        f.write(np.ascontiguousarray(arr).tobytes())
+
+
+def test_cli_merge_order_pb_and_pre_merge(tmp_path):
+    shape = (36, 48)
+    lab, pb, mask = _make(shape, 70, 47, True)
+    seg_f, pb_f, mask_f = str(tmp_path / "seg.npy"), str(tmp_path / "pb.mha"), str(tmp_path / "mask.npy")
+    np.save(seg_f, lab); np.save(mask_f, mask.astype(np.uint8)); _write_mha(pb_f, pb, "MET_FLOAT")
+    spec = [(pb, 1, 0.0, 1.0)]
+    for t in (1, 2):
+        o = ol.Oracle(lab, pb, ol.FeatureConfig(bimgs=spec, thr=(), use_median=(t == 1), contour_only=True), mask=mask)
+        want = o.merge_order_pb(t)
+        order_f, sal_f = str(tmp_path / ("order%d.txt" % t)), str(tmp_path / ("sal%d.txt" % t))
+        r = subprocess.run([os.path.join(BIN, "merge_order_pb"), "-s", seg_f, "-p", pb_f, "-m", mask_f, "-t", str(t),
+                            "-o", order_f, "-y", sal_f], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert np.array_equal(np.loadtxt(order_f, dtype=np.int64).reshape(-1, 3), want["order"])
+        np.testing.assert_allclose(np.loadtxt(sal_f), want["sal"], rtol=1e-5, atol=1e-12)
+    o = ol.Oracle(lab, pb, ol.FeatureConfig(rimgs=spec, bimgs=spec, thr=()), mask=mask)
+    want = o.pre_merge((25, 60), 0.4)
+    for out_f, dt in ((str(tmp_path / "out.npy"), np.uint32), (str(tmp_path / "out.mha"), np.uint16)):
+        cmd = [os.path.join(BIN, "pre_merge"), "-s", seg_f, "-p", pb_f, "-m", mask_f, "-t", "25", "60", "-b", "0.4", "-o", out_f]
+        if dt == np.uint16:
+            cmd += ["-u", "1"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        if out_f.endswith(".npy"):
+            got = np.load(out_f)
+        else:
+            raw = open(out_f, "rb").read()
+            got = np.frombuffer(raw[raw.index(b"ElementDataFile = LOCAL\n") + 24:], dt).reshape(shape)
+        assert got.dtype == dt and np.array_equal(got.astype(np.uint32), want["labels"])
