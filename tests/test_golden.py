@@ -222,3 +222,46 @@ def test_cuda_reproduces_variant_golden(path):
         np.testing.assert_allclose(g.bc_feat(z["order"]), z["bcfeat_rows"], rtol=RTOL, atol=1e-9)
         np.testing.assert_allclose(g.bc_feat(z["order"], sal=z["sal"], init_sal=1.0, sal_bias=0.25),
                                    z["bcfeat_rows_sal"], rtol=RTOL, atol=1e-9)
+
+
+# ---------------------------------------------------------------- merge_order_pb / pre_merge
+PGOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pb", "*.npz")))
+
+
+def _pb_case(path, mod, **kw):
+    z = np.load(path)
+    mask = z["mask"] if z["mask"].size else None
+    spec = [(z["pb"], 1, 0.0, 1.0)]
+    return z, z["labels"], z["pb"], mask, spec
+
+
+def test_pb_fixtures_present():
+    assert len(PGOLD) >= 3
+
+
+@pytest.mark.parametrize("path", PGOLD, ids=[os.path.basename(p)[:-4] for p in PGOLD])
+def test_oracle_reproduces_pb_golden(path):
+    z, lab, pb, mask, spec = _pb_case(path, ol)
+    for t, key in ((1, "median"), (2, "mean")):
+        o = ol.Oracle(lab, pb, ol.FeatureConfig(bimgs=spec, thr=(), use_median=(t == 1), contour_only=True), mask=mask)
+        r = o.merge_order_pb(t)
+        assert np.array_equal(r["order"], z[key + "_order"]) and np.array_equal(r["sal"], z[key + "_sal"])
+    r = ol.Oracle(lab, pb, ol.FeatureConfig(rimgs=spec, bimgs=spec, thr=()), mask=mask).pre_merge((25, 60), 0.4)
+    assert np.array_equal(r["order"], z["pm_order"]) and np.array_equal(r["sal"], z["pm_sal"])
+    assert np.array_equal(r["labels"], z["pm_labels"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", PGOLD, ids=[os.path.basename(p)[:-4] for p in PGOLD])
+def test_cuda_reproduces_pb_golden(path):
+    from glia_b200 import api
+    z, lab, pb, mask, spec = _pb_case(path, api)
+    for t, key in ((1, "median"), (2, "mean")):
+        g = api.MergeTreeBuilder(lab.shape, api.FeatureConfig(bimgs=spec, thr=(), use_median=(t == 1), contour_only=True))
+        r = g.build(lab, pb, mask).merge_order_pb(t)
+        assert np.array_equal(r["order"], z[key + "_order"]) and np.array_equal(r["sal"], z[key + "_sal"])
+        g.close()
+    g = api.MergeTreeBuilder(lab.shape, api.FeatureConfig(rimgs=spec, bimgs=spec, thr=())).build(lab, pb, mask)
+    r = g.pre_merge((25, 60), 0.4)
+    assert np.array_equal(r["order"], z["pm_order"]) and np.array_equal(r["sal"], z["pm_sal"])
+    assert np.array_equal(r["labels"], z["pm_labels"])
