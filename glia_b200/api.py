@@ -63,7 +63,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_tune", "glia_b200_candidate_ties", "glia_b200_set_tie_orientation",
            "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
            "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms",
-           "glia_b200_bc_feat_sharded", "glia_b200_merge_order_pb", "glia_b200_pre_merge"]
+           "glia_b200_bc_feat_sharded", "glia_b200_merge_order_pb", "glia_b200_pre_merge",
+           "glia_b200_segment_greedy"]
 
 
 def lib():
@@ -102,6 +103,7 @@ def lib():
         L.glia_b200_merge_order_bc.argtypes = [vp, vp, vp, vp, vp, C.POINTER(C.c_int64),
                                                C.POINTER(C.c_int64)]
         L.glia_b200_bc_feat.argtypes = [vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp]
+        L.glia_b200_segment_greedy.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_merge_order_pb.argtypes = [vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_pre_merge.argtypes = [vp, vp, C.c_int, C.c_double, vp, vp, C.POINTER(C.c_int64), vp]
         L.glia_b200_bc_feat_sharded.argtypes = [vp, vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp,
@@ -467,6 +469,27 @@ class MergeTreeBuilder:
         self._check(lib().glia_b200_pre_merge(self.h, _addr(thr), len(thr), C.c_double(rpb_thr), _addr(order), _addr(sal),
                                               C.byref(nm), _addr(out)))
         return dict(order=order[:nm.value], sal=sal[:nm.value], labels=out)
+
+    def segment_greedy(self, orders, merge_probs=None, region_probs=None, ignore_missing=True):
+        """hmt/main_segment_greedy.cxx: resolve one or more merge trees; returns (labels, picks [(tree, node)])."""
+        orders = [np.ascontiguousarray(o, np.uint32) for o in orders]
+        n = len(orders)
+        op = (C.c_void_p * n)(*[o.ctypes.data for o in orders])
+        nm = (C.c_int64 * n)(*[len(o) for o in orders])
+
+        def ptrs(lst):
+            if lst is None:
+                return None, None
+            arrs = [np.ascontiguousarray(a, np.float64) for a in lst]
+            return (C.c_void_p * n)(*[a.ctypes.data for a in arrs]), arrs
+        mp, keep1 = ptrs(merge_probs)
+        rp, keep2 = ptrs(region_probs)
+        out = np.zeros(self.shape, np.uint32)
+        picks = np.zeros((2 * max(self.R, 1) * n, 2), np.int32)
+        npk = C.c_int64()
+        self._check(lib().glia_b200_segment_greedy(self.h, n, op, nm, mp, rp, int(ignore_missing), _addr(out), _addr(picks),
+                                                   C.byref(npk)))
+        return out, picks[:npk.value]
 
     def bc_feat(self, order, sal=None, init_sal=1.0, sal_bias=0.0):
         order = np.ascontiguousarray(order, np.uint32)

@@ -178,6 +178,25 @@ int pb_chain(glia_handle* h, int type, PreMerge* pm, uint32_t* order, double* sa
 
 }  // namespace
 
+// labels_out[p] = lut[region index of labels[p]] over the volume the handle was built from (masked-out voxels keep their
+// label): one gather, 8 bytes per voxel.  labels_out is a host or device buffer as the handle's inputs are.
+int glia_relabel_by_region(glia_handle* h, const std::vector<uint32_t>& lut, uint32_t* labels_out) {
+  cudaStream_t st = h->stream;
+  const size_t n = h->nvoxBuf, R = lut.size();
+  DevBuf &dLut = h->k5[0], &dOut = h->k5[1];
+  CK(dLut.ensure(4 * (R + 1)));
+  CK(cudaMemcpyAsync(dLut.p, lut.data(), 4 * R, cudaMemcpyHostToDevice, st));
+  uint32_t* out = labels_out;
+  if (!h->prm.device_pointers) { CK(dOut.ensure(4 * n)); out = dOut.as<uint32_t>(); }
+  relabel_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->vp.labels, h->vp.mask, h->rank.as<uint32_t>(), dLut.as<uint32_t>(), n,
+                                                             h->vp.labelBound, out);
+  h->launches++;
+  CK(cudaGetLastError());
+  if (!h->prm.device_pointers) { int s = glia_copy_to_host(h, labels_out, out, 4 * n); if (s != GLIA_OK) return s; }
+  CK(cudaStreamSynchronize(st));
+  return GLIA_OK;
+}
+
 extern "C" int glia_b200_merge_order_pb(glia_handle* h, int type, uint32_t* order, double* sal, int64_t* n_merges) {
   if (!h || !order || !sal || (type != 1 && type != 2)) return GLIA_E_ARG;
   if (!h->built) return GLIA_E_STATE;
@@ -224,17 +243,5 @@ extern "C" int glia_b200_pre_merge(glia_handle* h, const int* size_thresholds, i
     while (parent[v] != v) v = parent[v];
     lut[r] = v < R ? lab[v] : maxLabel + 1 + (uint32_t)(v - R);
   }
-  const size_t n = h->nvoxBuf;
-  DevBuf &dLut = h->k5[0], &dOut = h->k5[1];
-  CK(dLut.ensure(4 * (size_t)R));
-  CK(cudaMemcpyAsync(dLut.p, lut.data(), 4 * (size_t)R, cudaMemcpyHostToDevice, st));
-  uint32_t* out = labels_out;
-  if (!h->prm.device_pointers) { CK(dOut.ensure(4 * n)); out = dOut.as<uint32_t>(); }
-  relabel_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(h->vp.labels, h->vp.mask, h->rank.as<uint32_t>(), dLut.as<uint32_t>(), n,
-                                                             h->vp.labelBound, out);
-  h->launches++;
-  CK(cudaGetLastError());
-  if (!h->prm.device_pointers) { s = glia_copy_to_host(h, labels_out, out, 4 * n); if (s != GLIA_OK) return s; }
-  CK(cudaStreamSynchronize(st));
-  return GLIA_OK;
+  return glia_relabel_by_region(h, lut, labels_out);
 }

@@ -122,6 +122,20 @@ GLIA_API int glia_b200_merge_order_pb(glia_handle* h, int type, uint32_t* order,
 GLIA_API int glia_b200_pre_merge(glia_handle* h, const int* size_thresholds, int n_thresholds, double rpb_threshold,
                                  uint32_t* order, double* sal, int64_t* n_merges, uint32_t* labels_out);
 
+/* SURVEY section 8f rank 3.  segment_greedy (hmt/main_segment_greedy.cxx:30-95): merge trees (one per order) with node
+ * potentials from the merge probabilities (hmt/tree_build.hxx:41-62; all 1 when merge_probs is NULL), optionally scaled
+ * by per-node region probabilities in tree node order, are resolved greedily over all trees (hmt/tree_greedy.hxx:107-152:
+ * repeatedly the valid node of largest potential, which invalidates its ancestors, its descendants and - through its
+ * leaf labels - the matching leaves and their ancestors in the other trees).  Pick k renames the superpixels below it
+ * to k + 1 (hmt/tree_segment.hxx:24-35); labels_out (host or device as the handle's inputs) receives the volume the
+ * handle was built from with those names, unmapped superpixels set to 0 when ignore_missing (the reference's default)
+ * and left alone otherwise, masked-out voxels untouched.  picks (optional, [2 R][2]) = (tree, node) in pick order with
+ * nodes numbered as genTree numbers them (first appearance in the order).  The boundary-confidence image (-b) and the
+ * ITK relabel (-r) of the reference program are not part of this call. */
+GLIA_API int glia_b200_segment_greedy(glia_handle* h, int n_trees, const uint32_t* const* orders, const int64_t* n_merges,
+                                      const double* const* merge_probs, const double* const* region_probs,
+                                      int ignore_missing, uint32_t* labels_out, int32_t* picks, int64_t* n_picks);
+
 /* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
  * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
  * kernel, "slots": its shared-memory table slots (0 = default); "notma": value != 0 makes the generic voxel kernel

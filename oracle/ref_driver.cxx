@@ -21,6 +21,8 @@
 #include "type/region_map.hxx"
 #include "util/struct_merge_bc.hxx"
 #include "util/struct_merge.hxx"
+#include "hmt/tree_build.hxx"
+#include "hmt/tree_greedy.hxx"
 #include "util/mp.hxx"
 
 using namespace glia;
@@ -399,6 +401,59 @@ int glia_ref_run_pb(int mode, const int* dims, const uint32_t* labels, const uin
   for (auto const& m : order) { G.order.push_back(m.x0); G.order.push_back(m.x1); G.order.push_back(m.x2); }
   G.sal = saliencies;
   G.t_total = now() - tStart;
+  return 0;
+}
+
+// ---- hmt/main_segment_greedy.cxx:30-95 (tree resolution + final segmentation) ----
+// Trees with node potentials from merge probabilities (hmt/tree_build.hxx:41-62), optional region probabilities,
+// resolveTreeGreedy over all trees (hmt/tree_greedy.hxx:107-152), then genLabelTransform + transformImage
+// (hmt/tree_segment.hxx:24-35, util/image.hxx:211-242 - both behind the ITK filter includes, their loops are restated).
+struct SegNodeData { Label label; double potential; };
+int glia_ref_segment_greedy(const int* dims, const uint32_t* labels, const uint32_t* maskBuf, int nTree,
+                            const uint32_t* const* ordersIn, const int* nMerges, const double* const* mergeProbsIn,
+                            const double* const* regionProbsIn, int ignore)
+{
+  G = Results();
+  typedef TTree<SegNodeData> Tree;
+  std::vector<std::vector<TTriple<Label>>> orders(nTree);
+  std::vector<Tree> trees(nTree);
+  for (int i = 0; i < nTree; ++i) {
+    for (int k = 0; k < nMerges[i]; ++k)
+      orders[i].emplace_back(ordersIn[i][3 * k], ordersIn[i][3 * k + 1], ordersIn[i][3 * k + 2]);
+    if (mergeProbsIn && mergeProbsIn[i]) {
+      std::vector<double> mergeProbs(mergeProbsIn[i], mergeProbsIn[i] + nMerges[i]);
+      genTreeWithNodePotentials(trees[i], orders[i], mergeProbs.begin());
+    } else {
+      genTree(trees[i], orders[i], [](Tree::Node& node, Label r) { node.data.label = r; node.data.potential = 1.0; });
+    }
+    if (regionProbsIn && regionProbsIn[i]) {
+      const double* rp = regionProbsIn[i];
+      for (auto& tn : trees[i]) { tn.data.potential *= std::max(*rp++, FEPS); }
+    }
+  }
+  auto segImage = wrap<LImage>(labels, dims);
+  LImage::Pointer mask = maskBuf ? wrap<LImage>(maskBuf, dims) : LImage::Pointer(nullptr);
+  std::vector<std::pair<int, int>> picks;
+  resolveTreeGreedy(picks, trees, [](Tree::Node const& node0, Tree::Node const& node1) -> bool {
+    return node0.data.potential < node1.data.potential; });
+  std::unordered_map<Label, Label> lmap;   // genLabelTransform(lmap, trees, picks, 1u)
+  Label keyToAssign = 1u;
+  for (auto const& pick : picks) {
+    trees[pick.first].traverseLeaves(pick.second, [keyToAssign, &lmap](Tree::Node const& node) { lmap[node.data.label] = keyToAssign; });
+    ++keyToAssign;
+  }
+  size_t n = segImage->GetBufferSize();
+  Label* px = segImage->GetBufferPointer();
+  const Label* mk = mask.IsNull() ? nullptr : mask->GetBufferPointer();
+  for (size_t p = 0; p < n; ++p) {   // transformImage(image, lmap, mask[, fillMissing = ignore])
+    if (mk && mk[p] == MASK_OUT_VAL) continue;
+    auto lit = lmap.find(px[p]);
+    if (lit != lmap.end()) px[p] = lit->second;
+    else if (ignore) px[p] = BG_VAL;
+  }
+  G.out_labels.assign(px, px + n);
+  for (auto const& pk : picks) { G.order.push_back((uint32_t)pk.first); G.order.push_back((uint32_t)pk.second); G.order.push_back(0); }
+  for (int i = 0; i < nTree; ++i) for (auto const& tn : trees[i]) G.sal.push_back(tn.data.potential);
   return 0;
 }
 

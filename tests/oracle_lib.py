@@ -365,6 +365,32 @@ def ref_run_pb(mode, labels, pb, mask=None, type=1, size_thr=(), rpb_thr=0.0):
     return out
 
 
+def ref_segment_greedy(labels, orders, merge_probs=None, region_probs=None, mask=None, ignore=True):
+    """The compiled reference's segment_greedy call sequence (oracle/ref_driver.cxx glia_ref_segment_greedy):
+    returns (final labels, picks [(tree, node)], potentials of all trees' nodes concatenated)."""
+    labels = np.ascontiguousarray(labels, np.uint32)
+    ndim = labels.ndim
+    L = ref_lib(ndim)
+    dims = (C.c_int * 3)(*(list(labels.shape[::-1]) + [1] * (3 - ndim)))
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint32)
+    n = len(orders)
+    oa = [np.ascontiguousarray(o, np.uint32) for o in orders]
+    op = (C.c_void_p * n)(*[a.ctypes.data for a in oa])
+    nm = (C.c_int * n)(*[len(a) for a in oa])
+
+    def ptrs(lst):
+        if lst is None:
+            return None, None
+        arrs = [np.ascontiguousarray(a, np.float64) for a in lst]
+        return (C.c_void_p * n)(*[a.ctypes.data for a in arrs]), arrs
+    mp, k1 = ptrs(merge_probs)
+    rp, k2 = ptrs(region_probs)
+    st = L.glia_ref_segment_greedy(dims, _ptr(labels), _ptr(m), C.c_int(n), op, nm, mp, rp, C.c_int(int(ignore)))
+    assert st == 0
+    picks = _ref_get(L, "order", np.uint32).reshape(-1, 3)[:, :2].astype(np.int64)
+    return _ref_get(L, "out_labels", np.uint32).reshape(labels.shape), picks, _ref_get(L, "sal", np.float64)
+
+
 def ref_run(mode, labels, pb, cfg, mask=None, pred=None, order=None, sal=None, init_sal=1.0,
             sal_bias=0.0, threads=0, pred_c=None):
     """Run the compiled unmodified reference (oracle/ref_driver.cxx). mode: 0 RAG, 1 init

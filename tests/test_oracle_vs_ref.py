@@ -324,3 +324,43 @@ def test_pre_merge_matches_reference(case, thr):
     assert np.array_equal(res["order"], ref["order"])
     assert np.array_equal(res["sal"], ref["sal"])
     assert np.array_equal(res["labels"], ref["labels"])
+
+
+# ---- segment_greedy (tree resolution + final segmentation)
+def _seg_inputs(shape, nl, seed, um, ntree):
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(ol.ORACLE_DIR), "oracle"))
+    lab, pb, mask = _make(shape, nl, seed, um)
+    rng = np.random.default_rng(seed)
+    o = ol.Oracle(lab, pb, ol.default_config(pb), mask=mask)
+    orders, probs, rprobs = [], [], []
+    for t in range(ntree):
+        # different trees over the same superpixels: mean-pb order, and greedy orders under random predictors
+        if t == 0:
+            o2 = ol.Oracle(lab, pb, ol.default_config(pb, contour_only=True), mask=mask)
+            res = o2.merge_order_pb(2)
+        else:
+            res = o.greedy(fn=lambda row, t=t: float(np.floor((np.sum(np.abs(row[:9])) * (3.1 + t)) % 1.0 * 16) / 16.0))
+        orders.append(res["order"])
+        probs.append(np.floor(rng.random(len(res["order"])) * 8) / 8.0)       # tie-heavy probabilities
+        rprobs.append(np.floor(rng.random(2 * len(res["order"]) + 1) * 4) / 4.0)
+    return lab, mask, orders, probs, rprobs
+
+
+@pytest.mark.parametrize("variant", ["probs", "noprobs", "regionprobs", "exact"])
+@pytest.mark.parametrize("case", [((24, 28), 30, 61, False, 1), ((22, 25), 20, 62, True, 2), ((8, 10, 9), 14, 63, False, 3)])
+def test_segment_greedy_matches_reference(case, variant):
+    """hmt/main_segment_greedy.cxx:30-95: potentials, picks and the final label volume of the Python restatement
+    (oracle/segment_oracle.py) against the compiled reference, one to three trees."""
+    shape, nl, seed, um, ntree = case
+    if not _have_ref(len(shape)):
+        pytest.skip("oracle/_ref not available")
+    lab, mask, orders, probs, rprobs = _seg_inputs(shape, nl, seed, um, ntree)
+    import segment_oracle as so
+    kw = dict(merge_probs=None if variant == "noprobs" else probs, region_probs=rprobs if variant == "regionprobs" else None,
+              mask=mask, ignore=variant != "exact")
+    want_lab, want_picks, want_pot = ol.ref_segment_greedy(lab, orders, **kw)
+    got_lab, got_picks, got_pot = so.segment_greedy(lab, orders, **kw)
+    assert np.array_equal(np.concatenate(got_pot), want_pot)
+    assert np.array_equal(np.array(got_picks, np.int64).reshape(-1, 2), want_picks)
+    assert np.array_equal(got_lab, want_lab)
