@@ -265,3 +265,47 @@ def test_cuda_reproduces_pb_golden(path):
     r = g.pre_merge((25, 60), 0.4)
     assert np.array_equal(r["order"], z["pm_order"]) and np.array_equal(r["sal"], z["pm_sal"])
     assert np.array_equal(r["labels"], z["pm_labels"])
+
+
+# ---------------------------------------------------------------- segment_greedy
+SGOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "seg", "*.npz")))
+SEG_VARIANTS = (("probs", True, False, True), ("noprobs", False, False, True), ("rp", True, True, True), ("exact", True, False, False))
+
+
+def _seg_case(path):
+    z = np.load(path)
+    n = int(z["ntree"])
+    mask = z["mask"] if z["mask"].size else None
+    return z, z["labels"], mask, [z["order%d" % i] for i in range(n)], [z["probs%d" % i] for i in range(n)], \
+        [z["rprobs%d" % i] for i in range(n)]
+
+
+def test_seg_fixtures_present():
+    assert len(SGOLD) >= 3
+
+
+@pytest.mark.parametrize("path", SGOLD, ids=[os.path.basename(p)[:-4] for p in SGOLD])
+def test_python_oracle_reproduces_seg_golden(path):
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import segment_oracle as so
+    z, lab, mask, orders, probs, rprobs = _seg_case(path)
+    for tag, use_p, use_rp, ignore in SEG_VARIANTS:
+        l, pk, _ = so.segment_greedy(lab, orders, merge_probs=probs if use_p else None, region_probs=rprobs if use_rp else None,
+                                     mask=mask, ignore=ignore)
+        assert np.array_equal(np.array(pk, np.int64).reshape(-1, 2), z["picks_" + tag]), tag
+        assert np.array_equal(l, z["labels_" + tag]), tag
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", SGOLD, ids=[os.path.basename(p)[:-4] for p in SGOLD])
+def test_cuda_reproduces_seg_golden(path):
+    from glia_b200 import api
+    z, lab, mask, orders, probs, rprobs = _seg_case(path)
+    zero = np.zeros(lab.shape, np.float32)
+    g = api.MergeTreeBuilder(lab.shape, api.FeatureConfig(thr=())).build(lab, zero, mask)
+    for tag, use_p, use_rp, ignore in SEG_VARIANTS:
+        l, pk = g.segment_greedy(orders, merge_probs=probs if use_p else None, region_probs=rprobs if use_rp else None,
+                                 ignore_missing=ignore)
+        assert np.array_equal(pk.astype(np.int64), z["picks_" + tag]), tag
+        assert np.array_equal(l, z["labels_" + tag]), tag

@@ -113,3 +113,57 @@ def test_cli_merge_order_pb_and_pre_merge(tmp_path):
             raw = open(out_f, "rb").read()
             got = np.frombuffer(raw[raw.index(b"ElementDataFile = LOCAL\n") + 24:], dt).reshape(shape)
         assert got.dtype == dt and np.array_equal(got.astype(np.uint32), want["labels"])
+
+
+# ---------------------------------------------------------------- segment_greedy
+def _trees(lab, pb, mask, ntree, seed):
+    rng = np.random.default_rng(seed)
+    o = ol.Oracle(lab, pb, ol.default_config(pb), mask=mask)
+    orders, probs, rprobs = [], [], []
+    for t in range(ntree):
+        if t == 0:
+            res = ol.Oracle(lab, pb, ol.default_config(pb, contour_only=True), mask=mask).merge_order_pb(2)
+        else:
+            res = o.greedy(fn=lambda row, t=t: float(np.floor((np.sum(np.abs(row[:9])) * (3.1 + t)) % 1.0 * 16) / 16.0))
+        orders.append(res["order"])
+        probs.append(np.floor(rng.random(len(res["order"])) * 8) / 8.0)
+        rprobs.append(np.floor(rng.random(2 * len(res["order"]) + 1) * 4) / 4.0)
+    return orders, probs, rprobs
+
+
+@pytest.mark.parametrize("case", [((30, 36), 60, 81, False, 1), ((28, 31), 40, 82, True, 2), ((9, 12, 11), 30, 83, True, 3)])
+def test_segment_greedy_matches_oracle(case):
+    """hmt/main_segment_greedy.cxx: picks and the final label volume against the Python restatement (pinned to the
+    compiled reference), with / without merge and region probabilities, ignore on / off, one to three trees."""
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import segment_oracle as so
+    shape, nl, seed, um, ntree = case
+    lab, pb, mask = _make(shape, nl, seed, um)
+    orders, probs, rprobs = _trees(lab, pb, mask, ntree, seed)
+    g = api.MergeTreeBuilder(shape, api.FeatureConfig(thr=())).build(lab, np.zeros(shape, np.float32), mask)
+    for mp, rp, ign in ((probs, None, True), (None, None, True), (probs, rprobs, True), (probs, None, False)):
+        want_l, want_pk, _ = so.segment_greedy(lab, orders, merge_probs=mp, region_probs=rp, mask=mask, ignore=ign)
+        got_l, got_pk = g.segment_greedy(orders, merge_probs=mp, region_probs=rp, ignore_missing=ign)
+        assert np.array_equal(got_pk.astype(np.int64), np.array(want_pk, np.int64).reshape(-1, 2))
+        assert np.array_equal(got_l, want_l)
+
+
+def test_cli_segment_greedy(tmp_path):
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import segment_oracle as so
+    shape = (32, 40)
+    lab, pb, mask = _make(shape, 50, 84, True)
+    orders, probs, _ = _trees(lab, pb, mask, 2, 84)
+    seg_f, mask_f, out_f = str(tmp_path / "seg.npy"), str(tmp_path / "mask.npy"), str(tmp_path / "final.npy")
+    np.save(seg_f, lab); np.save(mask_f, mask.astype(np.uint8))
+    of, pf = [], []
+    for i, (o, p) in enumerate(zip(orders, probs)):
+        of.append(str(tmp_path / ("order%d.txt" % i))); pf.append(str(tmp_path / ("prob%d.txt" % i)))
+        np.savetxt(of[-1], o, fmt="%d"); np.savetxt(pf[-1], p, fmt="%.17g")
+    r = subprocess.run([os.path.join(BIN, "segment_greedy"), "-s", seg_f, "-m", mask_f, "-o"] + of + ["-p"] + pf + ["-f", out_f],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want, _, _ = so.segment_greedy(lab, orders, merge_probs=probs, mask=mask, ignore=True)
+    assert np.array_equal(np.load(out_f), want)
