@@ -64,7 +64,7 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
            "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms",
            "glia_b200_bc_feat_sharded", "glia_b200_merge_order_pb", "glia_b200_pre_merge",
-           "glia_b200_segment_greedy"]
+           "glia_b200_segment_greedy", "glia_b200_rf_score_noalloc", "glia_b200_rf_score_noalloc_max_votes"]
 
 
 def lib():
@@ -103,6 +103,9 @@ def lib():
         L.glia_b200_merge_order_bc.argtypes = [vp, vp, vp, vp, vp, C.POINTER(C.c_int64),
                                                C.POINTER(C.c_int64)]
         L.glia_b200_bc_feat.argtypes = [vp, vp, C.c_int64, vp, C.c_double, C.c_double, vp]
+        L.glia_b200_rf_score_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int, vp, vp, C.c_char_p, C.c_size_t]
+        L.glia_b200_rf_score_noalloc_max_votes.argtypes = []
+        L.glia_b200_rf_score_noalloc_max_votes.restype = C.c_size_t
         L.glia_b200_segment_greedy.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_merge_order_pb.argtypes = [vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_pre_merge.argtypes = [vp, vp, C.c_int, C.c_double, vp, vp, C.POINTER(C.c_int64), vp]

@@ -276,6 +276,20 @@ GLIA_API int glia_b200_rf_info(const glia_rf* m, int* ntree, int* nrnodes, int* 
  * device_pointers: X, votes, prob are device buffers. stream may be NULL. */
 GLIA_API int glia_b200_rf_score(const glia_rf* m, const double* X, size_t N, int D, int label, int* votes,
                        double* prob, int device_pointers, void* stream);
+/* Allocation-free variant of glia_b200_rf_score (prob only, DEVICE buffers).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The per-row vote table [N][nclass] that the vote-counting scorer needs as scratch
+ * lives in a static __device__ array of GLIA_NOALLOC_MAX_VOTES (1 Mi) int counters = 4 MiB, held by every GPU that loads
+ * the library until the process exits; the call itself runs no cudaMalloc / cudaFree / allocating library routine.
+ * d_rows [N][D] and d_prob [N] are device buffers on the forest's device; the work is queued on `stream` (may be NULL)
+ * and d_prob is complete when that stream has drained.  N * nclass > GLIA_NOALLOC_MAX_VOTES is rejected with
+ * GLIA_E_CAPACITY and a message in err (optional buffer of err_len bytes).  All calls on a device share the one
+ * array: each call clears the counters it uses first, and calls that overlap on the GPU (different streams with no
+ * ordering between them) race on it - serialise them.  Same votes, hence the same probabilities, as glia_b200_rf_score. */
+#define GLIA_NOALLOC_MAX_VOTES (1u << 20)
+GLIA_API int glia_b200_rf_score_noalloc(const glia_rf* m, const double* d_rows, size_t N, int D, int label,
+                                        double* d_prob, void* stream, char* err, size_t err_len);
+GLIA_API size_t glia_b200_rf_score_noalloc_max_votes(void);
 
 /* Timing of the last glia_b200_build/score call, measured with CUDA events on the handle's
  * stream: which = 0 voxel-pass kernel, 1 graph (compaction+sort+CSR), 2 featurise, 3 RF score,
