@@ -346,6 +346,7 @@ extern "C" int glia_b200_get_regions(glia_handle* h, uint32_t* label, uint32_t* 
   const RecLayout L = h->vp.reg;
   std::vector<uint32_t> lab, add, mx;
   int s;
+  if ((s = glia_ensure_full_regions(h))) return s;
   if ((s = d2h(h, lab, h->regLabel.p, (size_t)h->R))) return s;
   if ((s = d2h(h, add, h->cAdd.p, (size_t)h->R * L.nAdd))) return s;
   if ((s = d2h(h, mx, h->cMax.p, (size_t)h->R * L.nMax))) return s;
@@ -391,6 +392,7 @@ extern "C" int glia_b200_get_region_stats(glia_handle* h, int kind, int i, uint3
   int nk = kind == 0 ? h->prm.n_rimg : h->prm.n_rlimg;
   if (kind < 0 || kind > 1 || i < 0 || i >= nk) return GLIA_E_ARG;
   const Channel& c = h->vc.reg[kind == 0 ? i : h->prm.n_rimg + i];
+  { int s = glia_ensure_full_regions(h); if (s != GLIA_OK) return s; }
   return dump_stats(h, h->R, h->vp.reg, c.bins, c.addOff, c.maxOff, c.f64Off, h->cAdd.p, h->cMax.p,
                     h->cF64.p, hist, sum, sum2, mn, mx);
 }

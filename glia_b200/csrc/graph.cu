@@ -26,11 +26,14 @@ __global__ void gather_regions_kernel(const uint32_t* __restrict__ flags,
                                       const uint32_t* __restrict__ gMax,
                                       const double* __restrict__ gF64, uint32_t* __restrict__ label,
                                       uint32_t* __restrict__ cAdd, uint32_t* __restrict__ cMax,
-                                      double* __restrict__ cF64) {
+                                      double* __restrict__ cF64, const unsigned char* __restrict__ interest,
+                                      int world, int me) {
   uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (w >= n || !flags[w]) return;
   uint32_t r = rank[w];
   if (lane == 0) label[r] = w;
+  // sharded build: only the regions this rank featurises (its own and their neighbours) need their records here
+  if (interest && !interest[(size_t)r * world + me]) return;
   for (int i = lane; i < L.nAdd; i += 32) cAdd[(size_t)r * L.nAdd + i] = gAdd[(size_t)w * L.nAdd + i];
   for (int i = lane; i < L.nMax; i += 32) cMax[(size_t)r * L.nMax + i] = gMax[(size_t)w * L.nMax + i];
   for (int i = lane; i < L.nF64; i += 32) cF64[(size_t)r * L.nF64 + i] = gF64[(size_t)w * L.nF64 + i];
@@ -140,10 +143,13 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
                                           const double* __restrict__ sF64,
                                           uint32_t* __restrict__ aAdd, uint32_t* __restrict__ aMax,
                                           double* __restrict__ aF64, uint32_t* __restrict__ aMax2,
-                                          int* __restrict__ aOwn, long long lo, long long hi) {
+                                          int* __restrict__ aOwn, long long lo, long long hi,
+                                          const unsigned char* __restrict__ interest, int world, int me) {
   long long r = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (r >= R) return;
+  // sharded build: the boundaries of a region this rank neither owns nor neighbours are incomplete here and never read
+  if (interest && !interest[(size_t)r * world + me]) return;
   int e0 = row[r], e1 = row[r + 1];
   (void)lo; (void)hi;  // every region whose boundaries are complete here (owned or neighbour of owned) is used
   for (int i = lane; i < L.nAdd; i += 32) {
@@ -181,6 +187,7 @@ static inline unsigned nblk(long long n, int per) { return (unsigned)((n + per -
 
 int glia_finalize_regions(glia_handle* h);
 int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi);
+int glia_gather_regions_some(glia_handle* h, const unsigned char* interest, int world, int me);
 
 // Builds the finalised graph from the raw tables.  Returns a GLIA_* status.
 int glia_finalize_graph(glia_handle* h) {
@@ -226,7 +233,16 @@ int glia_index_regions(glia_handle* h) {
   return GLIA_OK;
 }
 
-int glia_gather_regions(glia_handle* h) {
+int glia_gather_regions(glia_handle* h) { return glia_gather_regions_some(h, nullptr, 1, 0); }
+
+// A handle whose region records were compacted for the regions of interest only gets the rest on demand (dumps, the
+// bc_feat stage on a sharded build: they read every region).
+int glia_ensure_full_regions(glia_handle* h) {
+  if (!h->regionsPartial) return GLIA_OK;
+  return glia_gather_regions(h);
+}
+
+int glia_gather_regions_some(glia_handle* h, const unsigned char* interest, int world, int me) {
   cudaStream_t st = h->stream;
   PhaseTrace tr(st);
   const VoxParams& P = h->vp;
@@ -239,8 +255,9 @@ int glia_gather_regions(glia_handle* h) {
   gather_regions_kernel<<<nblk((long long)LB * 32, 256), 256, 0, st>>>(
       h->flags.as<uint32_t>(), h->rank.as<uint32_t>(), LB, P.reg, h->regAdd.as<uint32_t>(),
       h->regMax.as<uint32_t>(), h->regF64.as<double>(), h->regLabel.as<uint32_t>(),
-      h->cAdd.as<uint32_t>(), h->cMax.as<uint32_t>(), h->cF64.as<double>());
+      h->cAdd.as<uint32_t>(), h->cMax.as<uint32_t>(), h->cF64.as<double>(), interest, world, me);
   h->launches++;
+  h->regionsPartial = interest != nullptr;
   CK(cudaGetLastError());
   tr.mark("regions: gather");
   return GLIA_OK;
@@ -359,7 +376,8 @@ int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi) {
     boundary_aggregate_kernel<<<nblk(R * 32, 256), 256, 0, st>>>(
         h->row.as<int>(), R, P.edge, h->sAdd.as<uint32_t>(), h->sMax.as<uint32_t>(),
         h->sF64.as<double>(), h->bAggAdd.as<uint32_t>(), h->bAggMax.as<uint32_t>(),
-        h->bAggF64.as<double>(), h->bAggMax2.as<uint32_t>(), h->bAggOwn.as<int>(), ownLo, ownHi);
+        h->bAggF64.as<double>(), h->bAggMax2.as<uint32_t>(), h->bAggOwn.as<int>(), ownLo, ownHi,
+        h->shardWorld > 1 ? h->interest.as<unsigned char>() : nullptr, h->shardWorld, h->shardMe);
     h->launches++;
   }
   CK(cudaGetLastError());

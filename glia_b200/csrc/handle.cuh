@@ -178,10 +178,13 @@ struct glia_handle {
   glia::DevBuf medReg, medCand, medQ[6];
   glia::DevBuf k5[40];                                    // scratch of the bc_feat stage (merge.cu), kept between calls
   bool hasMedian = false;
+  int shardWorld = 0, shardMe = 0;  // set by glia_b200_build_sharded around its graph finalisation (interest mask valid)
+  bool regionsPartial = false;  // compact region records hold the regions of interest only (sharded build)
   // large results to pageable host memory: two pinned staging buffers, D2H of chunk k+1 overlaps the host copy of chunk k
   void* pin[2] = {nullptr, nullptr};
   cudaEvent_t evPin[2] = {nullptr, nullptr};
 };
 
+int glia_ensure_full_regions(glia_handle* h);  // graph.cu
 // device -> (pageable) host copy of a large result on the handle's stream; returns when dst is complete (api.cu)
 int glia_copy_to_host(glia_handle* h, void* dst, const void* dsrc, size_t bytes);

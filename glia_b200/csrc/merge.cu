@@ -309,6 +309,7 @@ int glia_bc_feat_impl(glia_handle* h, const uint32_t* order, int64_t n64, const 
   CK(cudaMemcpyAsync(dLevelNodes, levelNodes.data(), 4 * (size_t)n, cudaMemcpyHostToDevice, st));
   CK(cudaMemsetAsync(dTopd, 0x7f, 4 * (size_t)R, st));
   // leaves: region records and boundary-of aggregates of the base regions
+  { int s = glia_ensure_full_regions(h); if (s != GLIA_OK) return s; }
   CK(cudaMemcpyAsync(rAdd, h->cAdd.p, 4 * (size_t)R * LR.nAdd, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(rMax, h->cMax.p, 4 * (size_t)R * LR.nMax, cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(rF64, h->cF64.p, 8 * (size_t)R * LR.nF64, cudaMemcpyDeviceToDevice, st));

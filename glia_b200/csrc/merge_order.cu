@@ -188,6 +188,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
   auto dl = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
     return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
   };
+  { int s = glia_ensure_full_regions(h); if (s != GLIA_OK) return s; }
   CK(dl(lab.data(), h->regLabel.p, 4 * (size_t)R));
   CK(dl(cAdd.data(), h->cAdd.p, 4 * cAdd.size())); CK(dl(cMax.data(), h->cMax.p, 4 * cMax.size()));
   CK(dl(cF64.data(), h->cF64.p, 8 * cF64.size()));

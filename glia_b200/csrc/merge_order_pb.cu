@@ -220,6 +220,7 @@ extern "C" int glia_b200_pre_merge(glia_handle* h, const int* size_thresholds, i
   pm.hasRpb.assign(2 * (size_t)R + 1, 0);
   std::vector<uint32_t> cAdd((size_t)R * LR.nAdd);
   std::vector<double> cF64((size_t)R * LR.nF64);
+  { int s = glia_ensure_full_regions(h); if (s != GLIA_OK) return s; }
   if (R) {
     CK(cudaMemcpyAsync(cAdd.data(), h->cAdd.p, 4 * cAdd.size(), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(cF64.data(), h->cF64.p, 8 * cF64.size(), cudaMemcpyDeviceToHost, st));

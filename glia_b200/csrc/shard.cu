@@ -20,6 +20,7 @@ int glia_finalize_regions(glia_handle* h);
 int glia_region_presence(glia_handle* h);
 int glia_index_regions(glia_handle* h);
 int glia_gather_regions(glia_handle* h);
+int glia_gather_regions_some(glia_handle* h, const unsigned char* interest, int world, int me);
 int glia_finalize_edges(glia_handle* h, long long ownLo, long long ownHi);
 int glia_build_raw(glia_handle* h, const uint32_t* labels, const uint32_t* mask, const float* pb);
 
@@ -514,10 +515,12 @@ extern "C" int glia_b200_build_sharded(glia_handle* h, glia_comm* c, const uint3
   const long long chunkR = std::max<long long>(1, (R + world - 1) / world);
   const long long lo = std::min<long long>(R, (long long)me * chunkR);
   const long long hi = me == world - 1 ? R : std::min<long long>(R, lo + chunkR);
+  h->shardWorld = world; h->shardMe = me;
   s = glia_finalize_edges(h, lo, std::min<long long>(hi, R));
+  h->shardWorld = 0;
   if (s != GLIA_OK) return s;
   CK(cudaStreamWaitEvent(st, c->evSide, 0));  // the reduced record tables
-  s = glia_gather_regions(h);
+  s = glia_gather_regions_some(h, h->interest.as<unsigned char>(), world, me);
   if (s != GLIA_OK) return s;
   CK(cudaEventRecord(c->evC, st));
   int importOvf = 0;
