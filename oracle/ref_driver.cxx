@@ -23,6 +23,8 @@
 #include "util/struct_merge.hxx"
 #include "hmt/tree_build.hxx"
 #include "hmt/tree_greedy.hxx"
+#include "hmt/bc_label.hxx"
+#include <queue>
 #include "util/mp.hxx"
 
 using namespace glia;
@@ -454,6 +456,96 @@ int glia_ref_segment_greedy(const int* dims, const uint32_t* labels, const uint3
   G.out_labels.assign(px, px + n);
   for (auto const& pk : picks) { G.order.push_back((uint32_t)pk.first); G.order.push_back((uint32_t)pk.second); G.order.push_back(0); }
   for (int i = 0; i < nTree; ++i) for (auto const& tn : trees[i]) G.sal.push_back(tn.data.potential);
+  return 0;
+}
+
+// ---- hmt/main_bc_label_ri.cxx:31-155 (boundary-classifier training labels from a truth image) ----
+// The label functions are the reference's own templates (hmt/bc_label.hxx:44-122, util/image_stats.hxx:173-245,
+// util/stats.hxx:186-265), instantiated with __int128 where the reference's main uses boost's int512_t (boost is not
+// in this image; the pair counts of these inputs are far below 2^63, so both integer types hold the same values).
+// The option logic around them (optSplit, globalOpt 1 / 2) lives in the main file and is restated here.
+typedef __int128 RefInt;
+struct LabelNodeData { Label label; std::vector<int> bestSplits; int bcLabel = BC_LABEL_MERGE; };
+int glia_ref_bc_label(const int* dims, const uint32_t* labels, const uint32_t* maskBuf, const uint32_t* truth,
+                      const uint32_t* orderIn, int nOrder, int usePairF1, int optSplit, int globalOpt, int tweak,
+                      double maxPrecDrop)
+{
+  G = Results();
+  auto segImage = wrap<LImage>(labels, dims);
+  auto truthImage = wrap<LImage>(truth, dims);
+  LImage::Pointer mask = maskBuf ? wrap<LImage>(maskBuf, dims) : LImage::Pointer(nullptr);
+  std::vector<TTriple<Label>> order;
+  for (int i = 0; i < nOrder; ++i) order.emplace_back(orderIn[3 * i], orderIn[3 * i + 1], orderIn[3 * i + 2]);
+  RegionMap rmap(segImage, mask, order, false);
+  int n = order.size();
+  std::vector<int> bcLabels;
+  std::vector<double> mergeF1s(n, 0.0), splitF1s(n, 0.0);
+  if (globalOpt == 0) {
+    bcLabels.resize(n);
+    if (usePairF1) {
+      for (int i = 0; i < n; ++i)
+        bcLabels[i] = genBoundaryClassificationLabelF1<RefInt>(mergeF1s[i], splitF1s[i], rmap, order[i].x0, order[i].x1,
+                                                               order[i].x2, truthImage, tweak != 0, maxPrecDrop);
+      if (optSplit) {
+        std::unordered_map<Label, std::vector<RegionMap::Region const*>> smap;
+        for (int i = 0; i < n; ++i) {
+          auto sit0 = citerator(smap, order[i].x0, 1, &rmap.find(order[i].x0)->second);
+          auto sit1 = citerator(smap, order[i].x1, 1, &rmap.find(order[i].x1)->second);
+          std::vector<RegionMap::Region const*> pSplitRegions, pMergeRegions{&rmap.find(order[i].x2)->second};
+          append(pSplitRegions, sit0->second, sit1->second);
+          if (bcLabels[i] == BC_LABEL_SPLIT) { splice(smap[order[i].x2], pSplitRegions); }
+          else {
+            double optSplitF1, optSplitPrec, optSplitRec;
+            stats::pairF1<RefInt>(optSplitF1, optSplitPrec, optSplitRec, pSplitRegions, truthImage, {BG_VAL});
+            if (mergeF1s[i] > optSplitF1) { splice(smap[order[i].x2], pMergeRegions); }
+            else { bcLabels[i] = BC_LABEL_SPLIT; splice(smap[order[i].x2], pSplitRegions); }
+          }
+        }
+      }
+    } else {
+      for (int i = 0; i < n; ++i)
+        bcLabels[i] = genBoundaryClassificationLabelRI<RefInt>(mergeF1s[i], splitF1s[i], rmap, order[i].x0, order[i].x1,
+                                                               order[i].x2, truthImage);
+    }
+  } else {
+    typedef TTree<LabelNodeData> Tree;
+    Tree tree;
+    genTree(tree, order, [](Tree::Node& node, Label r) { node.data.label = r; });
+    for (auto& node : tree) {
+      if (node.isLeaf()) { node.data.bcLabel = BC_LABEL_MERGE; node.data.bestSplits.push_back(node.self); }
+      else {
+        std::vector<RegionMap::Region const*> pMergeRegions{&rmap.find(node.data.label)->second};
+        std::vector<RegionMap::Region const*> pSplitRegions;
+        for (auto c : node.children)
+          for (auto j : tree[c].data.bestSplits) pSplitRegions.push_back(&rmap.find(tree[j].data.label)->second);
+        double mergeF1 = stats::pairF1<RefInt>(pMergeRegions, truthImage, {BG_VAL});
+        double splitF1 = stats::pairF1<RefInt>(pSplitRegions, truthImage, {BG_VAL});
+        if (mergeF1 > splitF1) { node.data.bcLabel = BC_LABEL_MERGE; node.data.bestSplits.push_back(node.self); }
+        else {
+          node.data.bcLabel = BC_LABEL_SPLIT;
+          for (auto c : node.children) for (auto j : tree[c].data.bestSplits) node.data.bestSplits.push_back(j);
+        }
+      }
+    }
+    if (globalOpt == 1) {
+      std::queue<int> q;
+      q.push(tree.root());
+      while (!q.empty()) {
+        int ni = q.front(); q.pop();
+        if (tree[ni].data.bcLabel == BC_LABEL_MERGE)
+          tree.traverseDescendants(ni, [](Tree::Node& node) { node.data.bcLabel = BC_LABEL_MERGE; });
+        else for (auto c : tree[ni].children) q.push(c);
+      }
+    } else {
+      for (auto const& node : tree)
+        if (node.data.bcLabel == BC_LABEL_SPLIT)
+          tree.traverseAncestors(node.self, [](Tree::Node& tn) { tn.data.bcLabel = BC_LABEL_SPLIT; });
+    }
+    for (auto const& node : tree) if (!node.isLeaf()) bcLabels.push_back(node.data.bcLabel);
+  }
+  for (int v : bcLabels) G.order.push_back((uint32_t)(int32_t)v);
+  G.sal = mergeF1s;
+  G.cand_scores = splitF1s;
   return 0;
 }
 

@@ -365,6 +365,23 @@ def ref_run_pb(mode, labels, pb, mask=None, type=1, size_thr=(), rpb_thr=0.0):
     return out
 
 
+def ref_bc_label(labels, truth, order, mask=None, use_f1=True, opt_split=False, global_opt=0, tweak=False, max_prec_drop=1.0):
+    """The compiled reference's bc_label_ri logic (oracle/ref_driver.cxx glia_ref_bc_label): (labels, merge scores, split
+    scores)."""
+    labels = np.ascontiguousarray(labels, np.uint32)
+    truth = np.ascontiguousarray(truth, np.uint32)
+    ndim = labels.ndim
+    L = ref_lib(ndim)
+    dims = (C.c_int * 3)(*(list(labels.shape[::-1]) + [1] * (3 - ndim)))
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint32)
+    o = np.ascontiguousarray(order, np.uint32)
+    st = L.glia_ref_bc_label(dims, _ptr(labels), _ptr(m), _ptr(truth), _ptr(o), C.c_int(len(o)), C.c_int(int(use_f1)),
+                             C.c_int(int(opt_split)), C.c_int(global_opt), C.c_int(int(tweak)), C.c_double(max_prec_drop))
+    assert st == 0
+    return (_ref_get(L, "order", np.uint32).view(np.int32), _ref_get(L, "sal", np.float64),
+            _ref_get(L, "cand_scores", np.float64))
+
+
 def ref_segment_greedy(labels, orders, merge_probs=None, region_probs=None, mask=None, ignore=True):
     """The compiled reference's segment_greedy call sequence (oracle/ref_driver.cxx glia_ref_segment_greedy):
     returns (final labels, picks [(tree, node)], potentials of all trees' nodes concatenated)."""

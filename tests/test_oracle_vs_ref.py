@@ -364,3 +364,44 @@ def test_segment_greedy_matches_reference(case, variant):
     assert np.array_equal(np.concatenate(got_pot), want_pot)
     assert np.array_equal(np.array(got_picks, np.int64).reshape(-1, 2), want_picks)
     assert np.array_equal(got_lab, want_lab)
+
+
+# ---- bc label generation (hmt/main_bc_label_ri.cxx)
+def _truth(lab, seed, ntruth):
+    """A coarser segmentation: superpixels grouped at random into ntruth truth segments, 10 % of the voxels moved to
+    another segment, 6 % background (0 = BG_VAL, excluded from the pair counts)."""
+    rng = np.random.default_rng(seed + 500)
+    group = rng.integers(1, ntruth + 1, size=int(lab.max()) + 1).astype(np.uint32)
+    t = group[lab]
+    noise = rng.random(lab.shape)
+    t = np.where(noise < 0.10, rng.integers(1, ntruth + 1, size=lab.shape).astype(np.uint32), t)
+    t[noise > 0.94] = 0
+    return t.astype(np.uint32)
+
+
+BCL_VARIANTS = [dict(), dict(tweak=True), dict(max_prec_drop=0.05), dict(opt_split=True), dict(use_f1=False),
+                dict(global_opt=1), dict(global_opt=2), dict(tweak=True, max_prec_drop=0.2, opt_split=True)]
+
+
+@pytest.mark.parametrize("kw", BCL_VARIANTS, ids=lambda k: "-".join("%s=%s" % i for i in k.items()) or "default")
+@pytest.mark.parametrize("case", [((24, 28), 30, 91, False, 5), ((21, 26), 22, 92, True, 3), ((8, 10, 9), 14, 93, True, 4)])
+def test_bc_label_matches_reference(case, kw):
+    """Labels (and the F1 / RI scores behind them) of the Python restatement against the reference's own label templates
+    (instantiated with __int128 for boost's int512_t) on a greedy merge order."""
+    shape, nl, seed, um, ntruth = case
+    if not _have_ref(len(shape)):
+        pytest.skip("oracle/_ref not available")
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import bc_label_oracle as bo
+    lab, pb, mask = _make(shape, nl, seed, um)
+    truth = _truth(lab, seed, ntruth)
+    order = ol.Oracle(lab, pb, ol.default_config(pb), mask=mask).greedy(fn=quant_pred)["order"]
+    want, wm, ws = ol.ref_bc_label(lab, truth, order, mask=mask, **kw)
+    got, gm, gs = bo.bc_labels(lab, truth, order, mask=mask, **kw)
+    assert len(want) == len(order)
+    assert np.array_equal(got, want)
+    if kw.get("global_opt", 0) == 0:
+        assert np.array_equal(gm, wm, equal_nan=True) and np.array_equal(gs, ws, equal_nan=True)
+    if not kw:
+        assert len(set(want.tolist())) == 2   # both labels occur: the test discriminates
