@@ -64,7 +64,7 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
            "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms",
            "glia_b200_bc_feat_sharded", "glia_b200_merge_order_pb", "glia_b200_pre_merge",
-           "glia_b200_segment_greedy", "glia_b200_rf_score_noalloc", "glia_b200_rf_score_noalloc_max_votes"]
+           "glia_b200_segment_greedy", "glia_b200_rf_score_noalloc", "glia_b200_rf_score_noalloc_max_votes", "glia_b200_bc_label"]
 
 
 def lib():
@@ -106,6 +106,7 @@ def lib():
         L.glia_b200_rf_score_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int, vp, vp, C.c_char_p, C.c_size_t]
         L.glia_b200_rf_score_noalloc_max_votes.argtypes = []
         L.glia_b200_rf_score_noalloc_max_votes.restype = C.c_size_t
+        L.glia_b200_bc_label.argtypes = [vp, vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, vp, vp, vp]
         L.glia_b200_segment_greedy.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_merge_order_pb.argtypes = [vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_pre_merge.argtypes = [vp, vp, C.c_int, C.c_double, vp, vp, C.POINTER(C.c_int64), vp]
@@ -472,6 +473,18 @@ class MergeTreeBuilder:
         self._check(lib().glia_b200_pre_merge(self.h, _addr(thr), len(thr), C.c_double(rpb_thr), _addr(order), _addr(sal),
                                               C.byref(nm), _addr(out)))
         return dict(order=order[:nm.value], sal=sal[:nm.value], labels=out)
+
+    def bc_label(self, truth, order, use_f1=True, opt_split=False, global_opt=0, tweak=False, max_prec_drop=1.0):
+        """hmt/main_bc_label_ri.cxx: (labels [n] in {-1 merge, +1 split}, merge scores, split scores)."""
+        order = np.ascontiguousarray(order, np.uint32)
+        if not self.device_pointers:
+            truth = np.ascontiguousarray(truth, np.uint32)
+        n = len(order)
+        out = np.zeros(n, np.int32)
+        ms, ss = np.zeros(n), np.zeros(n)
+        self._check(lib().glia_b200_bc_label(self.h, _addr(truth), _addr(order), n, int(use_f1), int(opt_split), int(global_opt),
+                                             int(tweak), C.c_double(max_prec_drop), _addr(out), _addr(ms), _addr(ss)))
+        return out, ms, ss
 
     def segment_greedy(self, orders, merge_probs=None, region_probs=None, ignore_missing=True):
         """hmt/main_segment_greedy.cxx: resolve one or more merge trees; returns (labels, picks [(tree, node)])."""

@@ -136,6 +136,19 @@ GLIA_API int glia_b200_segment_greedy(glia_handle* h, int n_trees, const uint32_
                                       const double* const* merge_probs, const double* const* region_probs,
                                       int ignore_missing, uint32_t* labels_out, int32_t* picks, int64_t* n_picks);
 
+/* SURVEY section 8f rank 2.  Boundary-classifier training labels from a ground-truth segmentation
+ * (hmt/main_bc_label_ri.cxx:31-155; hmt/bc_label.hxx:44-122; util/image_stats.hxx:173-245; util/stats.hxx:186-265):
+ * for every merge of `order` decide BC_LABEL_MERGE (-1) or BC_LABEL_SPLIT (+1) by comparing the pixel-pair F1 score
+ * (use_pair_f1, the reference's default) or the Rand index of the merged region against that of the two parts, counted
+ * against `truth` (same extent as the label volume, host or device as the handle's inputs; truth label 0 is background
+ * and excluded; masked-out voxels are in no region).  tweak / max_prec_drop: the reference's -w / -d rules;
+ * opt_split: compare against the best split of the two sides found so far (-p); global_opt 0: every merge on its own,
+ * 1 / 2: best splits bottom-up, then path consistency by merging / by splitting (-g).  bc_labels [n] (host);
+ * merge_score / split_score [n] (host, optional): the F1 or Rand index values behind the labels (global_opt 0). */
+GLIA_API int glia_b200_bc_label(glia_handle* h, const uint32_t* truth, const uint32_t* order, int64_t n,
+                                int use_pair_f1, int opt_split, int global_opt, int tweak, double max_prec_drop,
+                                int32_t* bc_labels, double* merge_score, double* split_score);
+
 /* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
  * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
  * kernel, "slots": its shared-memory table slots (0 = default); "notma": value != 0 makes the generic voxel kernel

@@ -22,7 +22,7 @@ def _write_mha(path, arr, met_type):
 
 
 def test_binaries_exist_and_print_usage():
-    for name in ("merge_order_bc", "bc_feat", "pred_rf", "merge_order_pb", "pre_merge", "segment_greedy"):
+    for name in ("merge_order_bc", "bc_feat", "pred_rf", "merge_order_pb", "pre_merge", "segment_greedy", "bc_label_ri"):
         p = os.path.join(BIN, name)
         if not os.path.exists(p):
             api.build_library()

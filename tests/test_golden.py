@@ -309,3 +309,42 @@ def test_cuda_reproduces_seg_golden(path):
                                  ignore_missing=ignore)
         assert np.array_equal(pk.astype(np.int64), z["picks_" + tag]), tag
         assert np.array_equal(l, z["labels_" + tag]), tag
+
+
+# ---------------------------------------------------------------- bc label generation
+LGOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bclabel", "*.npz")))
+BCL_VARIANTS = {"default": dict(), "tweak": dict(tweak=True), "mpd": dict(max_prec_drop=0.05), "optsplit": dict(opt_split=True),
+                "ri": dict(use_f1=False), "g1": dict(global_opt=1), "g2": dict(global_opt=2)}
+
+
+def test_bclabel_fixtures_present():
+    assert len(LGOLD) >= 3
+
+
+@pytest.mark.parametrize("path", LGOLD, ids=[os.path.basename(p)[:-4] for p in LGOLD])
+def test_python_oracle_reproduces_bclabel_golden(path):
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import bc_label_oracle as bo
+    z = np.load(path)
+    mask = z["mask"] if z["mask"].size else None
+    for tag, kw in BCL_VARIANTS.items():
+        l, ms, ss = bo.bc_labels(z["labels"], z["truth"], z["order"], mask=mask, **kw)
+        assert np.array_equal(l, z["bc_" + tag]), tag
+        if kw.get("global_opt", 0) == 0:
+            assert np.array_equal(ms, z["ms_" + tag], equal_nan=True) and np.array_equal(ss, z["ss_" + tag], equal_nan=True), tag
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", LGOLD, ids=[os.path.basename(p)[:-4] for p in LGOLD])
+def test_cuda_reproduces_bclabel_golden(path):
+    from glia_b200 import api
+    z = np.load(path)
+    lab = z["labels"]
+    mask = z["mask"] if z["mask"].size else None
+    g = api.MergeTreeBuilder(lab.shape, api.FeatureConfig(thr=())).build(lab, np.zeros(lab.shape, np.float32), mask)
+    for tag, kw in BCL_VARIANTS.items():
+        l, ms, ss = g.bc_label(z["truth"], z["order"], **kw)
+        assert np.array_equal(l, z["bc_" + tag]), tag
+        if kw.get("global_opt", 0) == 0:   # integer pair counts -> the same doubles, bit for bit
+            assert np.array_equal(ms, z["ms_" + tag], equal_nan=True) and np.array_equal(ss, z["ss_" + tag], equal_nan=True), tag

@@ -167,3 +167,65 @@ def test_cli_segment_greedy(tmp_path):
     assert r.returncode == 0, r.stderr
     want, _, _ = so.segment_greedy(lab, orders, merge_probs=probs, mask=mask, ignore=True)
     assert np.array_equal(np.load(out_f), want)
+
+
+# ---------------------------------------------------------------- bc label generation
+def _truth_of(lab, seed, ntruth):
+    rng = np.random.default_rng(seed + 500)
+    group = rng.integers(1, ntruth + 1, size=int(lab.max()) + 1).astype(np.uint32)
+    t = group[lab]
+    noise = rng.random(lab.shape)
+    t = np.where(noise < 0.10, rng.integers(1, ntruth + 1, size=lab.shape).astype(np.uint32), t)
+    t[noise > 0.94] = 0
+    return t.astype(np.uint32)
+
+
+BCL_KW = [dict(), dict(tweak=True), dict(max_prec_drop=0.05), dict(opt_split=True), dict(use_f1=False), dict(global_opt=1),
+          dict(global_opt=2), dict(tweak=True, max_prec_drop=0.2, opt_split=True)]
+
+
+@pytest.mark.parametrize("case", [((30, 36), 60, 111, False, 6), ((28, 31), 40, 112, True, 4), ((9, 12, 11), 30, 113, True, 3)])
+def test_bc_label_matches_oracle(case):
+    """hmt/main_bc_label_ri.cxx: labels and the F1 / Rand-index values behind them against the voxel-set-by-voxel-set
+    Python restatement (pinned to the reference's templates), every option; a prefix of the order (a forest) as well."""
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import bc_label_oracle as bo
+    shape, nl, seed, um, ntruth = case
+    lab, pb, mask = _make(shape, nl, seed, um)
+    truth = _truth_of(lab, seed, ntruth)
+    order = ol.Oracle(lab, pb, ol.default_config(pb), mask=mask).greedy(
+        fn=lambda row: float(np.floor((np.sum(np.abs(row[:12])) * 3.7 % 1.0) * 8) / 8.0))["order"]
+    g = api.MergeTreeBuilder(shape, api.FeatureConfig(thr=())).build(lab, np.zeros(shape, np.float32), mask)
+    for kw in BCL_KW:
+        for o in (order, order[:len(order) // 2]):
+            want, wm, ws = bo.bc_labels(lab, truth, o, mask=mask, **kw)
+            got, gm, gs = g.bc_label(truth, o, **kw)
+            assert np.array_equal(got, want), kw
+            if kw.get("global_opt", 0) == 0:
+                assert np.array_equal(gm, wm, equal_nan=True) and np.array_equal(gs, ws, equal_nan=True), kw
+    with pytest.raises(api.GliaError):
+        bad = order.copy(); bad[0, 0] = 4000000
+        g.bc_label(truth, bad)
+
+
+def test_cli_bc_label_ri(tmp_path):
+    import sys
+    sys.path.insert(0, ol.ORACLE_DIR)
+    import bc_label_oracle as bo
+    shape = (32, 40)
+    lab, pb, mask = _make(shape, 50, 114, True)
+    truth = _truth_of(lab, 114, 5)
+    order = ol.Oracle(lab, pb, ol.default_config(pb), mask=mask).merge_order_pb(2)["order"] if False else \
+        ol.Oracle(lab, pb, ol.default_config(pb), mask=mask).greedy(fn=lambda row: float(np.sum(row[:5]) % 1.0))["order"]
+    seg_f, mask_f, truth_f = str(tmp_path / "seg.npy"), str(tmp_path / "mask.npy"), str(tmp_path / "truth.npy")
+    order_f, out_f = str(tmp_path / "order.txt"), str(tmp_path / "bclabel.txt")
+    np.save(seg_f, lab); np.save(mask_f, mask.astype(np.uint8)); np.save(truth_f, truth.astype(np.uint16))
+    np.savetxt(order_f, order, fmt="%d")
+    for flags, kw in (([], dict()), (["-g", "2"], dict(global_opt=2)), (["-p", "1", "-w", "1", "-d", "0.2"], dict(opt_split=True, tweak=True, max_prec_drop=0.2)),
+                      (["--f1", "0"], dict(use_f1=False))):
+        r = subprocess.run([os.path.join(BIN, "bc_label_ri"), "-s", seg_f, "-o", order_f, "-t", truth_f, "-n", mask_f, "-l", out_f] + flags,
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        want, _, _ = bo.bc_labels(lab, truth, order, mask=mask, **kw)
+        assert np.array_equal(np.loadtxt(out_f, dtype=np.int64), want), flags
