@@ -1039,3 +1039,134 @@ int go_pre_merge(go_state* s, const int* size_thr, int n_thr, double rpb_thr, ui
   free(c.size); free(c.sum); free(c.rpb); free(c.has_rpb);
   return M;
 }
+
+/* ------------------------------------------------------------------------
+ * section-classifier features of region pairs across two 2D
+ * sections (hmt/main_sc_feat.cxx:27-117; hmt/sc_feat.hxx:10-170;
+ * type/feat.hxx:124-132 shape differences, :191-268 advanced shape (central /
+ * Hu moments, eccentricity), :290-370 location, :373-440 set differences;
+ * alg/geometry.hxx:44-108; util/image_stats.hxx:308-335 overlaps).
+ * Row = RegionPairFeats | RegionFeatsWithLocation(smaller) | ...(larger).
+ * ---------------------------------------------------------------------- */
+typedef struct { double centroid[2]; double cm[7], hu[7], ecc; } advshape;
+
+/* type/feat.hxx:336-344 (centroid / (size * normLen)), alg/geometry.hxx:44-108, type/feat.hxx:223-243 */
+static void adv_shape(const uint32_t* L, const uint32_t* M, const int* dims, uint32_t label, double normLen, advshape* a) {
+  double sx = 0, sy = 0; size_t n = 0;
+  for (int y = 0; y < dims[1]; ++y)
+    for (int x = 0; x < dims[0]; ++x) {
+      size_t p = (size_t)y * dims[0] + x;
+      if (L[p] != label || (M && M[p] == 0)) continue;
+      sx += x; sy += y; ++n;
+    }
+  double siz = (double)n * normLen;
+  a->centroid[0] = sx / siz; a->centroid[1] = sy / siz;
+  double ms[7] = {0, 0, 0, 0, 0, 0, 0};
+  for (int y = 0; y < dims[1]; ++y)
+    for (int x = 0; x < dims[0]; ++x) {
+      size_t p = (size_t)y * dims[0] + x;
+      if (L[p] != label || (M && M[p] == 0)) continue;
+      double dx = x - a->centroid[0], dy = y - a->centroid[1]; /* about the NORMALISED centroid, as the reference does */
+      double dx2 = dx * dx, dy2 = dy * dy;
+      ms[0] += dy2; ms[1] += dy2 * dy; ms[2] += dx * dy; ms[3] += dx * dy2; ms[4] += dx2; ms[5] += dx2 * dy; ms[6] += dx2 * dx;
+    }
+  double m00 = (double)n, m002 = m00 * m00, m003 = pow(m00, 2.5), s[7];
+  s[0] = sdivide(ms[0], m002, 0.0); s[1] = sdivide(ms[1], m003, 0.0); s[2] = sdivide(ms[2], m002, 0.0);
+  s[3] = sdivide(ms[3], m003, 0.0); s[4] = sdivide(ms[4], m002, 0.0); s[5] = sdivide(ms[5], m003, 0.0);
+  s[6] = sdivide(ms[6], m003, 0.0);
+  if (normLen > 0.0) { /* feat.hxx:231-240: m21 is divided by L^2 there */
+    double l2 = normLen * normLen, l3 = l2 * normLen;
+    ms[0] /= l2; ms[1] /= l3; ms[2] /= l2; ms[3] /= l3; ms[4] /= l2; ms[5] /= l2; ms[6] /= l3;
+  }
+  memcpy(a->cm, ms, sizeof(ms));
+  double m02 = s[0], m03 = s[1], m11 = s[2], m12 = s[3], m20 = s[4], m21 = s[5], m30 = s[6];
+  a->hu[0] = m20 + m02;
+  a->hu[1] = pow(m20 - m02, 2) + 4.0 * m11 * m11;
+  a->hu[2] = pow(m30 - 3.0 * m12, 2) + pow(3.0 * m21 - m03, 2);
+  a->hu[3] = pow(m30 + m12, 2) + pow(m21 + m03, 2);
+  a->hu[4] = (m30 - 3.0 * m12) * (m30 + m12) * (pow(m30 + m12, 2) - 3.0 * pow(m21 + m03, 2)) +
+             (3.0 * m21 - m03) * (m21 + m03) * (3.0 * pow(m30 + m12, 2) - pow(m21 + m03, 2));
+  a->hu[5] = (m20 - m02) * (pow(m30 + m12, 2) - pow(m21 + m03, 2)) + 4.0 * m11 * (m30 + m12) * (m03 + m21);
+  a->hu[6] = (3.0 * m21 - m03) * (m12 + m30) * (pow(m30 + m12, 2) - 3.0 * pow(m21 + m03, 2)) -
+             (m30 - 3.0 * m12) * (m12 + m03) * (3.0 * pow(m30 + m12, 2) - pow(m21 + m03, 2));
+  double ea = a->cm[4] + a->cm[0], eb = ssqrt(pow(a->cm[4] - a->cm[0], 2) + 4.0 * a->cm[2] * a->cm[2], 0.0);
+  a->ecc = sdivide(ea + eb, ea - eb, 0.0);
+}
+
+int go_sc_row_dim(const go_state* s) {
+  const go_cfg* c = &s->cfg;
+  int real = c->use_median ? 5 : 4;
+  int xi = s->D + 4 + 2 * c->n_thr + 15;
+  for (int i = 0; i < c->n_rimg; ++i) xi += (c->use_hist ? s->rs[i].bins : 0) + 1 + real;
+  for (int i = 0; i < c->n_rlimg; ++i) xi += (c->use_hist ? s->rls[i].bins : 0) + 1;
+  for (int i = 0; i < c->n_bimg; ++i) xi += (c->use_hist ? s->bs[i].bins : 0) + 1 + real;
+  return 6 + 1 + 8 + 15 + (3 + real) * (c->n_rimg + c->n_rlimg) + 2 * xi;
+}
+
+/* pairs [n][2] = (label in section 0, label in section 1); rows [n][go_sc_row_dim].  s0 / s1 were built from the two
+ * sections with the same feature configuration (use_log is taken from the argument, normalisation from norm_*;
+ * norm_* <= 0 = image volume / diagonal).  Returns 0, or -1 for an unknown label / unsupported configuration. */
+int go_sc_feat(go_state* s0, go_state* s1, const uint32_t* L0, const uint32_t* M0, const uint32_t* L1, const uint32_t* M1,
+               const uint32_t* pairs, int n, double norm_area, double norm_len, int use_log, double* rows) {
+  if (s0->D != 2 || s1->D != 2 || s0->cfg.use_median || s0->cfg.n_rlimg > s0->cfg.n_rimg) return -1;
+  const int* dims = s0->cfg.dims;
+  const go_cfg* c = &s0->cfg;
+  double vol = (double)dims[0] * dims[1], diag = sqrt((double)dims[0] * dims[0] + (double)dims[1] * dims[1]);
+  if (norm_area <= 0.0) norm_area = vol;
+  if (norm_len <= 0.0) norm_len = diag;
+  go_state* ss[2] = {s0, s1};
+  for (int k = 0; k < 2; ++k) { ss[k]->normArea = norm_area; ss[k]->normLen = norm_len; ss[k]->cfg.use_log = use_log; }
+  int dim = go_sc_row_dim(s0);
+  size_t N = (size_t)dims[0] * dims[1];
+  for (int i = 0; i < n; ++i) {
+    int a = find_u32(s0->label, s0->R, pairs[2 * i]), b = find_u32(s1->label, s1->R, pairs[2 * i + 1]);
+    if (a < 0 || b < 0) return -1;
+    regfeat f[2]; advshape as[2];
+    region_feats(s0, &a, 1, &f[0], NULL);
+    region_feats(s1, &b, 1, &f[1], NULL);
+    adv_shape(L0, M0, dims, pairs[2 * i], norm_len, &as[0]);
+    adv_shape(L1, M1, dims, pairs[2 * i + 1], norm_len, &as[1]);
+    long ov = 0; /* util/image_stats.hxx:308-335: both unmasked, both non-background */
+    if (pairs[2 * i] != 0 && pairs[2 * i + 1] != 0)
+      for (size_t p = 0; p < N; ++p)
+        if (L0[p] == pairs[2 * i] && L1[p] == pairs[2 * i + 1] && (!M0 || M0[p]) && (!M1 || M1[p])) ++ov;
+    double* p = rows + (size_t)i * dim;
+    /* RegionPairFeats (sc_feat.hxx:119-147), logs as RegionPairFeats::log */
+    double areaDiff = fabs(f[0].area - f[1].area), perimDiff = fabs(f[0].perim - f[1].perim);
+    *p++ = use_log ? slog(areaDiff, 0) : areaDiff;
+    *p++ = sdivide(areaDiff, f[0].area, 0.0); *p++ = sdivide(areaDiff, f[1].area, 0.0);
+    *p++ = use_log ? slog(perimDiff, 0) : perimDiff;
+    *p++ = sdivide(perimDiff, f[0].perim, 0.0); *p++ = sdivide(perimDiff, f[1].perim, 0.0);
+    double d0 = as[0].centroid[0] - as[1].centroid[0], d1 = as[0].centroid[1] - as[1].centroid[1];
+    double dist = ssqrt(d0 * d0 + d1 * d1, 0.0);
+    if (use_log) { double l = slog(dist, 0.0); dist = l > 0.0 ? l : 0.0; }
+    *p++ = dist;
+    double o = (double)ov, sd0 = f[0].area - o, sd1 = f[1].area - o, sym = sd0 + sd1; /* areas are the normalised ones */
+    *p++ = use_log ? slog(o, 0) : o; *p++ = use_log ? slog(sd0, 0) : sd0; *p++ = use_log ? slog(sd1, 0) : sd1;
+    *p++ = use_log ? slog(sym, 0) : sym;
+    *p++ = o / f[0].area; *p++ = o / f[1].area; *p++ = sd0 / f[0].area; *p++ = sd1 / f[1].area;
+    for (int k = 0; k < 7; ++k) { double d = fabs(as[0].cm[k] - as[1].cm[k]); *p++ = use_log ? slog(d, 0) : d; }
+    for (int k = 0; k < 7; ++k) *p++ = fabs(as[0].hu[k] - as[1].hu[k]);
+    *p++ = fabs(as[0].ecc - as[1].ecc);
+    for (int pass = 0; pass < 2; ++pass) { /* imageRegionDiff, then labelImageRegionDiff - which reads region[i] too (:136-146) */
+      int cnt = pass ? c->n_rlimg : c->n_rimg;
+      for (int k = 0; k < cnt; ++k) {
+        const imgfeat *x = &f[0].region[k], *y = &f[1].region[k];
+        *p++ = dist_l1(x->hist, y->hist, s0->rs[k].bins);
+        *p++ = dist_x2(x->hist, y->hist, s0->rs[k].bins);
+        *p++ = fabs(x->entropy - y->entropy);
+        *p++ = fabs(x->mean - y->mean); *p++ = fabs(x->stddev - y->stddev);
+        *p++ = fabs(x->mn - y->mn); *p++ = fabs(x->mx - y->mx);
+      }
+    }
+    int first = f[0].area > f[1].area ? 1 : 0; /* keep region 0 area <= region 1 area (:98-101) */
+    for (int k = 0; k < 2; ++k) {
+      int w = k ? 1 - first : first;
+      push_region(ss[w], &f[w], &p);
+      for (int j = 0; j < 7; ++j) *p++ = as[w].cm[j];
+      for (int j = 0; j < 7; ++j) *p++ = as[w].hu[j];
+      *p++ = as[w].ecc;
+    }
+  }
+  return 0;
+}

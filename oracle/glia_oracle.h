@@ -88,6 +88,12 @@ int go_merge_order_pb(go_state* s, int type, uint32_t* order, double* sal);
 int go_pre_merge(go_state* s, const int* size_thr, int n_thr, double rpb_thr, uint32_t* order, double* sal,
                  const uint32_t* labels_in, const uint32_t* mask, uint32_t* labels_out);
 
+/* section-classifier features (hmt/main_sc_feat.cxx:27-117) of region pairs across two 2D sections;
+ * pairs [n][2] = (label in section 0, label in section 1), rows [n][go_sc_row_dim].  norm_* <= 0: image volume / diagonal. */
+int go_sc_row_dim(const go_state* s);
+int go_sc_feat(go_state* s0, go_state* s1, const uint32_t* L0, const uint32_t* M0, const uint32_t* L1, const uint32_t* M1,
+               const uint32_t* pairs, int n, double norm_area, double norm_len, int use_log, double* rows);
+
 /* ---- random forest (rf_oracle.c) ---- */
 rf_oracle* rf_oracle_load(const char* path);  /* rf_old binary model file */
 rf_oracle* rf_oracle_from_arrays(int ntree, int nrnodes, int nclass, int mdim,

@@ -24,6 +24,9 @@
 #include "hmt/tree_build.hxx"
 #include "hmt/tree_greedy.hxx"
 #include "hmt/bc_label.hxx"
+#ifndef GLIA_3D
+#include "hmt/sc_feat.hxx"
+#endif
 #include <queue>
 #include "util/mp.hxx"
 
@@ -548,6 +551,66 @@ int glia_ref_bc_label(const int* dims, const uint32_t* labels, const uint32_t* m
   G.cand_scores = splitF1s;
   return 0;
 }
+
+#ifndef GLIA_3D
+// ---- hmt/main_sc_feat.cxx:27-117 (section-classifier features of region pairs across two 2D
+// sections: RegionFeatsWithLocation incl. central / Hu moments and eccentricity, RegionPairFeats incl. overlaps).
+// The feature classes are the reference's own (hmt/sc_feat.hxx, type/feat.hxx, alg/geometry.hxx); the call sequence of
+// the main file is restated.  pairs: [n][2] = (label in section 0, label in section 1).
+int glia_ref_sc_feat(const int* dims, const uint32_t* labels0, const uint32_t* mask0Buf, const float* pb0,
+                     const uint32_t* labels1, const uint32_t* mask1Buf, const float* pb1, int bins, double lo, double hi,
+                     int nThr, const double* thr, double normalizingArea, double normalizingLength, int useLogShape,
+                     const uint32_t* pairs, int nPairs)
+{
+  G = Results();
+  auto segImage0 = wrap<LImage>(labels0, dims), segImage1 = wrap<LImage>(labels1, dims);
+  LImage::Pointer mask0 = mask0Buf ? wrap<LImage>(mask0Buf, dims) : LImage::Pointer(nullptr);
+  LImage::Pointer mask1 = mask1Buf ? wrap<LImage>(mask1Buf, dims) : LImage::Pointer(nullptr);
+  auto pbImage0 = wrap<RImage>(pb0, dims), pbImage1 = wrap<RImage>(pb1, dims);
+  ImgList rImages0, rlImages0, bImages0, rImages1, rlImages1, bImages1;   // --rbi pb (prepareImages, hmt_util.hxx:17-56)
+  rImages0.emplace_back(pbImage0, (glia::uint)bins, std::make_pair(lo, hi)); bImages0.push_back(rImages0.back());
+  rImages1.emplace_back(pbImage1, (glia::uint)bins, std::make_pair(lo, hi)); bImages1.push_back(rImages1.back());
+  std::vector<double> boundaryThresholds(thr, thr + nThr);
+  if (normalizingArea <= 0.0) normalizingArea = imageVolume(dims);       // max over two images of equal extent
+  if (normalizingLength <= 0.0) normalizingLength = imageDiagonal(dims);
+  RegionMap rmap0(segImage0, mask0, false), rmap1(segImage1, mask1, false);
+  std::unordered_map<Label, std::shared_ptr<RegionFeatsWithLocation>> rfmap0, rfmap1;
+  for (auto const& rp : rmap0) {
+    auto f = std::make_shared<RegionFeatsWithLocation>();
+    f->generate(rp.second, normalizingArea, normalizingLength, pbImage0, boundaryThresholds, rImages0, rlImages0, bImages0, nullptr);
+    rfmap0[rp.first] = f;
+  }
+  for (auto const& rp : rmap1) {
+    auto f = std::make_shared<RegionFeatsWithLocation>();
+    f->generate(rp.second, normalizingArea, normalizingLength, pbImage1, boundaryThresholds, rImages1, rlImages1, bImages1, nullptr);
+    rfmap1[rp.first] = f;
+  }
+  std::unordered_map<std::pair<Label, Label>, int> overlaps;
+  stats::getOverlap(overlaps, segImage0, mask0, {BG_VAL}, segImage1, mask1, {BG_VAL});
+  std::vector<SectionClassificationFeats> sfeats(nPairs);
+  for (int i = 0; i < nPairs; ++i) {
+    Label r0 = pairs[2 * i], r1 = pairs[2 * i + 1];
+    auto rf0 = rfmap0.find(r0)->second.get();
+    auto rf1 = rfmap1.find(r1)->second.get();
+    sfeats[i].x0.generate(*rf0, *rf1, (double)clookup(overlaps, std::make_pair(r0, r1), 0));
+    if (rf0->shape->area > rf1->shape->area) { std::swap(r0, r1); std::swap(rf0, rf1); }
+    sfeats[i].x1 = rf0;
+    sfeats[i].x2 = rf1;
+  }
+  if (useLogShape) {
+    for (auto& f : rfmap0) f.second->log();
+    for (auto& f : rfmap1) f.second->log();
+    for (auto& f : sfeats) f.x0.log();
+  }
+  for (int i = 0; i < nPairs; ++i) {
+    std::vector<FVal> row;
+    sfeats[i].serialize(row);
+    G.dim = row.size();
+    G.merge_rows.insert(G.merge_rows.end(), row.begin(), row.end());
+  }
+  return 0;
+}
+#endif
 
 // Leaf RegionFeats under the reference's own parfor (the GLIA_MT path,
 // hmt/main_bc_feat.cxx:59-69) — timing only, for the CPU baseline.

@@ -77,6 +77,9 @@ def lib():
         L.go_merge_order_pb.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.go_pre_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p]
+        L.go_sc_row_dim.argtypes = [C.c_void_p]
+        L.go_sc_feat.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                 C.c_double, C.c_double, C.c_int, C.c_void_p]
         L.rf_oracle_load.restype = C.c_void_p
         L.rf_oracle_load.argtypes = [C.c_char_p]
         L.rf_oracle_from_arrays.restype = C.c_void_p
@@ -363,6 +366,34 @@ def ref_run_pb(mode, labels, pb, mask=None, type=1, size_thr=(), rpb_thr=0.0):
     if mode == 5:
         out["labels"] = _ref_get(L, "out_labels", np.uint32).reshape(labels.shape)
     return out
+
+
+def sc_feat(o0, o1, pairs, norm_area=0.0, norm_len=0.0, use_log=False):
+    """Section-classifier rows (hmt/main_sc_feat.cxx) from two Oracle objects built on the two sections."""
+    pairs = np.ascontiguousarray(pairs, np.uint32)
+    rows = np.zeros((len(pairs), lib().go_sc_row_dim(o0.h)))
+    st = lib().go_sc_feat(o0.h, o1.h, _ptr(o0.labels), _ptr(o0.mask), _ptr(o1.labels), _ptr(o1.mask), _ptr(pairs), len(pairs),
+                          norm_area, norm_len, int(use_log), _ptr(rows))
+    assert st == 0
+    return rows
+
+
+def ref_sc_feat(lab0, pb0, lab1, pb1, pairs, mask0=None, mask1=None, bins=16, thr=(0.2, 0.5, 0.8), norm_area=0.0, norm_len=0.0,
+                use_log=False):
+    """The compiled reference's sc_feat call sequence (oracle/ref_driver.cxx glia_ref_sc_feat; 2D, --rbi pb)."""
+    lab0, lab1 = np.ascontiguousarray(lab0, np.uint32), np.ascontiguousarray(lab1, np.uint32)
+    pb0, pb1 = np.ascontiguousarray(pb0, np.float32), np.ascontiguousarray(pb1, np.float32)
+    L = ref_lib(2)
+    dims = (C.c_int * 3)(*(list(lab0.shape[::-1]) + [1]))
+    m0 = None if mask0 is None else np.ascontiguousarray(mask0, np.uint32)
+    m1 = None if mask1 is None else np.ascontiguousarray(mask1, np.uint32)
+    pairs = np.ascontiguousarray(pairs, np.uint32)
+    t = (C.c_double * max(len(thr), 1))(*thr)
+    st = L.glia_ref_sc_feat(dims, _ptr(lab0), _ptr(m0), _ptr(pb0), _ptr(lab1), _ptr(m1), _ptr(pb1), C.c_int(bins), C.c_double(0.0),
+                            C.c_double(1.0), C.c_int(len(thr)), t, C.c_double(norm_area), C.c_double(norm_len),
+                            C.c_int(int(use_log)), _ptr(pairs), C.c_int(len(pairs)))
+    assert st == 0
+    return _ref_get(L, "merge_rows", np.float64).reshape(len(pairs), -1)
 
 
 def ref_bc_label(labels, truth, order, mask=None, use_f1=True, opt_split=False, global_opt=0, tweak=False, max_prec_drop=1.0):

@@ -405,3 +405,40 @@ def test_bc_label_matches_reference(case, kw):
         assert np.array_equal(gm, wm, equal_nan=True) and np.array_equal(gs, ws, equal_nan=True)
     if not kw:
         assert len(set(want.tolist())) == 2   # both labels occur: the test discriminates
+
+
+# ---- section-classifier features (hmt/main_sc_feat.cxx)
+def _sections(shape, nl, seed, um):
+    """Two adjacent sections: the second is the first shifted by a voxel with some superpixels relabelled."""
+    lab0, pb0 = synth.speckle_volume(shape, nl, seed=seed)
+    lab1 = np.roll(lab0, (1, 2), axis=(0, 1)).copy()
+    rng = np.random.default_rng(seed + 9)
+    lab1[rng.random(shape) < 0.05] = rng.integers(1, nl + 1)
+    pb1 = np.roll(pb0, (1, 2), axis=(0, 1)).copy()
+    m0 = (rng.random(shape) > 0.04).astype(np.uint32) if um else None
+    m1 = (rng.random(shape) > 0.04).astype(np.uint32) if um else None
+    ok0 = np.ones(shape, bool) if m0 is None else m0 != 0
+    ok1 = np.ones(shape, bool) if m1 is None else m1 != 0
+    l0, l1 = np.unique(lab0[ok0]), np.unique(lab1[ok1])
+    pairs = np.stack([rng.choice(l0, 40), rng.choice(l1, 40)], axis=1).astype(np.uint32)
+    pairs[:10, 1] = [l if l in set(l1.tolist()) else l1[0] for l in pairs[:10, 0]]   # overlapping pairs
+    return lab0, pb0, m0, lab1, pb1, m1, pairs
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(use_log=True), dict(norm_area=1.0, norm_len=1.0), dict(norm_area=1.0, norm_len=1.0, use_log=True)],
+                         ids=["default", "logs", "unnormalised", "unnormalised-logs"])
+@pytest.mark.parametrize("case", [((24, 28), 30, 121, False), ((27, 22), 18, 122, True)])
+def test_sc_feat_matches_reference(case, kw):
+    """hmt/main_sc_feat.cxx:27-117 through the reference's own feature classes (moments, Hu moments, eccentricity,
+    overlaps, location) against the C restatement: dyadic pb, so everything but pow / log terms is bit-identical."""
+    shape, nl, seed, um = case
+    if not _have_ref(2):
+        pytest.skip("oracle/_ref not available")
+    lab0, pb0, m0, lab1, pb1, m1, pairs = _sections(shape, nl, seed, um)
+    want = ol.ref_sc_feat(lab0, pb0, lab1, pb1, pairs, mask0=m0, mask1=m1, **kw)
+    o0 = ol.Oracle(lab0, pb0, ol.default_config(pb0), mask=m0)
+    o1 = ol.Oracle(lab1, pb1, ol.default_config(pb1), mask=m1)
+    got = ol.sc_feat(o0, o1, pairs, **kw)
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-300)
+    assert (got == want).mean() > 0.95
