@@ -64,7 +64,8 @@ EXPORTS = ["glia_b200_create", "glia_b200_destroy", "glia_b200_last_error", "gli
            "glia_b200_reference_orientation", "glia_b200_comm_unique_id", "glia_b200_comm_create",
            "glia_b200_comm_destroy", "glia_b200_build_sharded", "glia_b200_comm_last_exchange_ms",
            "glia_b200_bc_feat_sharded", "glia_b200_merge_order_pb", "glia_b200_pre_merge",
-           "glia_b200_segment_greedy", "glia_b200_rf_score_noalloc", "glia_b200_rf_score_noalloc_max_votes", "glia_b200_bc_label"]
+           "glia_b200_segment_greedy", "glia_b200_rf_score_noalloc", "glia_b200_rf_score_noalloc_max_votes", "glia_b200_bc_label",
+           "glia_b200_sc_row_dim", "glia_b200_sc_feat"]
 
 
 def lib():
@@ -106,6 +107,8 @@ def lib():
         L.glia_b200_rf_score_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_int, C.c_int, vp, vp, C.c_char_p, C.c_size_t]
         L.glia_b200_rf_score_noalloc_max_votes.argtypes = []
         L.glia_b200_rf_score_noalloc_max_votes.restype = C.c_size_t
+        L.glia_b200_sc_row_dim.argtypes = [vp]
+        L.glia_b200_sc_feat.argtypes = [vp, vp, vp, C.c_int64, C.c_double, C.c_double, C.c_int, vp]
         L.glia_b200_bc_label.argtypes = [vp, vp, vp, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, vp, vp, vp]
         L.glia_b200_segment_greedy.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
         L.glia_b200_merge_order_pb.argtypes = [vp, C.c_int, vp, vp, C.POINTER(C.c_int64)]
@@ -473,6 +476,14 @@ class MergeTreeBuilder:
         self._check(lib().glia_b200_pre_merge(self.h, _addr(thr), len(thr), C.c_double(rpb_thr), _addr(order), _addr(sal),
                                               C.byref(nm), _addr(out)))
         return dict(order=order[:nm.value], sal=sal[:nm.value], labels=out)
+
+    def sc_feat(self, other, pairs, norm_area=0.0, norm_len=0.0, use_log=False):
+        """hmt/main_sc_feat.cxx: rows for (label in this section, label in `other`) pairs."""
+        pairs = np.ascontiguousarray(pairs, np.uint32)
+        rows = np.zeros((len(pairs), lib().glia_b200_sc_row_dim(self.h)))
+        self._check(lib().glia_b200_sc_feat(self.h, other.h, _addr(pairs), len(pairs), C.c_double(norm_area), C.c_double(norm_len),
+                                            int(use_log), _addr(rows)))
+        return rows
 
     def bc_label(self, truth, order, use_f1=True, opt_split=False, global_opt=0, tweak=False, max_prec_drop=1.0):
         """hmt/main_bc_label_ri.cxx: (labels [n] in {-1 merge, +1 split}, merge scores, split scores)."""

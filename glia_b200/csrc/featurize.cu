@@ -128,6 +128,17 @@ int glia_region_blocks_device(glia_handle* h, int* xiOut) {
   return GLIA_OK;
 }
 
+// The same blocks under another feature configuration (normalisation / --logs of the caller: sc_feat.cu), into dBlk
+// [R][F.xiLen() + 2]; the handle's own blocks are left alone.
+int glia_region_blocks_cfg(glia_handle* h, const glia::FeatCfg& F, double* dBlk) {
+  if (h->R == 0) return GLIA_OK;
+  GraphView G = glia_graph_view(h);
+  region_blocks_kernel<<<(unsigned)((h->R + 127) / 128), 128, 0, h->stream>>>(F, G, F.xiLen(), dBlk, nullptr);
+  h->launches++;
+  GLIA_CUDA_CHECK(h, cudaGetLastError());
+  return GLIA_OK;
+}
+
 // dKeys [C][2] or null, dRows [C][dim] or null: device buffers
 int glia_featurize_init_device(glia_handle* h, uint32_t* dKeys, double* dRows) {
   if (h->C == 0) return GLIA_OK;

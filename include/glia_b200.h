@@ -149,6 +149,18 @@ GLIA_API int glia_b200_bc_label(glia_handle* h, const uint32_t* truth, const uin
                                 int use_pair_f1, int opt_split, int global_opt, int tweak, double max_prec_drop,
                                 int32_t* bc_labels, double* merge_score, double* split_score);
 
+/* SURVEY section 8f rank 4.  Section-classifier features (hmt/main_sc_feat.cxx:27-117; hmt/sc_feat.hxx): one row per listed
+ * pair (region of section 0, region of section 1) across two 2D sections of equal extent, each built into its own
+ * handle (same device, same feature configuration; not with use_median_feat / simple).  Row = RegionPairFeats
+ * (shape, centroid distance, overlap / set differences, central-moment, Hu-moment and eccentricity differences, image
+ * differences) | RegionFeatsWithLocation of the region with the smaller area | that of the larger one (RegionFeats +
+ * 7 central moments, 7 Hu moments, eccentricity: type/feat.hxx:191-268, alg/geometry.hxx:44-108).  pairs [n][2] =
+ * labels (host); norm_area / norm_length <= 0 = image volume / diagonal (main_sc_feat.cxx:48-56); use_log = --logs.
+ * rows [n][glia_b200_sc_row_dim] (host, or device when h0 was created with device_pointers). */
+GLIA_API int glia_b200_sc_row_dim(const glia_handle* h);
+GLIA_API int glia_b200_sc_feat(glia_handle* h0, glia_handle* h1, const uint32_t* pairs, int64_t n, double norm_area,
+                               double norm_length, int use_log, double* rows);
+
 /* Per-handle knobs (nothing on the data path reads the environment).  key "generic": value != 0 forces the
  * generic voxel kernel (test hook: fast == generic); "tz": planes (2D: rows) per tile of the fast voxel
  * kernel, "slots": its shared-memory table slots (0 = default); "notma": value != 0 makes the generic voxel kernel

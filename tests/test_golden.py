@@ -348,3 +348,47 @@ def test_cuda_reproduces_bclabel_golden(path):
         assert np.array_equal(l, z["bc_" + tag]), tag
         if kw.get("global_opt", 0) == 0:   # integer pair counts -> the same doubles, bit for bit
             assert np.array_equal(ms, z["ms_" + tag], equal_nan=True) and np.array_equal(ss, z["ss_" + tag], equal_nan=True), tag
+
+
+# ---------------------------------------------------------------- section-classifier features
+CGOLD = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scfeat", "*.npz")))
+SC_VARIANTS = {"default": dict(), "logs": dict(use_log=True), "raw": dict(norm_area=1.0, norm_len=1.0),
+               "raw_logs": dict(norm_area=1.0, norm_len=1.0, use_log=True)}
+
+
+def _sc_case(path):
+    z = np.load(path)
+    return z, (z["mask0"] if z["mask0"].size else None), (z["mask1"] if z["mask1"].size else None)
+
+
+def test_scfeat_fixtures_present():
+    assert len(CGOLD) >= 2
+
+
+@pytest.mark.parametrize("path", CGOLD, ids=[os.path.basename(p)[:-4] for p in CGOLD])
+def test_oracle_reproduces_scfeat_golden(path):
+    z, m0, m1 = _sc_case(path)
+    o0 = ol.Oracle(z["lab0"], z["pb0"], ol.default_config(z["pb0"]), mask=m0)
+    o1 = ol.Oracle(z["lab1"], z["pb1"], ol.default_config(z["pb1"]), mask=m1)
+    for tag, kw in SC_VARIANTS.items():
+        np.testing.assert_allclose(ol.sc_feat(o0, o1, z["pairs"], **kw), z["rows_" + tag], rtol=1e-12, atol=1e-300, err_msg=tag)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", CGOLD, ids=[os.path.basename(p)[:-4] for p in CGOLD])
+def test_cuda_reproduces_scfeat_golden(path):
+    """Rows within 1e-5 relative; absolute slack only where a third-order moment of a near-symmetric region cancels."""
+    from glia_b200 import api
+    z, m0, m1 = _sc_case(path)
+    g0 = api.MergeTreeBuilder(z["lab0"].shape, api.default_config(z["pb0"])).build(z["lab0"], z["pb0"], m0)
+    g1 = api.MergeTreeBuilder(z["lab1"].shape, api.default_config(z["pb1"])).build(z["lab1"], z["pb1"], m1)
+    for tag, kw in SC_VARIANTS.items():
+        got, want = g0.sc_feat(g1, z["pairs"], **kw), z["rows_" + tag]
+        assert got.shape == want.shape
+        if kw.get("use_log"):
+            # the logarithm of a central-moment difference (columns 15..21) that is rounding noise of the reference's
+            # pixel sums (regions of equal shape) carries no information: compared where the difference is real
+            raw = z["rows_" + ("raw" if "norm_len" in kw else "default")][:, 15:22]
+            noise = raw < 1e-7 * np.maximum(1.0, np.abs(raw).max(axis=0))
+            got[:, 15:22][noise] = want[:, 15:22][noise]
+        np.testing.assert_allclose(got, want, rtol=RTOL, atol=1e-9 * max(1.0, float(np.abs(want).max())), err_msg=tag)

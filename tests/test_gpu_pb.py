@@ -229,3 +229,46 @@ def test_cli_bc_label_ri(tmp_path):
         assert r.returncode == 0, r.stderr
         want, _, _ = bo.bc_labels(lab, truth, order, mask=mask, **kw)
         assert np.array_equal(np.loadtxt(out_f, dtype=np.int64), want), flags
+
+
+# ---------------------------------------------------------------- section-classifier features
+@pytest.mark.parametrize("case", [((40, 48), 60, 141, False), ((37, 45), 40, 142, True), ((256, 256), 0, 143, False)])
+def test_sc_feat_matches_oracle(case):
+    """hmt/main_sc_feat.cxx: every row against the C restatement (pinned to the reference's feature classes); the
+    integer-derived columns are bit-identical, moments agree to ~1e-12 (closed form from integer power sums against a
+    pixel-by-pixel double sum)."""
+    shape, nl, seed, um = case
+    rng = np.random.default_rng(seed)
+    if nl:
+        lab0, pb0 = synth.speckle_volume(shape, nl, seed=seed)
+    else:
+        lab0, pb0 = synth.voronoi_volume(shape, 11, seed=seed)
+    lab1 = np.roll(lab0, (1, 2), axis=(0, 1)).copy()
+    pb1 = np.roll(pb0, (1, 2), axis=(0, 1)).copy()
+    m0 = (rng.random(shape) > 0.04).astype(np.uint32) if um else None
+    m1 = (rng.random(shape) > 0.04).astype(np.uint32) if um else None
+    l0 = np.unique(lab0[np.ones(shape, bool) if m0 is None else m0 != 0])
+    l1 = np.unique(lab1[np.ones(shape, bool) if m1 is None else m1 != 0])
+    pairs = np.stack([rng.choice(l0, 200), rng.choice(l1, 200)], axis=1).astype(np.uint32)
+    both = np.intersect1d(l0, l1)
+    pairs[:60, 0] = pairs[:60, 1] = rng.choice(both, 60)      # overlapping pairs
+    o0 = ol.Oracle(lab0, pb0, ol.default_config(pb0), mask=m0)
+    o1 = ol.Oracle(lab1, pb1, ol.default_config(pb1), mask=m1)
+    g0 = api.MergeTreeBuilder(shape, api.default_config(pb0)).build(lab0, pb0, m0)
+    g1 = api.MergeTreeBuilder(shape, api.default_config(pb1)).build(lab1, pb1, m1)
+    for kw in (dict(), dict(use_log=True), dict(norm_area=1.0, norm_len=1.0), dict(norm_area=1.0, norm_len=1.0, use_log=True)):
+        want = ol.sc_feat(o0, o1, pairs, **kw)
+        got = g0.sc_feat(g1, pairs, **kw)
+        assert got.shape == want.shape
+        if kw.get("use_log"):
+            # --logs takes the logarithm of the central-moment differences (columns 15..21): where two regions have the
+            # same shape that difference is rounding noise of the pixel sums (1e-13) and its logarithm means nothing
+            raw = ol.sc_feat(o0, o1, pairs, **dict(kw, use_log=False))[:, 15:22]
+            noise = raw < 1e-7 * np.maximum(1.0, np.abs(raw).max(axis=0))
+            got[:, 15:22][noise] = want[:, 15:22][noise]
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-9 * max(1.0, float(np.abs(want).max())), err_msg=str(kw))
+        assert (got == want).mean() > 0.5
+    assert (want[:60, 7] > 0).any()                          # the overlap column is exercised
+    with pytest.raises(api.GliaError):
+        bad = pairs.copy(); bad[0, 0] = 4000000
+        g0.sc_feat(g1, bad)
