@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <map>
 #include <set>
+#include <queue>
 #include <unordered_map>
 #include <vector>
 #include <chrono>
@@ -43,7 +44,7 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
                    double* __restrict__ rows, double* __restrict__ sal, const double* __restrict__ med, int nMed,
                    double* __restrict__ rowsHost) {
   // stage / sal / med / rowsHost are pinned HOST buffers read and written in place (unified addressing): a merge is
-  // one launch and one synchronisation, no separate copies (58 -> ~25 us per merge on the chain's critical path);
+  // one launch and one synchronisation, no separate copies (58 -> 45 us per merge on the chain's critical path);
   // rows is device scratch (the row is re-read for the forest walk).
   extern __shared__ __align__(16) double srow[];
   __shared__ int shits;
@@ -52,9 +53,14 @@ merge_batch_kernel(const __grid_constant__ FeatCfg F, int m, const uint32_t* __r
   const RecLayout LR = F.reg, LE = F.edge;
   const int regW = LR.nAdd + LR.nMax + ((LR.nAdd + LR.nMax) & 1) + 2 * LR.nF64;
   const int edgeW = LE.nAdd + LE.nMax + ((LE.nAdd + LE.nMax) & 1) + 2 * LE.nF64;
-  const uint32_t* base = stage + (size_t)w * stageWords;
+  // the candidate's six records arrive in ONE coalesced read of the host-mapped staging buffer (word-by-word reads
+  // over PCIe by the featurising threads cost more than the copy they replaced)
+  uint32_t* sstage = (uint32_t*)(srow + ((F.dim + 1) & ~1));
+  for (int i = threadIdx.x; i < stageWords; i += MERGE_TPB) sstage[i] = stage[(size_t)w * stageWords + i];
+  const uint32_t* base = sstage;
   double* row = rows + (size_t)w * F.dim;
   if (threadIdx.x == 0) shits = 0;
+  __syncthreads();
   if ((threadIdx.x & 31) == 0 && threadIdx.x < 128) {  // four warps, one part of the row each
     auto regRec = [&](int k) {
       const uint32_t* p = base + (size_t)k * regW;
@@ -121,7 +127,12 @@ struct Greedy {
   std::vector<Rec> reg;                                          // region record per id
   std::vector<Rec> btot;                                         // boundary-of totals (add, f64 only)
   std::vector<std::vector<int>> nmOut;                           // non-mutual boundaries by source region
-  std::vector<std::map<int, Rec>> dm;                            // dm[x][w] = mutual boundaries x -> w
+  std::vector<std::unordered_map<int, Rec>> dm;                  // dm[x][w] = mutual boundaries x -> w
+  // per region and max word: the largest value over its boundary entries, the neighbour owning it (-1: a non-mutual
+  // entry, -2: none) and the largest over all OTHER entries.  Kept up to date across merges instead of re-scanned
+  // for every new candidate (the scans were most of the staging time, profiles/r2_merge_order_wall.txt).
+  struct Top2 { std::vector<uint32_t> b1, b2; std::vector<int> o1; bool valid = false; };
+  std::vector<Top2> t2;
   // median features only (median.cu): the base sets behind the records
   std::vector<std::map<int, std::vector<int>>> de;               // de[x][w] = base directed boundaries of dm[x][w]
   std::vector<std::vector<int>> mem;                             // base regions of a region id
@@ -214,7 +225,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
   CK(cudaStreamSynchronize(st));
   // ---- host state
   const int maxIds = 2 * R;
-  G.reg.resize(maxIds); G.btot.resize(maxIds); G.nmOut.resize(maxIds); G.dm.resize(maxIds);
+  G.reg.resize(maxIds); G.btot.resize(maxIds); G.nmOut.resize(maxIds); G.dm.resize(maxIds); G.t2.resize(maxIds);
   G.ufParent.resize(R); G.idOfRoot.resize(R); G.repBase.assign(maxIds, 0);
   for (int a = 0; a < R; ++a) {
     G.ufParent[a] = a; G.idOfRoot[a] = a; G.repBase[a] = a;
@@ -247,17 +258,22 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       for (int e = G.row[a]; e < G.row[a + 1]; ++e) if (G.rev[e] >= 0) G.de[a][G.eb[e]].assign(1, e);
     }
   }
-  std::map<Key, Item> table;
-  typedef std::tuple<double, unsigned long long, Key> QKey;
-  std::set<QKey> queue;
+  // The reference keeps an ordered table and a multimap queue (type/boundary_table.hxx:19-33).  Nothing here walks the
+  // table in key order (the keys touching a merge come from the adjacency), so it is a hash map; the queue is a binary
+  // heap with lazy deletion: an entry is live while the table still holds its key with the same insertion sequence.
+  auto tkey = [](const Key& k) { return ((unsigned long long)(unsigned)k.first << 32) | (unsigned)k.second; };
+  std::unordered_map<unsigned long long, Item> table;
+  table.reserve((size_t)C * 2 + 16);
+  typedef std::tuple<double, unsigned long long, Key> QKey;  // largest saliency first, among equals the latest insertion
+  std::priority_queue<QKey> queue;
   unsigned long long seq = 0;
   for (int c = 0; c < C; ++c) {  // ascending (min,max) key order == candidate order
     int e = cand[c];
     Item it; it.sal = sal0[c]; it.seq = seq++;
     if (rows) it.row.assign(rows0.begin() + (size_t)c * dim, rows0.begin() + (size_t)(c + 1) * dim);
     Key k(G.ea[e], G.eb[e]);
-    queue.insert(QKey(it.sal, it.seq, k));
-    table.emplace(k, std::move(it));
+    queue.push(QKey(it.sal, it.seq, k));
+    table.emplace(tkey(k), std::move(it));
   }
   rows0.clear(); rows0.shrink_to_fit();
   long long nfeat = C;
@@ -293,31 +309,41 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
   const bool trace = getenv("GLIA_B200_TRACE") != nullptr;
   double tBook = 0.0, tStage = 0.0, tDev = 0.0, tIns = 0.0;
   auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-  std::vector<uint32_t> best1, best2; std::vector<int> owner1;
-  auto top2 = [&](int X) {  // per max word: best, its owning neighbour (-1: non-mutual), second best
-    best1.assign(LE.nMax, 0); best2.assign(LE.nMax, 0); owner1.assign(LE.nMax, -2);
+  auto top2 = [&](int X) -> const Greedy::Top2& {  // per max word: best, its owning neighbour, best of the others
+    Greedy::Top2& t = G.t2[X];
+    if (t.valid) return t;
+    t.b1.assign(LE.nMax, 0); t.b2.assign(LE.nMax, 0); t.o1.assign(LE.nMax, -2);
     auto feed = [&](const uint32_t* mx, int own) {
       for (int i = 0; i < LE.nMax; ++i) {
         uint32_t v = mx[i];
-        if (v > best1[i]) { best2[i] = best1[i]; best1[i] = v; owner1[i] = own; }
-        else if (v > best2[i]) best2[i] = v;
+        if (v > t.b1[i]) { t.b2[i] = t.b1[i]; t.b1[i] = v; t.o1[i] = own; }
+        else if (v > t.b2[i]) t.b2[i] = v;
       }
     };
     for (auto& kv : G.dm[X]) feed(kv.second.mx.data(), kv.first);
     for (int e : G.nmOut[X]) feed(G.sMax.data() + (size_t)e * LE.nMax, -1);
+    t.valid = true;
+    return t;
   };
+  std::vector<int> seenStamp(maxIds, -1);
   while (!table.empty()) {
     const double tA = trace ? now() : 0.0;
     // top: largest saliency, among equals the most recently inserted (boundary_table.hxx:47-52)
-    QKey q = *queue.rbegin();
-    Key k01 = std::get<2>(q);
-    auto it01 = table.find(k01);
+    auto it01 = table.end();
+    Key k01;
+    for (;;) {  // skip heap entries whose table item is gone or was re-created since
+      const QKey& q = queue.top();
+      k01 = std::get<2>(q);
+      it01 = table.find(tkey(k01));
+      const bool live = it01 != table.end() && it01->second.seq == std::get<1>(q);
+      queue.pop();
+      if (live) break;
+    }
     const int r0 = k01.first, r1 = k01.second, r2 = nextId++;
     order[3 * (size_t)M] = label_of(r0); order[3 * (size_t)M + 1] = label_of(r1); order[3 * (size_t)M + 2] = label_of(r2);
     sal[M] = it01->second.sal;
     if (rows) memcpy(rows + (size_t)M * dim, it01->second.row.data(), 8 * (size_t)dim);
     ++M;
-    queue.erase(q);
     table.erase(it01);
     // ---- rmap.merge(r0, r1, r2) on the records
     G.reg[r2] = G.reg[r0]; G.reg[r2].merge(G.reg[r1]);
@@ -341,19 +367,35 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       }
     std::sort(keys.begin(), keys.end());
     std::vector<int> Ws;
-    {
-      std::set<int> seen;
-      for (auto& kw : keys) if (seen.insert(kw.second).second) Ws.push_back(kw.second);
-    }
-    // adjacency of r2 and of its neighbours
+    for (auto& kw : keys) if (seenStamp[kw.second] != M) { seenStamp[kw.second] = M; Ws.push_back(kw.second); }
+    // adjacency of r2 and of its neighbours (the records of r0 / r1 are moved, not copied: their maps are dropped below)
+    G.dm[r2].reserve(Ws.size() * 2 + 2);
     for (int W : Ws) {
-      Rec out; out.init(LE); Rec in; in.init(LE);
+      Rec out, in; bool haveOut = false, haveIn = false;
+      const uint32_t* vin[2] = {nullptr, nullptr};  // max words of W -> r0, W -> r1 before they are merged
+      Rec inParts[2];
+      int k = 0;
       for (int r : {r0, r1}) {
         auto f = G.dm[r].find(W);
-        if (f != G.dm[r].end()) out.merge(f->second);
+        if (f != G.dm[r].end()) { if (!haveOut) { out = std::move(f->second); haveOut = true; } else out.merge(f->second); }
         auto g = G.dm[W].find(r);
-        if (g != G.dm[W].end()) { in.merge(g->second); G.dm[W].erase(g); }
+        if (g != G.dm[W].end()) { inParts[k] = std::move(g->second); vin[k] = inParts[k].mx.data(); G.dm[W].erase(g); }
+        ++k;
       }
+      // W's cached maxima: its entries towards r0 / r1 become ONE entry towards r2 holding their maximum
+      Greedy::Top2& tw = G.t2[W];
+      if (tw.valid)
+        for (int i = 0; i < LE.nMax && tw.valid; ++i) {
+          if (tw.o1[i] != r0 && tw.o1[i] != r1) continue;       // the best entry is elsewhere: nothing changes
+          const uint32_t* other = tw.o1[i] == r0 ? vin[1] : vin[0];
+          const uint32_t vo = other ? other[i] : 0u;
+          if (vo != 0 && vo == tw.b2[i]) tw.valid = false;      // the runner-up may have been the other merged entry: rescan
+          else tw.o1[i] = r2;
+        }
+      for (int q = 0; q < 2; ++q)
+        if (vin[q]) { if (!haveIn) { in = std::move(inParts[q]); haveIn = true; } else in.merge(inParts[q]); }
+      if (!haveOut) out.init(LE);
+      if (!haveIn) in.init(LE);
       G.dm[r2].emplace(W, std::move(out));
       G.dm[W].emplace(r2, std::move(in));
       if (nMed) {
@@ -368,7 +410,8 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
         G.de[W].emplace(r2, std::move(li));
       }
     }
-    G.dm[r0].clear(); G.dm[r1].clear();
+    { std::unordered_map<int, Rec>().swap(G.dm[r0]); std::unordered_map<int, Rec>().swap(G.dm[r1]); }
+    G.t2[r0] = Greedy::Top2(); G.t2[r1] = Greedy::Top2();
     if (nMed) {
       G.de[r0].clear(); G.de[r1].clear();
       G.mem[r2] = std::move(G.mem[r0]);
@@ -377,9 +420,12 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     }
     G.ufUnion(r0, r1, r2);
     // erase the stale table items
-    for (auto& kw : keys) {
-      auto t = table.find(kw.first);
-      if (t != table.end()) { queue.erase(QKey(t->second.sal, t->second.seq, kw.first)); table.erase(t); }
+    for (auto& kw : keys) table.erase(tkey(kw.first));  // their heap entries die with them
+    if (queue.size() > 4 * table.size() + 4096) {       // mostly dead entries: rebuild the heap from the table
+      std::vector<QKey> live;
+      live.reserve(table.size());
+      for (auto& kv : table) live.push_back(QKey(kv.second.sal, kv.second.seq, Key((int)(kv.first >> 32), (int)(unsigned)kv.first)));
+      queue = std::priority_queue<QKey>(std::less<QKey>(), std::move(live));
     }
     const size_t m = Ws.size();
     if (!m) continue;
@@ -391,8 +437,8 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
     // ---- stage the six records of every new candidate (X = W, Y = r2)
     std::unordered_map<int, std::vector<int>> nmByTarget;
     for (int e : G.nmOut[r2]) { int t = G.cur(G.eb[e]); if (t != r2) nmByTarget[t].push_back(e); }
-    top2(r2);
-    std::vector<uint32_t> yb1 = best1, yb2 = best2; std::vector<int> yo1 = owner1;
+    const Greedy::Top2& ty = top2(r2);
+    const std::vector<uint32_t>&yb1 = ty.b1, &yb2 = ty.b2; const std::vector<int>& yo1 = ty.o1;
     uint32_t* p = hStage;
     // records are written straight into the staging buffer; the two scratch records below are reused for
     // every candidate (no allocation per candidate)
@@ -424,7 +470,8 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       const Rec& dWY = G.dm[W][r2]; const Rec& dYW = G.dm[r2][W];
       put_rec(p, G.reg[W]);
       put_rec(p, G.reg[r2]);
-      top2(W);
+      const Greedy::Top2& tw = top2(W);
+      const std::vector<uint32_t>&best1 = tw.b1, &best2 = tw.b2; const std::vector<int>& owner1 = tw.o1;
       const Rec& bx = G.btot[W];   // boundary-of totals: add + f64; the max words are best1 / yb1
       const Rec& by = G.btot[r2];
       for (int i = 0; i < LE.nAdd; ++i) bzz.add[i] = bx.add[i] + by.add[i] - dWY.add[i] - dYW.add[i];
@@ -486,7 +533,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       memcpy(hMed, med.data(), 8 * med.size());
     }
     const double tC = trace ? now() : 0.0;
-    merge_batch_kernel<<<(unsigned)m, MERGE_TPB, 8 * (size_t)dim, st>>>(
+    merge_batch_kernel<<<(unsigned)m, MERGE_TPB, 8 * (size_t)((dim + 1) & ~1) + 4 * (size_t)stageWords, st>>>(
         h->fc, (int)m, hStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, hSal,
         nMed ? hMed : nullptr, nMed, rows ? hRows : nullptr);
     h->launches++;
@@ -497,8 +544,8 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       Item it; it.sal = hSal[j]; it.seq = seq++;
       if (rows) it.row.assign(hRows + j * dim, hRows + (j + 1) * dim);
       Key k(Ws[j], r2);
-      queue.insert(QKey(it.sal, it.seq, k));
-      table.emplace(k, std::move(it));
+      queue.push(QKey(it.sal, it.seq, k));
+      table.emplace(tkey(k), std::move(it));
     }
     if (trace) { const double tE = now(); tBook += tB - tA; tStage += tC - tB; tDev += tD - tC; tIns += tE - tD; }
   }
