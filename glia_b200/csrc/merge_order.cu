@@ -410,8 +410,6 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
         G.de[W].emplace(r2, std::move(li));
       }
     }
-    { std::unordered_map<int, Rec>().swap(G.dm[r0]); std::unordered_map<int, Rec>().swap(G.dm[r1]); }
-    G.t2[r0] = Greedy::Top2(); G.t2[r1] = Greedy::Top2();
     if (nMed) {
       G.de[r0].clear(); G.de[r1].clear();
       G.mem[r2] = std::move(G.mem[r0]);
@@ -419,16 +417,22 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
       G.mem[r1].clear(); G.mem[r1].shrink_to_fit();
     }
     G.ufUnion(r0, r1, r2);
-    // erase the stale table items
-    for (auto& kw : keys) table.erase(tkey(kw.first));  // their heap entries die with them
-    if (queue.size() > 4 * table.size() + 4096) {       // mostly dead entries: rebuild the heap from the table
-      std::vector<QKey> live;
-      live.reserve(table.size());
-      for (auto& kv : table) live.push_back(QKey(kv.second.sal, kv.second.seq, Key((int)(kv.first >> 32), (int)(unsigned)kv.first)));
-      queue = std::priority_queue<QKey>(std::less<QKey>(), std::move(live));
-    }
+    // Clean-up that neither the staging below nor the batch kernel reads - the emptied maps of r0 / r1, the stale table
+    // items, the heap rebuild - runs AFTER the launch, while the GPU featurises and scores the new candidates; it only
+    // has to be done before the next pop.
+    auto finish_merge = [&]() {
+      { std::unordered_map<int, Rec>().swap(G.dm[r0]); std::unordered_map<int, Rec>().swap(G.dm[r1]); }
+      G.t2[r0] = Greedy::Top2(); G.t2[r1] = Greedy::Top2();
+      for (auto& kw : keys) table.erase(tkey(kw.first));  // their heap entries die with them
+      if (queue.size() > 4 * table.size() + 4096) {       // mostly dead entries: rebuild the heap from the table
+        std::vector<QKey> live;
+        live.reserve(table.size());
+        for (auto& kv : table) live.push_back(QKey(kv.second.sal, kv.second.seq, Key((int)(kv.first >> 32), (int)(unsigned)kv.first)));
+        queue = std::priority_queue<QKey>(std::less<QKey>(), std::move(live));
+      }
+    };
     const size_t m = Ws.size();
-    if (!m) continue;
+    if (!m) { finish_merge(); continue; }
     {
       cudaError_t e = ensure_batch(m);
       if (e != cudaSuccess) { h->err = std::string("merge_order_bc batch buffers: ") + cudaGetErrorString(e); return GLIA_E_CUDA; }
@@ -537,6 +541,7 @@ extern "C" int glia_b200_merge_order_bc(glia_handle* h, const glia_rf* rf, uint3
         h->fc, (int)m, hStage, stageWords, (const RfNode16*)rf->d_nodes, rf->d_treeOff, rf->dist, li, dRows, hSal,
         nMed ? hMed : nullptr, nMed, rows ? hRows : nullptr);
     h->launches++;
+    finish_merge();  // overlapped with the kernel
     CK(cudaStreamSynchronize(st));
     const double tD = trace ? now() : 0.0;
     nfeat += (long long)m;
